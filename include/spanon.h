@@ -1,0 +1,226 @@
+/*
+ * spanon.h -- C ABI of libspanon.so, the B200 (sm_100a) implementation of the
+ * Fbank + anonymizer hot path of viswavi/speech-anonymization.
+ *
+ * The reference has no FFI layer: its boundary is a set of PyTorch module calls
+ * (SURVEY.md section 8b).  Each entry point below replaces the library-kernel
+ * sequence behind one of those calls; the reference call site is cited next to
+ * it.  Conventions:
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless
+ *     its name ends in _host;
+ *   - the caller owns all memory (inputs, outputs, workspace); the library
+ *     never frees or retains a pointer past the call;
+ *   - `stream` is a cudaStream_t passed as void*; calls only enqueue work and
+ *     never synchronise the host (except the *_host convenience entry points);
+ *   - return value 0 = success, negative = SpanonStatus error code
+ *     (spanon_strerror() gives the text).
+ */
+#ifndef SPANON_H_
+#define SPANON_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SPANON_API __attribute__((visibility("default")))
+#else
+#define SPANON_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum SpanonStatus {
+  SPANON_OK = 0,
+  SPANON_ERR_BAD_SHAPE = -1,     /* a size is <= 0, inconsistent or unsupported   */
+  SPANON_ERR_NULL_POINTER = -2,  /* a required pointer is NULL                    */
+  SPANON_ERR_MISALIGNED = -3,    /* a pointer breaks the stated alignment         */
+  SPANON_ERR_WORKSPACE = -4,     /* workspace smaller than *_workspace_bytes()    */
+  SPANON_ERR_UNSUPPORTED = -5,   /* configuration outside what the kernels cover  */
+  SPANON_ERR_CUDA = -6,          /* a CUDA runtime call / kernel launch failed    */
+  SPANON_ERR_ARCH = -7           /* device is not sm_100                          */
+} SpanonStatus;
+
+SPANON_API const char* spanon_strerror(int status);
+/* Version of this ABI (bumped on any signature change). */
+SPANON_API int spanon_abi_version(void);
+/* Number of kernels launched by this library since process start (bench.py's gpu_launches). */
+SPANON_API uint64_t spanon_launch_count(void);
+/* Last CUDA error string seen by the library (empty if none). */
+SPANON_API const char* spanon_last_cuda_error(void);
+
+/* ------------------------------------------------------------------------- *
+ * Fbank: STFT -> power spectrum -> mel projection -> dB (+ per-utterance max)
+ * replaces  Fbank.forward            speechbrain/speechbrain/lobes/features.py:126-143
+ *           STFT.forward             speechbrain/speechbrain/processing/features.py:133-188
+ *           spectral_magnitude       speechbrain/speechbrain/processing/features.py:327-356
+ *           Filterbank.forward       speechbrain/speechbrain/processing/features.py:490-560
+ *           Filterbank._amplitude_to_DB                                     :691-712
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonFbankCfg {
+  int32_t n_fft;        /* 400 in every reference config                              */
+  int32_t win_length;   /* samples (reference: round(sample_rate/1000*25) = 400)      */
+  int32_t hop_length;   /* samples (160)                                              */
+  int32_t n_mels;       /* 80 (configs) or 40 (class default)                         */
+  float amin;           /* 1e-10                                                      */
+  float multiplier;     /* 10 (power spectrogram)                                     */
+  float db_offset;      /* multiplier * log10(max(amin, ref_value)) = 0               */
+  float top_db;         /* 80                                                         */
+  const float* window;  /* [win_length] analysis window (periodic Hamming)            */
+  const int32_t* mel_start; /* [n_mels] first STFT bin with a non-zero weight         */
+  const int32_t* mel_len;   /* [n_mels] number of consecutive bins                    */
+  const int32_t* mel_off;   /* [n_mels] offset of the filter's weights in mel_w       */
+  const float* mel_w;       /* packed filter weights                                  */
+} SpanonFbankCfg;
+
+/* Number of frames torch.stft(center=True) produces: 1 + n_samples / hop. */
+SPANON_API int64_t spanon_num_frames(int64_t n_samples, int32_t hop_length);
+
+/* pcm [B, n_samples] fp32 (row stride pcm_stride elements) -> out [B, T, n_mels]
+ * fp32 UNCLAMPED dB, and utt_max [B] int32 order-preserving keys of the per-utterance
+ * maximum (over all T frames incl. the zero padded tail, like the reference).
+ * Follow with spanon_fbank_clamp() (or let a fused consumer apply the floor). */
+SPANON_API int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
+                     float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream);
+
+/* x = max(x, max_b - top_db) in place on [B, T, n_mels]  (features.py:706-710). */
+SPANON_API int spanon_fbank_clamp(float* feats, const int32_t* utt_max, int64_t B, int64_t T,
+                       int64_t n_mels, float top_db, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * InputNormalization statistics and application
+ * replaces  InputNormalization.forward / _compute_current_stats
+ *           speechbrain/speechbrain/processing/features.py:998-1148
+ *           and the x36 time padding of speechbrain_convae_train.py:62-63
+ * ------------------------------------------------------------------------- */
+/* Per utterance: n = round_half_even(rel_len[b] * T) valid frames; mean and UNBIASED
+ * std over them, std floored at eps (1e-10).  n_valid [B] receives n (bit exact mask).
+ * If utt_max != NULL the top_db floor is applied to the values first (fused clamp). */
+SPANON_API int spanon_norm_stats(const float* feats, const float* rel_len, int64_t B, int64_t T,
+                      int64_t F, const int32_t* utt_max, float top_db, int mean_norm,
+                      int std_norm, float eps, float* mean_out, float* std_out,
+                      int32_t* n_valid, void* stream);
+
+/* out[b,t,:] = (x - mean)/std for t < T, 0 for T <= t < T_pad.  mean/std are [F]
+ * (stat_bstride = 0) or [B, F] (stat_bstride = F).  In place allowed when T_pad == T. */
+SPANON_API int spanon_norm_apply(const float* feats, float* out, const float* mean, const float* std,
+                      int64_t stat_bstride, const int32_t* utt_max, float top_db,
+                      int64_t B, int64_t T, int64_t T_pad, int64_t F, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * FullyConnectedAutoencoder forward (eval-mode BatchNorm)
+ * replaces  FullyConnectedAutoencoder.forward  models/FullyConnected.py:147-159
+ *           FullyConnSexClassifier.forward     models/FullyConnected.py:90-104
+ *           StatisticsPooling.forward          speechbrain/speechbrain/nnet/pooling.py:263-312
+ * Weight pointers are the module's own fp32 parameter storages (PyTorch layouts).
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonBatchNorm {
+  const float* weight; const float* bias; const float* running_mean; const float* running_var;
+} SpanonBatchNorm;
+
+typedef struct SpanonFcaeWeights {
+  int32_t in_dim;                        /* mfcc_feature_dim (80) */
+  const float* enc_w[3]; const float* enc_b[3];   /* in->60, 60->40, 40->20 */
+  const float* dec_w[3]; const float* dec_b[3];   /* 20->40, 40->60, 60->80 */
+  SpanonBatchNorm clf_norm;                        /* BatchNorm1d(20)        */
+  const float* init_w[2]; const float* init_b[2]; /* 20->40, 40->40         */
+  const float* cls_w[4]; const float* cls_b[4];   /* 80->40, 40->40, 40->20, 20->2 */
+  SpanonBatchNorm cls_bn1;                         /* BatchNorm1d(40) after cls 0 */
+  SpanonBatchNorm cls_bn6;                         /* BatchNorm1d(20) after cls 2 */
+} SpanonFcaeWeights;
+
+SPANON_API size_t spanon_fcae_workspace_bytes(int64_t B, int64_t T);
+/* feats [B,T,in_dim] -> recon [B,T,80], logp [B,2].  pool_noise [B,40] is the tensor
+ * StatisticsPooling adds to the mean (NULL = none).  If norm_mean != NULL the input is
+ * raw Fbank dB and (clamp, (x-mean)/std) is applied on load (fused path). */
+SPANON_API int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, const float* pool_noise,
+                    const float* norm_mean, const float* norm_std, const int32_t* utt_max,
+                    float top_db, float* recon, float* logp, void* workspace,
+                    size_t workspace_bytes, int64_t B, int64_t T, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * ConvAutoencoder forward (eval-mode BatchNorm in the TDNN sex classifier)
+ * replaces  ConvAutoencoder.forward     models/ConvAutoEncoder.py:178-200
+ *           TDNNSexClassifier.forward   models/ConvAutoEncoder.py:57-69
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonConvAEWeights {
+  /* encoder.{0,2,5,8,11}: Conv1d weight [Cout,Cin,k], bias [Cout] */
+  const float* enc_w[5]; const float* enc_b[5];
+  /* encoder.{3,6,9,12}: InstanceNorm1d affine weight/bias */
+  const float* enc_in_w[4]; const float* enc_in_b[4];
+  /* decoder.{0,1,4,5,8}: Conv1d [Cout,Cin,k] / ConvTranspose1d [Cin,Cout,k] */
+  const float* dec_w[5]; const float* dec_b[5];
+  /* decoder.{2,6}: InstanceNorm1d affine */
+  const float* dec_in_w[2]; const float* dec_in_b[2];
+  /* sex_classifier.norm, .tdnn.{0,3,6} convs, .tdnn.{2,5,8} BatchNorm1d(128) */
+  SpanonBatchNorm clf_norm;
+  const float* tdnn_w[3]; const float* tdnn_b[3];
+  SpanonBatchNorm tdnn_bn[3];
+  /* sex_classifier.classify.{0,3,6} Linear, .{2,5} BatchNorm1d */
+  const float* cls_w[3]; const float* cls_b[3];
+  SpanonBatchNorm cls_bn[2];
+} SpanonConvAEWeights;
+
+enum { SPANON_PREC_FP32 = 0, SPANON_PREC_BF16 = 1 };
+
+typedef struct SpanonConvAEOpts {
+  int32_t precision;      /* SPANON_PREC_FP32: fp32 activations + CUDA-core FMA (<=1e-4 parity);
+                             SPANON_PREC_BF16: bf16 activations + tcgen05 tensor cores (<=1e-2) */
+  int32_t chunk_utts;     /* utterances per L2-resident chunk; 0 = library default             */
+  int32_t skip_classifier;/* 1 = do not run the sex classifier (logp untouched)                */
+  int32_t reserved;
+} SpanonConvAEOpts;
+
+SPANON_API size_t spanon_convae_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts);
+/* feats [B,T,F] fp32 with (T*F) % 4 == 0 -> recon [B,T,F] fp32, logp [B,2].
+ * pool_noise [B,128] as above.  Fused-normalisation inputs (all NULL for plain feats):
+ * feats is then raw Fbank dB [B, T_valid, F], rows >= T_valid are the zero padding. */
+SPANON_API int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* w, const float* pool_noise,
+                      const float* norm_mean, const float* norm_std, const int32_t* utt_max,
+                      float top_db, int64_t T_valid, float* recon, float* logp,
+                      void* workspace, size_t workspace_bytes, int64_t B, int64_t T, int64_t F,
+                      const SpanonConvAEOpts* opts, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Loss statistics
+ * replaces  CosineSimilarityLoss.forward   utils/cosine_similarity_loss.py:53-56
+ *           _pairwise_dists / ClusterMI._mutual_information  utils/ClusterMI.py:12-63,88-121
+ * ------------------------------------------------------------------------- */
+/* x1,x2 [B,T,D] -> loss[0] = sum_{b,t}(1 - cos(x1,x2)) / T ; optional per-row 1-cos in
+ * row_loss [B*T] (NULL to skip). eps = 1e-6 in the reference. */
+SPANON_API int spanon_cosine_loss(const float* x1, const float* x2, int64_t B, int64_t T, int64_t D,
+                       float eps, float* loss, float* row_loss, void* stream);
+/* Gradients of the above wrt x1 and x2 scaled by grad_out[0] (either may be NULL). */
+SPANON_API int spanon_cosine_loss_bwd(const float* x1, const float* x2, const float* grad_out, int64_t B,
+                           int64_t T, int64_t D, float eps, float* gx1, float* gx2, void* stream);
+
+/* Batched kNN mutual-information statistics.  X [Ntot, D]; for each of `n_sets` index
+ * sets idx[s, 0..N) (NULL = one set 0..N-1) with labels y[Ntot] (int32):
+ *   dists [n_sets, N, N] cosine distances (NULL to skip the store),
+ *   m_i   [n_sets, N]    neighbour counts  (ClusterMI.py:115),
+ *   mi    [n_sets]       MI in bits        (ClusterMI.py:120-121). */
+SPANON_API int spanon_knn_mi_stats(const float* X, const int32_t* y, const int32_t* idx, int64_t n_sets,
+                        int64_t N, int64_t D, int32_t n_classes, int32_t k, float* dists,
+                        int32_t* m_i, float* mi, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * End-to-end convenience entry point with HOST buffers (bench.py's e2e leg and
+ * the ctypes binding shown in INTEGRATION.md): copies pcm H2D, runs
+ * Fbank -> clamp -> (x-mean)/std -> pad -> anonymizer, copies recon/logp D2H and
+ * synchronises.  kind: 0 = ConvAutoencoder, 1 = FullyConnectedAutoencoder.
+ * `weights` points to a SpanonConvAEWeights / SpanonFcaeWeights of DEVICE pointers.
+ * dev_workspace must hold spanon_anonymize_workspace_bytes().
+ * ------------------------------------------------------------------------- */
+SPANON_API size_t spanon_anonymize_workspace_bytes(int kind, int64_t B, int64_t n_samples, int32_t hop_length,
+                                        int32_t n_mels, const SpanonConvAEOpts* opts);
+SPANON_API int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B, int64_t n_samples,
+                          const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                          const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                          float* recon_host, float* logp_host, void* dev_workspace,
+                          size_t dev_workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPANON_H_ */

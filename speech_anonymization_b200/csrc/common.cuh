@@ -1,0 +1,93 @@
+// Shared helpers for libspanon (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+#include "../../include/spanon.h"
+
+namespace spanon {
+
+extern std::atomic<uint64_t> g_launch_count;
+void set_last_cuda_error(const char* what, cudaError_t e);
+
+inline int check_launch(const char* what) {
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_cuda_error(what, e);
+    return SPANON_ERR_CUDA;
+  }
+  return SPANON_OK;
+}
+
+#define SPANON_CUDA_TRY(expr)                                   \
+  do {                                                          \
+    cudaError_t _e = (expr);                                    \
+    if (_e != cudaSuccess) {                                    \
+      ::spanon::set_last_cuda_error(#expr, _e);                 \
+      return SPANON_ERR_CUDA;                                   \
+    }                                                           \
+  } while (0)
+
+#define SPANON_TRY(expr)            \
+  do {                              \
+    int _s = (expr);                \
+    if (_s != SPANON_OK) return _s; \
+  } while (0)
+
+// Order-preserving float <-> int32 key so that atomicMax(int) orders floats.
+__host__ __device__ inline int32_t float_to_key(float f) {
+#ifdef __CUDA_ARCH__
+  int32_t i = __float_as_int(f);
+#else
+  int32_t i; memcpy(&i, &f, 4);
+#endif
+  return i >= 0 ? i : (i ^ 0x7FFFFFFF);
+}
+__host__ __device__ inline float key_to_float(int32_t k) {
+  int32_t i = k >= 0 ? k : (k ^ 0x7FFFFFFF);
+#ifdef __CUDA_ARCH__
+  return __int_as_float(i);
+#else
+  float f; memcpy(&f, &i, 4); return f;
+#endif
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float silu_precise(float x) { return x / (1.0f + expf(-x)); }
+// x*sigmoid(x) = h + h*tanh(h), h = x/2 : one MUFU op (tanh.approx), ~2^-11 rel. error.
+__device__ __forceinline__ float silu_fast(float x) {
+  float h = 0.5f * x, t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  return fmaf(h, t, h);
+}
+
+__device__ __forceinline__ float to_float(float v) { return v; }
+__device__ __forceinline__ float to_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_float(float v);
+template <> __device__ __forceinline__ float from_float<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+
+inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+}  // namespace spanon

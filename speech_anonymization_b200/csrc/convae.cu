@@ -1,0 +1,528 @@
+// ConvAutoencoder forward (models/ConvAutoEncoder.py:136-200) lowered to tap GEMMs.
+//
+// The reference flattens the [B,T,F] feature grid to ONE 1-D signal of length L = T*F
+// with a single channel (:181,188) and runs ten 1-D convolutions over it; the adversarial
+// TDNN sex classifier (:30-69) reads the 128-channel bottleneck.  Here:
+//   encoder.0 (1->32, k15)            first_layer_kernel   (CUDA cores; K = 15 is too thin for UMMA)
+//   encoder.2..11, decoder.0..8, tdnn tap GEMMs            (tapgemm.cuh; tcgen05 in bf16 mode)
+//   InstanceNorm1d                    statistics in the producer's epilogue, affine + SiLU in
+//                                     the consumer's operand load (instnorm_finalize_kernel
+//                                     turns the sums into per-(b,c) scale/shift)
+//   eval-mode BatchNorm1d             folded into per-channel scale/shift (bn_fold_kernel)
+//   reshape + StatisticsPooling       pool_kernel on the reference's channels-first memory image
+//   classify MLP + log_softmax        clf_head_kernel
+// Utterances are processed in chunks sized so that a layer's output is still in the 126 MB L2
+// when the next layer reads it.
+#include "tapgemm.cuh"
+#include <algorithm>
+#include <math.h>
+
+namespace spanon {
+int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
+
+namespace {
+
+// ------------------------------------------------------------------ weight packing
+enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2 };
+
+// Source value of packed element (tap, civ, cov); cin/cout/k are the REAL layer sizes.
+__device__ __forceinline__ float packed_src(const float* __restrict__ w, int mode, int cin, int cout, int k,
+                                            int tap, int civ, int cov) {
+  if (mode == PACK_CONV_S1) {            // Conv1d weight [cout][cin][k]
+    if (cov >= cout) return 0.f;         // padded output channels (decoder.8)
+    return w[((int64_t)cov * cin + civ) * k + tap];
+  } else if (mode == PACK_CONV_S2) {     // input pair rows: civ = half*cin + ci, t = 2*tap + half
+    const int half = civ / cin, ci = civ - half * cin;
+    const int t = 2 * tap + half;
+    if (t >= k) return 0.f;
+    return w[((int64_t)cov * cin + ci) * k + t];
+  } else {                               // ConvTranspose1d weight [cin][cout][k]; cov = phase*cout + co
+    const int phase = cov / cout, co = cov - phase * cout;
+    const int t = 4 - 2 * tap + phase;   // shifts -1,0,+1 <-> taps (4|-), (2|3), (0|1)
+    if (t >= k) return 0.f;
+    return w[((int64_t)civ * cout + co) * k + t];
+  }
+}
+
+// fp32 [ntaps][cin_v][cout_v]
+__global__ void pack_f32_kernel(const float* __restrict__ w, float* __restrict__ dst, int mode, int cin, int cout,
+                                int k, int ntaps, int cin_v, int cout_v) {
+  const int64_t n = (int64_t)ntaps * cin_v * cout_v;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cov = (int)(i % cout_v);
+    const int civ = (int)((i / cout_v) % cin_v);
+    const int tap = (int)(i / ((int64_t)cout_v * cin_v));
+    dst[i] = packed_src(w, mode, cin, cout, k, tap, civ, cov);
+  }
+}
+
+// bf16 UMMA K-major core-matrix layout [ntaps][cin_v/8][cout_v][8]
+__global__ void pack_umma_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int mode, int cin,
+                                 int cout, int k, int ntaps, int cin_v, int cout_v) {
+  const int64_t n = (int64_t)ntaps * cin_v * cout_v;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i % 8);
+    const int cov = (int)((i / 8) % cout_v);
+    const int kc = (int)((i / (8 * (int64_t)cout_v)) % (cin_v / 8));
+    const int tap = (int)(i / ((int64_t)cout_v * cin_v));
+    dst[i] = __float2bfloat16_rn(packed_src(w, mode, cin, cout, k, tap, kc * 8 + e, cov));
+  }
+}
+
+// ------------------------------------------------------------------ small fusions
+__global__ void bn_fold_kernel(SpanonBatchNorm bn, int C, float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) {
+    const float s = bn.weight[c] / sqrtf(bn.running_var[c] + 1e-5f);
+    scale[c] = s;
+    shift[c] = bn.bias[c] - bn.running_mean[c] * s;
+  }
+}
+
+// nn.InstanceNorm1d(affine=True): biased variance over the sequence, eps 1e-5
+__global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
+                                         const float* __restrict__ beta, int B, int C, double count,
+                                         float* __restrict__ scale, float* __restrict__ shift) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B * C) {
+    const int c = i % C;
+    const double mean = stats[2 * i] / count;
+    double var = stats[2 * i + 1] / count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const float rstd = (float)(1.0 / sqrt(var + 1e-5));
+    const float s = gamma[c] * rstd;
+    scale[i] = s;
+    shift[i] = beta[c] - (float)mean * s;
+  }
+}
+
+// ------------------------------------------------------------------ encoder.0 (1 -> 32, k15, p7) + SiLU
+constexpr int FL_NT = 256;
+template <typename TAct, bool FAST_ACT>
+__global__ void __launch_bounds__(FL_NT)
+first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64_t n_valid /*valid elems*/, int L,
+                   int F, const float* __restrict__ norm_mean, const float* __restrict__ norm_std,
+                   const int32_t* __restrict__ utt_max, float top_db, const float* __restrict__ w /*[32][1][15]*/,
+                   const float* __restrict__ bias, TAct* __restrict__ out, int64_t out_bstride) {
+  __shared__ float sig[FL_NT + 14];
+  __shared__ __align__(16) float ws[15 * 32];
+  __shared__ float bs[32];
+  const int tid = threadIdx.x, b = blockIdx.y;
+  const int l0 = blockIdx.x * FL_NT;
+  const float* x = feats + (int64_t)b * feats_bstride;
+  const float floor_db = utt_max ? key_to_float(utt_max[b]) - top_db : -INFINITY;
+  for (int i = tid; i < FL_NT + 14; i += FL_NT) {
+    const int l = l0 - 7 + i;
+    float v = 0.f;
+    if (l >= 0 && l < L && (int64_t)l < n_valid) {
+      v = __ldg(x + l);
+      if (norm_mean) {
+        const int f = l % F;
+        v = (fmaxf(v, floor_db) - __ldg(norm_mean + f)) / __ldg(norm_std + f);
+      }
+    }
+    sig[i] = v;
+  }
+  for (int i = tid; i < 15 * 32; i += FL_NT) {
+    const int t = i / 32, c = i - t * 32;
+    ws[i] = __ldg(w + c * 15 + t);
+  }
+  if (tid < 32) bs[tid] = __ldg(bias + tid);
+  __syncthreads();
+  const int l = l0 + tid;
+  float acc[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) acc[c] = bs[c];
+#pragma unroll
+  for (int t = 0; t < 15; ++t) {
+    const float xv = sig[tid + t];
+    const float4* w4 = reinterpret_cast<const float4*>(ws + t * 32);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const float4 wv = w4[q];
+      acc[4 * q + 0] = fmaf(xv, wv.x, acc[4 * q + 0]);
+      acc[4 * q + 1] = fmaf(xv, wv.y, acc[4 * q + 1]);
+      acc[4 * q + 2] = fmaf(xv, wv.z, acc[4 * q + 2]);
+      acc[4 * q + 3] = fmaf(xv, wv.w, acc[4 * q + 3]);
+    }
+  }
+  if (l < L) {
+    TAct* o = out + (int64_t)b * out_bstride + (int64_t)l * 32;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) acc[c] = FAST_ACT ? silu_fast(acc[c]) : silu_precise(acc[c]);
+    if (sizeof(TAct) == 4) {
+      float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) o4[q] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+    } else {
+      uint4* o4 = reinterpret_cast<uint4*>(o);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(acc[8 * q + 0], acc[8 * q + 1]);
+        __nv_bfloat162 h1 = __floats2bfloat162_rn(acc[8 * q + 2], acc[8 * q + 3]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[8 * q + 4], acc[8 * q + 5]);
+        __nv_bfloat162 h3 = __floats2bfloat162_rn(acc[8 * q + 6], acc[8 * q + 7]);
+        uint4 r;
+        r.x = *reinterpret_cast<uint32_t*>(&h0); r.y = *reinterpret_cast<uint32_t*>(&h1);
+        r.z = *reinterpret_cast<uint32_t*>(&h2); r.w = *reinterpret_cast<uint32_t*>(&h3);
+        o4[q] = r;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ reshape + StatisticsPooling
+// ConvAutoEncoder.py:61 reinterprets the channels-first [128][L3] block as [L3][128]; pooled
+// column j therefore collects flat[r*128 + j].  grid = (chunks, B), block = 256.
+__global__ void __launch_bounds__(256)
+pool_kernel(const float* __restrict__ x, int64_t bstride, int64_t n_elems /*128*L3*/, double* __restrict__ pool) {
+  __shared__ double red[256][2];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const float* p = x + (int64_t)b * bstride;
+  double s = 0.0, q = 0.0;
+  // stride 256*gridDim.x keeps (index % 128) == tid % 128 for every element this thread reads
+  for (int64_t i = blockIdx.x * 256 + tid; i < n_elems; i += (int64_t)gridDim.x * 256) {
+    const float v = __ldg(p + i);
+    s += (double)v;
+    q += (double)v * (double)v;
+  }
+  red[tid][0] = s; red[tid][1] = q;
+  __syncthreads();
+  if (tid < 128) {
+    s = red[tid][0] + red[tid + 128][0];
+    q = red[tid][1] + red[tid + 128][1];
+    atomicAdd(pool + ((int64_t)b * 128 + tid) * 2 + 0, s);
+    atomicAdd(pool + ((int64_t)b * 128 + tid) * 2 + 1, q);
+  }
+}
+
+__device__ __forceinline__ float bn_eval(float x, const SpanonBatchNorm& bn, int c) {
+  return (x - bn.running_mean[c]) / sqrtf(bn.running_var[c] + 1e-5f) * bn.weight[c] + bn.bias[c];
+}
+
+// classify: Linear(256,128) ReLU BN | Linear(128,64) ReLU BN | Linear(64,2) | log_softmax.  grid = B, block = 128
+__global__ void __launch_bounds__(128)
+clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise, int64_t n /*L3*/,
+                SpanonConvAEWeights w, float* __restrict__ logp) {
+  __shared__ float s0[256], s1[128], s2[64], s3[2];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  {
+    const double s = pool[((int64_t)b * 128 + tid) * 2 + 0], q = pool[((int64_t)b * 128 + tid) * 2 + 1];
+    const double mean = s / (double)n;
+    double var = n > 1 ? (q - s * s / (double)n) / (double)(n - 1) : (double)NAN;
+    if (var < 0.0) var = 0.0;
+    s0[tid] = (float)mean + (noise ? noise[(int64_t)b * 128 + tid] : 0.f);
+    s0[128 + tid] = (float)sqrt(var) + 1e-5f;
+  }
+  __syncthreads();
+  {
+    float a = w.cls_b[0][tid];
+    const float* wr = w.cls_w[0] + tid * 256;
+    for (int i = 0; i < 256; ++i) a = fmaf(s0[i], __ldg(wr + i), a);
+    s1[tid] = bn_eval(fmaxf(a, 0.f), w.cls_bn[0], tid);
+  }
+  __syncthreads();
+  if (tid < 64) {
+    float a = w.cls_b[1][tid];
+    const float* wr = w.cls_w[1] + tid * 128;
+    for (int i = 0; i < 128; ++i) a = fmaf(s1[i], __ldg(wr + i), a);
+    s2[tid] = bn_eval(fmaxf(a, 0.f), w.cls_bn[1], tid);
+  }
+  __syncthreads();
+  if (tid < 2) {
+    float a = w.cls_b[2][tid];
+    const float* wr = w.cls_w[2] + tid * 64;
+    for (int i = 0; i < 64; ++i) a = fmaf(s2[i], __ldg(wr + i), a);
+    s3[tid] = a;
+  }
+  __syncthreads();
+  if (tid < 2) {
+    const float m = fmaxf(s3[0], s3[1]);
+    const float lse = m + logf(expf(s3[0] - m) + expf(s3[1] - m));
+    logp[(int64_t)b * 2 + tid] = s3[tid] - lse;
+  }
+}
+
+// ------------------------------------------------------------------ layer table
+struct LayerSpec {
+  int mode;                 // PackMode
+  int cin, cout, k;         // real sizes
+  int cin_v, cout_v;        // view widths
+  int ntaps;
+  int shift[MAX_TAPS];
+  int rows_div;             // rows = L / rows_div (view rows of the input)
+  int rows_shrink;          // rows_out = rows_in - rows_shrink (TDNN, no padding)
+};
+
+enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, N_LAYERS };
+
+// tc = this layer runs on the tcgen05 kernel (bf16 UMMA-packed weights, decoder.8 padded to N = 16)
+LayerSpec make_spec(int id, bool tc) {
+  LayerSpec s{};
+  auto taps = [&](std::initializer_list<int> sh) { s.ntaps = 0; for (int v : sh) s.shift[s.ntaps++] = v; };
+  switch (id) {
+    case L_ENC2:  s = {PACK_CONV_S2, 32, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-1, 0, 1}); break;
+    case L_ENC5:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
+    case L_ENC8:  s = {PACK_CONV_S2, 64, 128, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
+    case L_ENC11: s = {PACK_CONV_S1, 128, 128, 5, 128, 128, 0, {}, 4, 0}; taps({-2, -1, 0, 1, 2}); break;
+    case L_TD0:   s = {PACK_CONV_S1, 128, 128, 5, 128, 128, 0, {}, 4, 4}; taps({0, 1, 2, 3, 4}); break;
+    case L_TD3:   s = {PACK_CONV_S1, 128, 128, 3, 128, 128, 0, {}, 4, 4}; taps({0, 2, 4}); break;
+    case L_TD6:   s = {PACK_CONV_S1, 128, 128, 3, 128, 128, 0, {}, 4, 6}; taps({0, 3, 6}); break;
+    case L_DEC0:  s = {PACK_CONV_S1, 128, 128, 5, 128, 128, 0, {}, 4, 0}; taps({-2, -1, 0, 1, 2}); break;
+    case L_DEC1:  s = {PACK_CONVT_S2, 128, 64, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
+    case L_DEC4:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
+    case L_DEC5:  s = {PACK_CONVT_S2, 64, 32, 5, 64, 64, 0, {}, 2, 0};   taps({-1, 0, 1}); break;
+    case L_DEC8:  s = {PACK_CONV_S1, 32, 1, 15, 32, tc ? 16 : 4, 0, {}, 1, 0};
+                  taps({-7, -6, -5, -4, -3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7}); break;
+  }
+  return s;
+}
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Workspace {
+  // carved in this order from the caller's buffer (all 256-byte aligned)
+  void* packed[N_LAYERS];
+  float* bn_scale[4]; float* bn_shift[4];      // clf norm, tdnn bn 0..2
+  double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
+  float* in_scale[6]; float* in_shift[6];      // [chunk][C]
+  double* pool;                                // [chunk][128][2]
+  void* act[4];                                // activation ring, each chunk*L*32 elements
+  float* tdnn_out;                             // [chunk][128][L4-14] fp32
+  size_t total;
+};
+
+const int kInC[6] = {64, 64, 128, 128, 64, 32};
+
+int default_chunk(int64_t L, size_t esize) {
+  // keep ~3 live activation planes of a chunk inside L2 (126 MB): chunk * L*32*esize * 3 <= ~96 MB
+  const double per = (double)L * 32.0 * (double)esize;
+  int c = (int)(96.0e6 / (3.0 * per));
+  return std::max(1, std::min(c, 64));
+}
+
+void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t esize) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { void* p = base ? base + off : nullptr; off += align_up(bytes, 256); return p; };
+  for (int i = 0; i < N_LAYERS; ++i) {
+    LayerSpec s = make_spec(i, tc);
+    ws.packed[i] = take((size_t)s.ntaps * s.cin_v * std::max(s.cout_v, 16) * 4);
+  }
+  for (int i = 0; i < 4; ++i) { ws.bn_scale[i] = (float*)take(128 * 4); ws.bn_shift[i] = (float*)take(128 * 4); }
+  // stats are contiguous so one memset clears them
+  for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * kInC[i] * 2 * sizeof(double));
+  ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
+  for (int i = 0; i < 6; ++i) {
+    ws.in_scale[i] = (float*)take((size_t)chunk * kInC[i] * 4);
+    ws.in_shift[i] = (float*)take((size_t)chunk * kInC[i] * 4);
+  }
+  for (int i = 0; i < 4; ++i) ws.act[i] = take((size_t)chunk * L * 32 * esize + 1024);
+  ws.tdnn_out = (float*)take((size_t)chunk * 128 * (size_t)std::max<int64_t>(L / 4 - 14, 1) * 4);
+  ws.total = off;
+}
+
+struct Ctx {
+  const SpanonConvAEWeights* w;
+  Workspace ws;
+  bool tc;       // bf16 activations (+ tcgen05 where supported)
+  int n_sm;
+  int64_t L;
+  cudaStream_t st;
+};
+
+bool layer_on_tc(const Ctx& c, int id) { return c.tc && tapgemm_tc_available(); (void)id; }
+
+int pack_layer(const Ctx& c, int id, const float* w) {
+  const bool on_tc = layer_on_tc(c, id);
+  LayerSpec s = make_spec(id, on_tc);
+  const int64_t n = (int64_t)s.ntaps * s.cin_v * s.cout_v;
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n, 256), 1024);
+  if (on_tc)
+    pack_umma_kernel<<<grid, 256, 0, c.st>>>(w, (__nv_bfloat16*)c.ws.packed[id], s.mode, s.cin, s.cout, s.k, s.ntaps,
+                                             s.cin_v, s.cout_v);
+  else
+    pack_f32_kernel<<<grid, 256, 0, c.st>>>(w, (float*)c.ws.packed[id], s.mode, s.cin, s.cout, s.k, s.ntaps, s.cin_v,
+                                            s.cout_v);
+  return check_launch("pack_kernel");
+}
+
+struct LayerIO {
+  const void* in; void* out;
+  int in_norm;        // index into stats/in_scale of the InstanceNorm applied on load (+SiLU), -1 none
+  int t2_bn;          // bn_scale index applied after the activation on load, -1 none
+  const float* bias;
+  int relu;
+  int e_bn;           // bn index folded into the epilogue, -1 none
+  int out_stats;      // stats index accumulated in the epilogue, -1 none
+  int out_mode;
+};
+
+int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
+  const bool on_tc = layer_on_tc(c, id);
+  LayerSpec s = make_spec(id, on_tc);
+  TapGemmParams p{};
+  p.in = io.in; p.out = io.out;
+  p.rows_in = (int)(c.L / s.rows_div);
+  if (id == L_TD3) p.rows_in -= 4;
+  if (id == L_TD6) p.rows_in -= 8;
+  p.rows_out = p.rows_in - s.rows_shrink;
+  p.cin_v = s.cin_v; p.cout_v = s.cout_v;
+  p.cin_mod = s.cin; p.cout_mod = s.cout;
+  p.in_bstride = (int64_t)p.rows_in * s.cin_v;
+  p.out_bstride = io.out_mode == OUT_CH0_F32 ? (int64_t)p.rows_out : (int64_t)p.rows_out * s.cout_v;
+  p.ntaps = s.ntaps;
+  for (int t = 0; t < s.ntaps; ++t) p.shift[t] = s.shift[t];
+  p.w = c.ws.packed[id];
+  if (io.in_norm >= 0) { p.t1_scale = c.ws.in_scale[io.in_norm]; p.t1_shift = c.ws.in_shift[io.in_norm]; p.silu = 1; }
+  if (io.t2_bn >= 0) { p.t2_scale = c.ws.bn_scale[io.t2_bn]; p.t2_shift = c.ws.bn_shift[io.t2_bn]; }
+  p.bias = io.bias;
+  p.relu = io.relu;
+  if (io.e_bn >= 0) { p.e_scale = c.ws.bn_scale[io.e_bn]; p.e_shift = c.ws.bn_shift[io.e_bn]; }
+  p.stats = io.out_stats >= 0 ? c.ws.stats[io.out_stats] : nullptr;
+  p.out_mode = io.out_mode;
+  p.B = nb;
+  if (on_tc) return launch_tapgemm_tc(p, c.n_sm, c.st);
+  if (c.tc) return launch_tapgemm_simt<__nv_bfloat16>(p, c.st);
+  return launch_tapgemm_simt<float>(p, c.st);
+}
+
+int finalize_in(const Ctx& c, int idx, const float* gamma, const float* beta, int nb, double count) {
+  const int C = kInC[idx];
+  instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * C, 128), 128, 0, c.st>>>(
+      c.ws.stats[idx], gamma, beta, nb, C, count, c.ws.in_scale[idx], c.ws.in_shift[idx]);
+  return check_launch("instnorm_finalize_kernel");
+}
+
+}  // namespace
+}  // namespace spanon
+
+using namespace spanon;
+
+static int resolve_opts(const SpanonConvAEOpts* o, int64_t L, bool* tc, int* chunk) {
+  const int prec = o ? o->precision : SPANON_PREC_BF16;
+  if (prec != SPANON_PREC_FP32 && prec != SPANON_PREC_BF16) return SPANON_ERR_UNSUPPORTED;
+  *tc = prec == SPANON_PREC_BF16;
+  int ch = o ? o->chunk_utts : 0;
+  if (ch <= 0) ch = default_chunk(L, *tc ? 2 : 4);
+  *chunk = ch;
+  return SPANON_OK;
+}
+
+extern "C" size_t spanon_convae_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts) {
+  if (B <= 0 || T <= 0 || F <= 0) return 0;
+  bool tc; int chunk;
+  if (resolve_opts(opts, T * F, &tc, &chunk) != SPANON_OK) return 0;
+  chunk = (int)std::min<int64_t>(chunk, B);
+  Workspace ws;
+  carve(ws, nullptr, chunk, T * F, tc, tc ? 2 : 4);
+  return ws.total + 256;
+}
+
+extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* w, const float* pool_noise,
+                                 const float* norm_mean, const float* norm_std, const int32_t* utt_max, float top_db,
+                                 int64_t T_valid, float* recon, float* logp, void* workspace, size_t workspace_bytes,
+                                 int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts, void* stream) {
+  if (!w) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || T <= 0 || F <= 0) return SPANON_ERR_BAD_SHAPE;
+  const int64_t L = T * F;
+  // the reference fails in its final reshape unless two stride-2 stages divide L (ConvAutoEncoder.py:197-198)
+  if (L % 4 != 0 || L > (int64_t)1 << 30) return SPANON_ERR_BAD_SHAPE;
+  if (B == 0) return SPANON_OK;
+  if (!feats || !recon || !workspace) return SPANON_ERR_NULL_POINTER;
+  if ((norm_mean == nullptr) != (norm_std == nullptr)) return SPANON_ERR_NULL_POINTER;
+  const bool fused_norm = norm_mean != nullptr;
+  if (!fused_norm) T_valid = T;
+  if (T_valid < 0 || T_valid > T) return SPANON_ERR_BAD_SHAPE;
+  const bool run_clf = logp != nullptr && !(opts && opts->skip_classifier);
+  if (run_clf && L / 4 < 16) return SPANON_ERR_BAD_SHAPE;  // TDNN (k5, k3 d2, k3 d3) needs >= 15 rows
+  Ctx c{};
+  int chunk;
+  SPANON_TRY(resolve_opts(opts, L, &c.tc, &chunk));
+  chunk = (int)std::min<int64_t>(chunk, B);
+  if (workspace_bytes < spanon_convae_workspace_bytes(B, T, F, opts)) return SPANON_ERR_WORKSPACE;
+  char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
+  const size_t esize = c.tc ? 2 : 4;
+  carve(c.ws, base, chunk, L, c.tc, esize);
+  c.w = w; c.L = L; c.st = as_stream(stream);
+  {
+    int dev = 0;
+    SPANON_CUDA_TRY(cudaGetDevice(&dev));
+    SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
+  }
+  // ---- per-call weight preparation (weights may have changed since the last call) ----
+  SPANON_TRY(pack_layer(c, L_ENC2, w->enc_w[1]));
+  SPANON_TRY(pack_layer(c, L_ENC5, w->enc_w[2]));
+  SPANON_TRY(pack_layer(c, L_ENC8, w->enc_w[3]));
+  SPANON_TRY(pack_layer(c, L_ENC11, w->enc_w[4]));
+  SPANON_TRY(pack_layer(c, L_DEC0, w->dec_w[0]));
+  SPANON_TRY(pack_layer(c, L_DEC1, w->dec_w[1]));
+  SPANON_TRY(pack_layer(c, L_DEC4, w->dec_w[2]));
+  SPANON_TRY(pack_layer(c, L_DEC5, w->dec_w[3]));
+  SPANON_TRY(pack_layer(c, L_DEC8, w->dec_w[4]));
+  if (run_clf) {
+    SPANON_TRY(pack_layer(c, L_TD0, w->tdnn_w[0]));
+    SPANON_TRY(pack_layer(c, L_TD3, w->tdnn_w[1]));
+    SPANON_TRY(pack_layer(c, L_TD6, w->tdnn_w[2]));
+    bn_fold_kernel<<<1, 128, 0, c.st>>>(w->clf_norm, 128, c.ws.bn_scale[0], c.ws.bn_shift[0]);
+    SPANON_TRY(check_launch("bn_fold_kernel"));
+    for (int i = 0; i < 3; ++i) {
+      bn_fold_kernel<<<1, 128, 0, c.st>>>(w->tdnn_bn[i], 128, c.ws.bn_scale[1 + i], c.ws.bn_shift[1 + i]);
+      SPANON_TRY(check_launch("bn_fold_kernel"));
+    }
+  }
+  const int64_t L2 = L / 2, L4 = L / 4;
+  const size_t stats_bytes = reinterpret_cast<char*>(c.ws.pool) + align_up((size_t)chunk * 128 * 2 * sizeof(double), 256) -
+                             reinterpret_cast<char*>(c.ws.stats[0]);
+  for (int64_t b0 = 0; b0 < B; b0 += chunk) {
+    const int nb = (int)std::min<int64_t>(chunk, B - b0);
+    SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.stats[0], 0, stats_bytes, c.st));
+    void** X = c.ws.act;
+    // encoder.0 + GLU
+    {
+      const int64_t fstride = fused_norm ? T_valid * F : L;
+      const float* src = feats + b0 * fstride;
+      dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
+      const int32_t* um = utt_max ? utt_max + b0 : nullptr;
+      if (c.tc)
+        first_layer_kernel<__nv_bfloat16, true><<<grid, FL_NT, 0, c.st>>>(
+            src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um, top_db, w->enc_w[0], w->enc_b[0],
+            (__nv_bfloat16*)X[0], L * 32);
+      else
+        first_layer_kernel<float, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
+                                                                   norm_mean, norm_std, um, top_db, w->enc_w[0],
+                                                                   w->enc_b[0], (float*)X[0], L * 32);
+      SPANON_TRY(check_launch("first_layer_kernel"));
+    }
+    //                         in    out   in_norm t2  bias          relu e_bn stats out_mode
+    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, w->enc_b[1], 0, -1, 0, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, w->enc_b[3], 0, -1, 2, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 2, w->enc_in_w[2], w->enc_in_b[2], nb, (double)L4));
+    SPANON_TRY(run_layer(c, L_ENC11, {X[3], X[0], 2, -1, w->enc_b[4], 0, -1, 3, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 3, w->enc_in_w[3], w->enc_in_b[3], nb, (double)L4));
+    // X[0] = raw encoder.11 output; the bottleneck is SiLU(IN(X[0])), applied by both consumers on load
+    if (run_clf) {
+      SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
+      SPANON_TRY(run_layer(c, L_TD3, {X[1], X[2], -1, -1, w->tdnn_b[1], 1, 2, -1, OUT_CHANNELS_LAST}, nb));
+      SPANON_TRY(run_layer(c, L_TD6, {X[2], c.ws.tdnn_out, -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_FIRST_F32}, nb));
+      const int64_t L3 = L4 - 14;
+      const int64_t n_el = 128 * L3;
+      dim3 pg((unsigned)std::min<int64_t>(ceil_div(n_el, 256 * 16), 256), (unsigned)nb);
+      pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
+      SPANON_TRY(check_launch("pool_kernel"));
+      clf_head_kernel<<<(unsigned)nb, 128, 0, c.st>>>(c.ws.pool, pool_noise ? pool_noise + b0 * 128 : nullptr, L3, *w,
+                                                      logp + b0 * 2);
+      SPANON_TRY(check_launch("clf_head_kernel"));
+    }
+    SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST}, nb));
+    SPANON_TRY(finalize_in(c, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
+    SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
+  }
+  return SPANON_OK;
+}

@@ -1,0 +1,350 @@
+// Fused Fbank for B200: PCM -> frames (smem) -> Hamming window -> 400-point FFT ->
+// power -> sparse triangular mel projection -> dB, plus the per-utterance maximum the
+// top_db clamp needs.  The spectrum never leaves shared memory.
+//
+// Reference behaviour reproduced (speechbrain/speechbrain/processing/features.py):
+//   STFT.forward :161-172      torch.stft(center=True, pad_mode="constant", onesided)
+//   spectral_magnitude :347    re^2 + im^2 (power = 1)
+//   Filterbank.forward :548    spectrogram @ fbank_matrix
+//   _amplitude_to_DB :701-710  10*log10(clamp(x, amin)) - offset, max(., amax - top_db)
+//
+// Kernel design (fbank400_kernel): one CTA = 16 consecutive frames of one utterance.
+//   * the 2800 PCM samples the 16 frames cover are loaded once with 128-bit coalesced
+//     loads (each sample is used by 2.5 frames);
+//   * two real frames are packed into one complex 400-point FFT (frame t -> real part,
+//     frame t+1 -> imaginary part) and separated afterwards, so the CTA runs 8 complex
+//     FFTs; the FFT is a Stockham autosort radix 4,4,5,5 in shared memory with a
+//     twiddle table evaluated in fp64 on first use;
+//   * power, mel (only the <= 13 non-zero taps of each filter) and log run from shared
+//     memory; the only HBM traffic is 4 B/sample in and 4 B/mel-bin out.
+#include "common.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace spanon {
+
+namespace {
+
+constexpr int N_FFT = 400;
+constexpr int HOP = 160;
+constexpr int FRAMES_PER_CTA = 16;
+constexpr int PAIRS = FRAMES_PER_CTA / 2;
+constexpr int SEG = (FRAMES_PER_CTA - 1) * HOP + N_FFT;  // 2800 samples
+constexpr int NT = 256;
+constexpr int N_BINS = N_FFT / 2 + 1;  // 201
+constexpr int P_STRIDE = 204;          // padded row of the power buffer
+
+struct FbankSmem {
+  float2 bufA[PAIRS * N_FFT];
+  float2 bufB[PAIRS * N_FFT];
+  float2 tw[N_FFT];
+  float win[N_FFT];
+  float seg[SEG];
+  float red[NT / 32];
+};
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+
+__device__ __forceinline__ void dft4(float2* v) {
+  float2 t0 = make_float2(v[0].x + v[2].x, v[0].y + v[2].y);
+  float2 t1 = make_float2(v[0].x - v[2].x, v[0].y - v[2].y);
+  float2 t2 = make_float2(v[1].x + v[3].x, v[1].y + v[3].y);
+  // (v1 - v3) * (-i) = (im, -re)
+  float2 t3 = make_float2(v[1].y - v[3].y, -(v[1].x - v[3].x));
+  v[0] = make_float2(t0.x + t2.x, t0.y + t2.y);
+  v[1] = make_float2(t1.x + t3.x, t1.y + t3.y);
+  v[2] = make_float2(t0.x - t2.x, t0.y - t2.y);
+  v[3] = make_float2(t1.x - t3.x, t1.y - t3.y);
+}
+
+__device__ __forceinline__ void dft5(float2* v) {
+  const float c1 = 0.30901699437494742f;   // cos(2pi/5)
+  const float c2 = -0.80901699437494742f;  // cos(4pi/5)
+  const float s1 = 0.95105651629515357f;   // sin(2pi/5)
+  const float s2 = 0.58778525229247313f;   // sin(4pi/5)
+  float2 a1 = make_float2(v[1].x + v[4].x, v[1].y + v[4].y);
+  float2 a2 = make_float2(v[2].x + v[3].x, v[2].y + v[3].y);
+  float2 b1 = make_float2(v[1].x - v[4].x, v[1].y - v[4].y);
+  float2 b2 = make_float2(v[2].x - v[3].x, v[2].y - v[3].y);
+  float2 m1 = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
+  float2 m2 = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
+  float2 n1 = make_float2(s1 * b1.x + s2 * b2.x, s1 * b1.y + s2 * b2.y);
+  float2 n2 = make_float2(s2 * b1.x - s1 * b2.x, s2 * b1.y - s1 * b2.y);
+  v[0] = make_float2(v[0].x + a1.x + a2.x, v[0].y + a1.y + a2.y);
+  // y1 = m1 - i n1 ; y4 = m1 + i n1 ; y2 = m2 - i n2 ; y3 = m2 + i n2 ;  -i n = (n.y, -n.x)
+  v[1] = make_float2(m1.x + n1.y, m1.y - n1.x);
+  v[4] = make_float2(m1.x - n1.y, m1.y + n1.x);
+  v[2] = make_float2(m2.x + n2.y, m2.y - n2.x);
+  v[3] = make_float2(m2.x - n2.y, m2.y + n2.x);
+}
+
+// One Stockham stage of radix R with Ns = product of the previous radices, over PAIRS
+// independent 400-point transforms.
+template <int R, int NS>
+__device__ __forceinline__ void stockham_stage(const float2* __restrict__ in, float2* __restrict__ out,
+                                               const float2* __restrict__ tw, int tid) {
+  constexpr int NB = N_FFT / R;               // butterflies per transform
+  constexpr int TWS = N_FFT / (NS * R);       // twiddle index stride
+  for (int w = tid; w < PAIRS * NB; w += NT) {
+    const int f = w / NB;
+    const int j = w - f * NB;
+    const int k = j % NS;
+    const float2* src = in + f * N_FFT;
+    float2 v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      v[r] = src[j + r * NB];
+      if (NS > 1 && r > 0) v[r] = cmul(v[r], tw[(r * k * TWS) % N_FFT]);
+    }
+    if (R == 4) dft4(v); else dft5(v);
+    float2* dst = out + f * N_FFT + (j - k) * R + k;
+#pragma unroll
+    for (int r = 0; r < R; ++r) dst[r * NS] = v[r];
+  }
+}
+
+__global__ void __launch_bounds__(NT)
+fbank400_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
+                float* __restrict__ out, int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FbankSmem& S = *reinterpret_cast<FbankSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * FRAMES_PER_CTA;
+  const float* x = pcm + (int64_t)b * pcm_stride;
+
+  // twiddles (fp64 evaluation, once per CTA: 400 sincos) and the window
+  for (int i = tid; i < N_FFT; i += NT) {
+    double s, c;
+    sincospi(-2.0 * (double)i / (double)N_FFT, &s, &c);
+    S.tw[i] = make_float2((float)c, (float)s);
+    S.win[i] = cfg.window[i];
+  }
+  // PCM segment: padded sample p = t*HOP + n - N_FFT/2  (center=True, zero padding)
+  const int64_t base = (int64_t)t0 * HOP - N_FFT / 2;
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && ((base & 3) == 0);
+  for (int i4 = tid; i4 < SEG / 4; i4 += NT) {
+    const int64_t s = base + 4 * (int64_t)i4;
+    float4 v;
+    if (vec_ok && s >= 0 && s + 3 < n_samples) {
+      v = __ldg(reinterpret_cast<const float4*>(x + s));
+    } else {
+      v.x = (s + 0 >= 0 && s + 0 < n_samples) ? __ldg(x + s + 0) : 0.f;
+      v.y = (s + 1 >= 0 && s + 1 < n_samples) ? __ldg(x + s + 1) : 0.f;
+      v.z = (s + 2 >= 0 && s + 2 < n_samples) ? __ldg(x + s + 2) : 0.f;
+      v.w = (s + 3 >= 0 && s + 3 < n_samples) ? __ldg(x + s + 3) : 0.f;
+    }
+    *reinterpret_cast<float4*>(&S.seg[4 * i4]) = v;
+  }
+  __syncthreads();
+
+  // stage 1: radix 4, Ns = 1, reads the windowed frames straight from the PCM segment
+  {
+    constexpr int NB = N_FFT / 4;
+    for (int w = tid; w < PAIRS * NB; w += NT) {
+      const int f = w / NB;
+      const int j = w - f * NB;
+      const float* fa = S.seg + (2 * f) * HOP;
+      const float* fb = fa + HOP;
+      float2 v[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int n = j + r * NB;
+        const float wn = S.win[n];
+        v[r] = make_float2(wn * fa[n], wn * fb[n]);
+      }
+      dft4(v);
+      float2* dst = S.bufA + f * N_FFT + j * 4;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) dst[r] = v[r];
+    }
+  }
+  __syncthreads();
+  stockham_stage<4, 4>(S.bufA, S.bufB, S.tw, tid);
+  __syncthreads();
+  stockham_stage<5, 16>(S.bufB, S.bufA, S.tw, tid);
+  __syncthreads();
+  stockham_stage<5, 80>(S.bufA, S.bufB, S.tw, tid);
+  __syncthreads();
+
+  // separate the two real transforms and take |.|^2 ; P aliases bufA
+  float* P = reinterpret_cast<float*>(S.bufA);
+  for (int w = tid; w < PAIRS * N_BINS; w += NT) {
+    const int f = w / N_BINS;
+    const int k = w - f * N_BINS;
+    const float2 zk = S.bufB[f * N_FFT + k];
+    const float2 zn = S.bufB[f * N_FFT + ((N_FFT - k) % N_FFT)];
+    const float ar = zk.x + zn.x, ai = zk.y - zn.y;   // 2*X_a
+    const float br = zk.y + zn.y, bi = zk.x - zn.x;   // 2*X_b (up to a unit factor)
+    P[(2 * f) * P_STRIDE + k] = 0.25f * (ar * ar + ai * ai);
+    P[(2 * f + 1) * P_STRIDE + k] = 0.25f * (br * br + bi * bi);
+  }
+  __syncthreads();
+
+  // mel projection + dB + running max
+  const int n_mels = cfg.n_mels;
+  float lmax = -INFINITY;
+  for (int w = tid; w < FRAMES_PER_CTA * n_mels; w += NT) {
+    const int fr = w / n_mels;
+    const int m = w - fr * n_mels;
+    const int t = t0 + fr;
+    if (t >= T) continue;
+    const int st = __ldg(cfg.mel_start + m);
+    const int ln = __ldg(cfg.mel_len + m);
+    const float* wv = cfg.mel_w + __ldg(cfg.mel_off + m);
+    const float* p = P + fr * P_STRIDE + st;
+    float acc = 0.f;
+    for (int i = 0; i < ln; ++i) acc = fmaf(p[i], __ldg(wv + i), acc);
+    // fp64 log10: exactly -100 dB for silence (reference test_features.py:66-77)
+    const float db = (float)((double)cfg.multiplier * log10((double)fmaxf(acc, cfg.amin))) - cfg.db_offset;
+    out[((int64_t)b * T + t) * n_mels + m] = db;
+    lmax = fmaxf(lmax, db);
+  }
+  lmax = warp_max(lmax);
+  if ((tid & 31) == 0) S.red[tid >> 5] = lmax;
+  __syncthreads();
+  if (tid == 0) {
+    float m = S.red[0];
+#pragma unroll
+    for (int i = 1; i < NT / 32; ++i) m = fmaxf(m, S.red[i]);
+    if (m > -INFINITY) atomicMax(utt_max + b, float_to_key(m));
+  }
+}
+
+// Generic (any n_fft <= 4096, win_length <= n_fft) direct-DFT path: one CTA per frame.
+// O(n_fft^2) per frame -- correctness path for non-reference configurations only.
+__global__ void __launch_bounds__(256)
+fbank_generic_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
+                     float* __restrict__ out, int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int n_fft = cfg.n_fft;
+  const int n_bins = n_fft / 2 + 1;
+  float2* tw = reinterpret_cast<float2*>(smem_raw);      // [n_fft]
+  float* fr = reinterpret_cast<float*>(tw + n_fft);      // [n_fft] windowed frame
+  float* P = fr + n_fft;                                 // [n_bins]
+  __shared__ float red[8];
+  const int tid = threadIdx.x;
+  const int t = blockIdx.x, b = blockIdx.y;
+  const float* x = pcm + (int64_t)b * pcm_stride;
+  const int wl = cfg.win_length;
+  const int woff = (n_fft - wl) / 2;  // torch.stft centres a short window inside n_fft
+  for (int i = tid; i < n_fft; i += blockDim.x) {
+    double s, c;
+    sincospi(-2.0 * (double)i / (double)n_fft, &s, &c);
+    tw[i] = make_float2((float)c, (float)s);
+    const int64_t p = (int64_t)t * cfg.hop_length + i - n_fft / 2;
+    const float v = (p >= 0 && p < n_samples) ? __ldg(x + p) : 0.f;
+    const float w = (i >= woff && i < woff + wl) ? cfg.window[i - woff] : 0.f;
+    fr[i] = v * w;
+  }
+  __syncthreads();
+  for (int k = tid; k < n_bins; k += blockDim.x) {
+    float re = 0.f, im = 0.f;
+    int idx = 0;
+    for (int n = 0; n < n_fft; ++n) {
+      const float2 w = tw[idx];
+      re = fmaf(fr[n], w.x, re);
+      im = fmaf(fr[n], w.y, im);
+      idx += k; if (idx >= n_fft) idx -= n_fft;
+    }
+    P[k] = re * re + im * im;
+  }
+  __syncthreads();
+  float lmax = -INFINITY;
+  for (int m = tid; m < cfg.n_mels; m += blockDim.x) {
+    const int st = cfg.mel_start[m], ln = cfg.mel_len[m];
+    const float* wv = cfg.mel_w + cfg.mel_off[m];
+    float acc = 0.f;
+    for (int i = 0; i < ln; ++i) acc = fmaf(P[st + i], wv[i], acc);
+    const float db = (float)((double)cfg.multiplier * log10((double)fmaxf(acc, cfg.amin))) - cfg.db_offset;
+    out[((int64_t)b * T + t) * cfg.n_mels + m] = db;
+    lmax = fmaxf(lmax, db);
+  }
+  lmax = warp_max(lmax);
+  if ((tid & 31) == 0) red[tid >> 5] = lmax;
+  __syncthreads();
+  if (tid == 0) {
+    float m = red[0];
+    for (int i = 1; i < (int)(blockDim.x >> 5); ++i) m = fmaxf(m, red[i]);
+    if (m > -INFINITY) atomicMax(utt_max + b, float_to_key(m));
+  }
+}
+
+__global__ void fill_i32_kernel(int32_t* p, int64_t n, int32_t v) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+__global__ void fbank_clamp_kernel(float* __restrict__ x, const int32_t* __restrict__ utt_max,
+                                   int64_t per_utt, float top_db) {
+  const int b = blockIdx.y;
+  const float floor_db = key_to_float(utt_max[b]) - top_db;
+  float* p = x + (int64_t)b * per_utt;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < per_utt;
+       i += (int64_t)gridDim.x * blockDim.x)
+    p[i] = fmaxf(p[i], floor_db);
+}
+
+}  // namespace
+
+int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st) {
+  if (n <= 0) return SPANON_OK;
+  fill_i32_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(p, n, v);
+  return check_launch("fill_i32");
+}
+
+}  // namespace spanon
+
+using namespace spanon;
+
+extern "C" int64_t spanon_num_frames(int64_t n_samples, int32_t hop_length) {
+  if (hop_length <= 0 || n_samples < 0) return -1;
+  return 1 + n_samples / hop_length;
+}
+
+extern "C" int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
+                                float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream) {
+  if (!cfg) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || n_samples < 0 || pcm_stride < n_samples) return SPANON_ERR_BAD_SHAPE;
+  if (cfg->n_fft <= 0 || cfg->hop_length <= 0 || cfg->win_length <= 0 || cfg->win_length > cfg->n_fft ||
+      cfg->n_mels <= 0)
+    return SPANON_ERR_BAD_SHAPE;
+  if (B == 0) return SPANON_OK;
+  if (!pcm || !out || !utt_max || !cfg->window || !cfg->mel_start || !cfg->mel_len || !cfg->mel_off ||
+      !cfg->mel_w)
+    return SPANON_ERR_NULL_POINTER;
+  if (B > 65535) return SPANON_ERR_BAD_SHAPE;
+  cudaStream_t st = as_stream(stream);
+  const int64_t T = 1 + n_samples / cfg->hop_length;
+  SPANON_TRY(fill_i32(utt_max, B, INT32_MIN, st));
+  if (cfg->n_fft == N_FFT && cfg->win_length == N_FFT && cfg->hop_length == HOP) {
+    static bool attr_done = false;
+    if (!attr_done) {
+      SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(FbankSmem)));
+      attr_done = true;
+    }
+    dim3 grid((unsigned)ceil_div(T, FRAMES_PER_CTA), (unsigned)B);
+    fbank400_kernel<<<grid, NT, sizeof(FbankSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+    return check_launch("fbank400_kernel");
+  }
+  if (cfg->n_fft > 4096) return SPANON_ERR_UNSUPPORTED;
+  const size_t smem = (size_t)cfg->n_fft * (sizeof(float2) + sizeof(float)) + (cfg->n_fft / 2 + 1) * sizeof(float);
+  dim3 grid((unsigned)T, (unsigned)B);
+  fbank_generic_kernel<<<grid, 256, smem, st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+  return check_launch("fbank_generic_kernel");
+}
+
+extern "C" int spanon_fbank_clamp(float* feats, const int32_t* utt_max, int64_t B, int64_t T, int64_t n_mels,
+                                  float top_db, void* stream) {
+  if (B < 0 || T < 0 || n_mels <= 0) return SPANON_ERR_BAD_SHAPE;
+  if (B == 0 || T == 0) return SPANON_OK;
+  if (!feats || !utt_max) return SPANON_ERR_NULL_POINTER;
+  if (B > 65535) return SPANON_ERR_BAD_SHAPE;
+  const int64_t per = T * n_mels;
+  dim3 grid((unsigned)std::min<int64_t>(ceil_div(per, 256 * 4), 1024), (unsigned)B);
+  fbank_clamp_kernel<<<grid, 256, 0, as_stream(stream)>>>(feats, utt_max, per, top_db);
+  return check_launch("fbank_clamp_kernel");
+}

@@ -1,0 +1,284 @@
+// FullyConnectedAutoencoder forward, fused into one persistent kernel + a tiny head kernel.
+//
+// Reference: models/FullyConnected.py
+//   FullyConnectedAutoencoder.forward :147-159  encoder 80-60-40-20 (ReLU), decoder 20-40-60-80
+//   FullyConnSexClassifier.forward    :90-104   reshape-BN(20)-reshape, 20-40-40 (ReLU),
+//                                               StatisticsPooling over T, MLP 80-40-40-20-2, log_softmax
+//   StatisticsPooling                 speechbrain/speechbrain/nnet/pooling.py:263-312
+//
+// Kernel design: one thread = one frame; the six autoencoder layers and the two per-frame
+// classifier layers run back to back with activations in shared memory ([dim][frame],
+// conflict free) and all 18.4 k weights resident in shared memory (transposed so that one
+// broadcast 128-bit load feeds four FMAs).  HBM traffic is the algorithmic minimum: 320 B in
+// and 320 B out per frame; the pooled classifier statistics leave the kernel as fp64 atomics.
+// BatchNorm layers use running statistics (eval mode).
+#include "common.cuh"
+#include <algorithm>
+#include <math.h>
+
+namespace spanon {
+namespace {
+
+constexpr int NTHR = 256;
+constexpr int LDA = NTHR + 1;  // activation row stride (floats): conflict-free transposed access
+constexpr int D_IN = 80;
+
+struct FcLayer { int in, out, w_off, b_off; };
+// smem weight offsets (floats), layers in execution order
+constexpr int W_E0 = 0;                    // 80x60
+constexpr int W_E1 = W_E0 + 80 * 60;       // 60x40
+constexpr int W_E2 = W_E1 + 60 * 40;       // 40x20
+constexpr int W_C0 = W_E2 + 40 * 20;       // 20x40 (classifier initial.0)
+constexpr int W_C1 = W_C0 + 20 * 40;       // 40x40 (classifier initial.2)
+constexpr int W_D0 = W_C1 + 40 * 40;       // 20x40
+constexpr int W_D1 = W_D0 + 20 * 40;       // 40x60
+constexpr int W_D2 = W_D1 + 40 * 60;       // 60x80
+constexpr int W_END = W_D2 + 60 * 80;      // 18400
+constexpr int B_E0 = 0, B_E1 = 60, B_E2 = 100, B_C0 = 120, B_C1 = 160, B_D0 = 200, B_D1 = 240, B_D2 = 300,
+              B_END = 380;
+
+struct FcSmem {
+  float X[80 * LDA];
+  float Y[60 * LDA];
+  float W[W_END];
+  float Bv[B_END];
+  float bn_s[20], bn_t[20];
+  float nmean[D_IN], nstd[D_IN];
+};
+
+__device__ __forceinline__ void load_wt(float* dst, const float* __restrict__ w, int out, int in, int tid) {
+  // PyTorch Linear weight [out][in] -> smem [in][out]
+  for (int e = tid; e < out * in; e += NTHR) {
+    const int o = e / in, i = e - o * in;
+    dst[i * out + o] = __ldg(w + e);
+  }
+}
+
+template <int IN, int OUT, bool RELU>
+__device__ __forceinline__ void dense(const float* __restrict__ xin, float* __restrict__ xout,
+                                      const float* __restrict__ Wt, const float* __restrict__ bias, int tid) {
+  constexpr int JB = 20;
+  static_assert(OUT % JB == 0, "OUT must be a multiple of 20");
+#pragma unroll 1
+  for (int j0 = 0; j0 < OUT; j0 += JB) {
+    float acc[JB];
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) acc[jj] = bias[j0 + jj];
+#pragma unroll 4
+    for (int i = 0; i < IN; ++i) {
+      const float x = xin[i * LDA + tid];
+      const float4* w4 = reinterpret_cast<const float4*>(Wt + i * OUT + j0);
+#pragma unroll
+      for (int q = 0; q < JB / 4; ++q) {
+        const float4 w = w4[q];
+        acc[4 * q + 0] = fmaf(x, w.x, acc[4 * q + 0]);
+        acc[4 * q + 1] = fmaf(x, w.y, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(x, w.z, acc[4 * q + 2]);
+        acc[4 * q + 3] = fmaf(x, w.w, acc[4 * q + 3]);
+      }
+    }
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) xout[(j0 + jj) * LDA + tid] = RELU ? fmaxf(acc[jj], 0.f) : acc[jj];
+  }
+}
+
+__global__ void __launch_bounds__(NTHR, 1)
+fcae_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* __restrict__ norm_mean,
+            const float* __restrict__ norm_std, const int32_t* __restrict__ utt_max, float top_db,
+            float* __restrict__ recon, double* __restrict__ pool /*[B][40][2]*/, int64_t n_frames, int T,
+            int run_clf) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FcSmem& S = *reinterpret_cast<FcSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  load_wt(S.W + W_E0, w.enc_w[0], 60, 80, tid);
+  load_wt(S.W + W_E1, w.enc_w[1], 40, 60, tid);
+  load_wt(S.W + W_E2, w.enc_w[2], 20, 40, tid);
+  load_wt(S.W + W_C0, w.init_w[0], 40, 20, tid);
+  load_wt(S.W + W_C1, w.init_w[1], 40, 40, tid);
+  load_wt(S.W + W_D0, w.dec_w[0], 40, 20, tid);
+  load_wt(S.W + W_D1, w.dec_w[1], 60, 40, tid);
+  load_wt(S.W + W_D2, w.dec_w[2], 80, 60, tid);
+  for (int i = tid; i < 60; i += NTHR) S.Bv[B_E0 + i] = w.enc_b[0][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_E1 + i] = w.enc_b[1][i];
+  for (int i = tid; i < 20; i += NTHR) S.Bv[B_E2 + i] = w.enc_b[2][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_C0 + i] = w.init_b[0][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_C1 + i] = w.init_b[1][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_D0 + i] = w.dec_b[0][i];
+  for (int i = tid; i < 60; i += NTHR) S.Bv[B_D1 + i] = w.dec_b[1][i];
+  for (int i = tid; i < 80; i += NTHR) S.Bv[B_D2 + i] = w.dec_b[2][i];
+  if (tid < 20) {
+    const float s = w.clf_norm.weight[tid] / sqrtf(w.clf_norm.running_var[tid] + 1e-5f);
+    S.bn_s[tid] = s;
+    S.bn_t[tid] = w.clf_norm.bias[tid] - w.clf_norm.running_mean[tid] * s;
+  }
+  if (tid < D_IN) {
+    S.nmean[tid] = norm_mean ? norm_mean[tid] : 0.f;
+    S.nstd[tid] = norm_std ? norm_std[tid] : 1.f;
+  }
+  __syncthreads();
+
+  const int64_t n_tiles = (n_frames + NTHR - 1) / NTHR;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t f0 = tile * NTHR;
+    const int nf = (int)min((int64_t)NTHR, n_frames - f0);
+    // coalesced load of nf*80 contiguous floats, transposed into X[d][frame]
+    const float* src = feats + f0 * D_IN;
+    for (int e = tid; e < NTHR * D_IN; e += NTHR) {
+      const int fr = e / D_IN, d = e - fr * D_IN;
+      float v = 0.f;
+      if (fr < nf) {
+        v = __ldg(src + e);
+        if (norm_mean) {
+          const int b = (int)((f0 + fr) / T);
+          const float floor_db = utt_max ? key_to_float(utt_max[b]) - top_db : -INFINITY;
+          v = (fmaxf(v, floor_db) - S.nmean[d]) / S.nstd[d];
+        }
+      }
+      S.X[d * LDA + fr] = v;
+    }
+    __syncthreads();
+    dense<80, 60, true>(S.X, S.Y, S.W + W_E0, S.Bv + B_E0, tid);
+    dense<60, 40, true>(S.Y, S.X, S.W + W_E1, S.Bv + B_E1, tid);
+    dense<40, 20, false>(S.X, S.Y, S.W + W_E2, S.Bv + B_E2, tid);  // bottleneck z in Y[0..20)
+    const int64_t frame = f0 + tid;
+    const bool valid = tid < nf;
+    const int b = valid ? (int)(frame / T) : -1;
+    if (run_clf) {
+      // FullyConnected.py:93-95: BatchNorm1d(20) on the [B,20,T] REINTERPRETATION of z
+      const int t = valid ? (int)(frame - (int64_t)b * T) : 0;
+#pragma unroll
+      for (int d = 0; d < 20; ++d) {
+        const int ch = (int)(((int64_t)t * 20 + d) / T);
+        S.X[(60 + d) * LDA + tid] = fmaf(S.Y[d * LDA + tid], S.bn_s[ch], S.bn_t[ch]);
+      }
+      dense<20, 40, true>(S.X + 60 * LDA, S.X, S.W + W_C0, S.Bv + B_C0, tid);
+      dense<40, 40, true>(S.X, S.X + 40 * LDA, S.W + W_C1, S.Bv + B_C1, tid);
+      // StatisticsPooling sums over frames: warp reduce when the whole warp is in one utterance
+      const int b0 = __shfl_sync(0xffffffffu, b, 0);
+      const bool uniform = __all_sync(0xffffffffu, b == b0) && b0 >= 0;
+#pragma unroll 1
+      for (int c = 0; c < 40; ++c) {
+        const float h = valid ? S.X[(40 + c) * LDA + tid] : 0.f;
+        if (uniform) {
+          const float s = warp_sum(h), q = warp_sum(h * h);
+          if ((tid & 31) == 0) {
+            atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 0, (double)s);
+            atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 1, (double)q);
+          }
+        } else if (valid) {
+          atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 0, (double)h);
+          atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 1, (double)h * (double)h);
+        }
+      }
+    }
+    dense<20, 40, true>(S.Y, S.X, S.W + W_D0, S.Bv + B_D0, tid);
+    dense<40, 60, true>(S.X, S.Y, S.W + W_D1, S.Bv + B_D1, tid);
+    dense<60, 80, false>(S.Y, S.X, S.W + W_D2, S.Bv + B_D2, tid);
+    __syncthreads();
+    float* dst = recon + f0 * D_IN;
+    for (int e = tid; e < nf * D_IN; e += NTHR) {
+      const int fr = e / D_IN, d = e - fr * D_IN;
+      dst[e] = S.X[d * LDA + fr];
+    }
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ float bn_eval(float x, const SpanonBatchNorm& bn, int c) {
+  return (x - bn.running_mean[c]) / sqrtf(bn.running_var[c] + 1e-5f) * bn.weight[c] + bn.bias[c];
+}
+
+// grid = B, block = 64
+__global__ void fcae_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise,
+                                 SpanonFcaeWeights w, int T, float* __restrict__ logp) {
+  __shared__ float s0[80], s1[40], s2[40], s3[20], s4[2];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  if (tid < 40) {
+    const double s = pool[((int64_t)b * 40 + tid) * 2 + 0], q = pool[((int64_t)b * 40 + tid) * 2 + 1];
+    const double mean = s / (double)T;
+    double var = T > 1 ? (q - s * s / (double)T) / (double)(T - 1) : (double)NAN;
+    if (var < 0.0) var = 0.0;
+    s0[tid] = (float)mean + (noise ? noise[(int64_t)b * 40 + tid] : 0.f);  // pooling.py:295-298
+    s0[40 + tid] = (float)sqrt(var) + 1e-5f;                                  // pooling.py:299-300
+  }
+  __syncthreads();
+  if (tid < 40) {
+    float a = w.cls_b[0][tid];
+    for (int i = 0; i < 80; ++i) a = fmaf(s0[i], w.cls_w[0][tid * 80 + i], a);
+    s1[tid] = fmaxf(bn_eval(a, w.cls_bn1, tid), 0.f);
+  }
+  __syncthreads();
+  if (tid < 40) {
+    float a = w.cls_b[1][tid];
+    for (int i = 0; i < 40; ++i) a = fmaf(s1[i], w.cls_w[1][tid * 40 + i], a);
+    s2[tid] = fmaxf(a, 0.f);
+  }
+  __syncthreads();
+  if (tid < 20) {
+    float a = w.cls_b[2][tid];
+    for (int i = 0; i < 40; ++i) a = fmaf(s2[i], w.cls_w[2][tid * 40 + i], a);
+    s3[tid] = bn_eval(a, w.cls_bn6, tid);
+  }
+  __syncthreads();
+  if (tid < 2) {
+    float a = w.cls_b[3][tid];
+    for (int i = 0; i < 20; ++i) a = fmaf(s3[i], w.cls_w[3][tid * 20 + i], a);
+    s4[tid] = a;
+  }
+  __syncthreads();
+  if (tid < 2) {
+    const float m = fmaxf(s4[0], s4[1]);
+    const float lse = m + logf(expf(s4[0] - m) + expf(s4[1] - m));
+    logp[(int64_t)b * 2 + tid] = s4[tid] - lse;
+  }
+}
+
+}  // namespace
+}  // namespace spanon
+
+using namespace spanon;
+
+extern "C" size_t spanon_fcae_workspace_bytes(int64_t B, int64_t T) {
+  (void)T;
+  if (B < 0) return 0;
+  return (size_t)B * 40 * 2 * sizeof(double) + 256;
+}
+
+extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, const float* pool_noise,
+                               const float* norm_mean, const float* norm_std, const int32_t* utt_max, float top_db,
+                               float* recon, float* logp, void* workspace, size_t workspace_bytes, int64_t B,
+                               int64_t T, void* stream) {
+  if (!w) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || T < 0) return SPANON_ERR_BAD_SHAPE;
+  if (w->in_dim != D_IN) return SPANON_ERR_UNSUPPORTED;
+  if (B == 0 || T == 0) return SPANON_OK;
+  if (!feats || !recon) return SPANON_ERR_NULL_POINTER;
+  if ((norm_mean == nullptr) != (norm_std == nullptr)) return SPANON_ERR_NULL_POINTER;
+  const int run_clf = logp != nullptr;
+  if (run_clf && (!workspace || workspace_bytes < spanon_fcae_workspace_bytes(B, T))) return SPANON_ERR_WORKSPACE;
+  if (run_clf && (reinterpret_cast<uintptr_t>(workspace) & 7)) return SPANON_ERR_MISALIGNED;
+  cudaStream_t st = as_stream(stream);
+  static bool attr_done = false;
+  static int n_sm = 148;
+  if (!attr_done) {
+    SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sizeof(FcSmem)));
+    int dev = 0;
+    SPANON_CUDA_TRY(cudaGetDevice(&dev));
+    SPANON_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    attr_done = true;
+  }
+  double* pool = reinterpret_cast<double*>(workspace);
+  if (run_clf) SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
+  const int64_t n_frames = B * T;
+  const int64_t n_tiles = ceil_div(n_frames, NTHR);
+  const unsigned grid = (unsigned)std::min<int64_t>(n_tiles, n_sm);
+  fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                  n_frames, (int)T, run_clf);
+  SPANON_TRY(check_launch("fcae_kernel"));
+  if (run_clf) {
+    fcae_head_kernel<<<(unsigned)B, 64, 0, st>>>(pool, pool_noise, *w, (int)T, logp);
+    SPANON_TRY(check_launch("fcae_head_kernel"));
+  }
+  return SPANON_OK;
+}

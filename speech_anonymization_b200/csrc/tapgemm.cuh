@@ -1,0 +1,60 @@
+// "Tap GEMM": the one operator every ConvAutoencoder / TDNN layer is lowered to.
+//
+// Activations live channels-last, [utterance][row][channel].  A layer is
+//     out[b, m, :] = epilogue( sum_taps  T(in[b, m + shift[tap], :]) @ W[tap] )
+// with rows outside [0, rows_in) contributing zeros (= the conv's zero padding, applied
+// AFTER the input transform T like in the reference, where the padded tensor is the
+// already normalised/activated one).
+//   * Conv1d stride 1 (any dilation): shift = dilation*t - padding, W[tap] = w[:, :, t]^T.
+//   * Conv1d stride 2 (k5, p2): the input is VIEWED as [rows/2][2*Cin] (same bytes), three
+//     taps at shifts -1, 0, +1; the sixth (non-existent) tap slice is zero weights.
+//   * ConvTranspose1d stride 2 (k5, p2, op1): the OUTPUT is viewed as [rows][2*Cout]
+//     (even | odd phase), three taps at shifts -1, 0, +1, one zero slice.
+//   (models/ConvAutoEncoder.py:141-172 for the layer list; :33-43 for the dilated TDNN.)
+// Input transform T (consumer-side fusion of the previous layer's InstanceNorm + "GLU"):
+//     T(x)[c] = act(x*s1[b,c] + h1[b,c]) * s2[c] + h2[c]      (each part optional)
+// Epilogue: + bias, optional ReLU, per-(b,c) sum / sum-of-squares for the NEXT
+// InstanceNorm (fp64 atomics), optional affine (folded eval-mode BatchNorm), store.
+#pragma once
+#include "common.cuh"
+
+namespace spanon {
+
+constexpr int MAX_TAPS = 16;
+
+enum OutMode {
+  OUT_CHANNELS_LAST = 0,   // [B][rows_out][cout_v] in the activation dtype
+  OUT_CHANNELS_FIRST_F32,  // [B][cout_v][rows_out] fp32 (TDNN output -> pooling, reference layout)
+  OUT_CH0_F32              // [B][rows_out] fp32, channel 0 only (decoder.8 -> recon)
+};
+
+struct TapGemmParams {
+  const void* in;
+  void* out;
+  int64_t in_bstride, out_bstride;  // elements per utterance
+  int rows_in, rows_out;
+  int cin_v, cout_v, cin_mod, cout_mod;
+  int ntaps;
+  int shift[MAX_TAPS];
+  const void* w;       // packed weights (layout depends on the kernel family)
+  const float* t1_scale; const float* t1_shift;  // [B][cin_mod] or null
+  int silu;
+  const float* t2_scale; const float* t2_shift;  // [cin_mod] or null
+  const float* bias;   // [cout_mod]
+  int relu;
+  const float* e_scale; const float* e_shift;    // [cout_mod] or null
+  double* stats;       // [B][cout_mod][2] or null
+  int out_mode;
+  int B;
+};
+
+// fp32 CUDA-core family (conv_fp32.cu).  Packed weights: fp32 [ntaps][cin_v][cout_v].
+template <typename TAct>
+int launch_tapgemm_simt(const TapGemmParams& p, cudaStream_t st);
+
+// tcgen05 family (conv_tc.cu).  bf16 activations; packed weights: bf16 UMMA core-matrix
+// layout [ntaps][cin_v/8][cout_v][8].
+int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st);
+bool tapgemm_tc_available();  // false until SPANON_DISABLE_TC is unset and the kernel is built in
+
+}  // namespace spanon
