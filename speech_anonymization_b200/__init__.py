@@ -1,0 +1,16 @@
+"""speech_anonymization_b200 -- B200-native (sm_100a) Fbank + anonymizer hot path of
+viswavi/speech-anonymization behind the reference's own Python class API.
+
+Everything numeric runs in libspanon.so (include/spanon.h); there is no CPU or PyTorch
+fallback -- a missing library or a non-CUDA tensor raises.
+"""
+from ._lib import SpanonError, lib  # noqa: F401
+from .features import Fbank, InputNormalization, pad_time  # noqa: F401
+from .losses import (ClusterMI, CosineSimilarityLoss, GroupSampler, GroupSamplingMI, MILoss,  # noqa: F401
+                     SimilarityMetricsStats, cosine_distance_2d, knn_mi)
+from .models import (GLU, ConvAutoencoder, FullyConnectedAutoencoder, FullyConnSexClassifier,  # noqa: F401
+                     GradReverse, StatisticsPooling, TDNNSexClassifier)
+from .pipeline import AnonymizerPipeline, shard_range  # noqa: F401
+
+__all__ = ["Fbank", "InputNormalization", "ConvAutoencoder", "FullyConnectedAutoencoder", "CosineSimilarityLoss",
+           "MILoss", "ClusterMI", "GroupSamplingMI", "AnonymizerPipeline", "shard_range", "pad_time", "lib"]

@@ -259,9 +259,10 @@ class InputNormalization(torch.nn.Module):
         return out
 
     def _glob_uninitialised(self, t):
-        # features.py:1114-1117 (`shape[0] == 1 and not is_nonzero`): only the ctor sentinel tensor([0])
-        # (or a loaded all-zero scalar) satisfies it; checked without touching the device
-        return t.dim() == 1 and t.shape[0] == 1 and t.device.type == "cpu" and not torch.is_nonzero(t)
+        # features.py:1114-1117 (`shape[0] == 1 and not is_nonzero`): true only for the constructor's
+        # sentinel torch.tensor([0]).  The sentinel is the only INTEGER tensor these attributes ever
+        # hold (statistics are fp32), so the dtype identifies it without a device round trip.
+        return isinstance(t, int) or (t.dim() == 1 and t.shape[0] == 1 and not t.is_floating_point())
 
     def forward(self, x, lengths, spk_ids=torch.tensor([]), epoch=0):
         """Returns the normalised tensor (features.py:998-1121)."""

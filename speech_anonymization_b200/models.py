@@ -1,0 +1,313 @@
+"""Host-side mirror of the reference's anonymizer modules, backed by libspanon's CUDA kernels.
+
+  ConvAutoencoder / TDNNSexClassifier / GLU / GradReverse   models/ConvAutoEncoder.py:12-69,113-200
+  FullyConnectedAutoencoder / FullyConnSexClassifier        models/FullyConnected.py:65-159
+  StatisticsPooling                                         speechbrain/speechbrain/nnet/pooling.py:229-326
+
+The modules are built from the same torch.nn layer objects in the same order as the reference,
+so `state_dict()` keys, default initialisation under a given seed and checkpoint loading are
+identical; the layer objects are parameter containers only -- `forward` hands the parameter
+storages to one C call (spanon_convae_fwd / spanon_fcae_fwd).  Forward only (inference /
+evaluation, eval-mode BatchNorm): the backward pass is a later row of the scope table.
+"""
+import ctypes as C
+import os
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class GradReverse(torch.autograd.Function):
+    """models/ConvAutoEncoder.py:12-28 (identity forward, negated gradient)."""
+
+    @staticmethod
+    def forward(ctx, input):
+        return input
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return -grad_output.clone()
+
+    def grad_reverse(input):
+        return GradReverse.apply(input)
+
+
+class GLU(nn.Module):
+    """models/ConvAutoEncoder.py:113-120: x * sigmoid(x), no channel halving (marker module:
+    the kernels fuse it into the consumer's operand load)."""
+
+    def forward(self, input):
+        return input * torch.sigmoid(input)
+
+
+class StatisticsPooling(nn.Module):
+    """Noise source of speechbrain.nnet.pooling.StatisticsPooling (pooling.py:313-326); the pooling
+    itself runs inside the classifier kernels."""
+
+    def __init__(self, return_mean=True, return_std=True):
+        super().__init__()
+        self.eps = 1e-5
+        self.return_mean = return_mean
+        self.return_std = return_std
+        if not (self.return_mean or self.return_std):
+            raise ValueError("both of statistics are equal to False \n"
+                             "consider enabling mean and/or std statistic pooling")
+
+    def _get_gauss_noise(self, shape_of_tensor, device="cpu"):
+        gnoise = torch.randn(shape_of_tensor, device=device)
+        gnoise -= torch.min(gnoise)
+        gnoise /= torch.max(gnoise)
+        gnoise = self.eps * ((1 - 9) * gnoise + 9)
+        return gnoise
+
+
+def _p(t):
+    if t.dtype != torch.float32 or not t.is_cuda:
+        raise _lib.SpanonError("module parameters must be fp32 CUDA tensors (got %s on %s); call .to('cuda')"
+                               % (t.dtype, t.device))
+    if not t.is_contiguous():
+        raise _lib.SpanonError("module parameters must be contiguous")
+    return t.data_ptr()
+
+
+def _bn(m):
+    return _lib.BatchNorm(_p(m.weight), _p(m.bias), _p(m.running_mean), _p(m.running_var))
+
+
+def _forward_only_guard(module, inp):
+    if torch.is_grad_enabled() and (inp.requires_grad or any(p.requires_grad for p in module.parameters())):
+        raise NotImplementedError(
+            "%s: only the forward pass runs on the CUDA kernels; call under torch.no_grad() "
+            "(the backward pass is scope row 8(f)-1)" % type(module).__name__)
+    if any(isinstance(m, nn.modules.batchnorm._BatchNorm) and m.training for m in module.modules()):
+        raise NotImplementedError(
+            "%s: train-mode BatchNorm (batch statistics) is not implemented; call .eval()"
+            % type(module).__name__)
+
+
+def _precision_from_env():
+    v = os.environ.get("SPANON_PRECISION", "bf16").lower()
+    if v not in ("bf16", "fp32"):
+        raise ValueError("SPANON_PRECISION must be bf16 or fp32")
+    return v
+
+
+class TDNNSexClassifier(nn.Module):
+    """models/ConvAutoEncoder.py:30-69 (parameter container; computed inside spanon_convae_fwd)."""
+
+    def __init__(self, num_classes):
+        super().__init__()
+        self.tdnn = nn.Sequential(
+            nn.Conv1d(in_channels=128, out_channels=128, kernel_size=5, dilation=1), nn.ReLU(), nn.BatchNorm1d(128),
+            nn.Conv1d(in_channels=128, out_channels=128, kernel_size=3, dilation=2), nn.ReLU(), nn.BatchNorm1d(128),
+            nn.Conv1d(in_channels=128, out_channels=128, kernel_size=3, dilation=3), nn.ReLU(), nn.BatchNorm1d(128),
+        )
+        self.norm = nn.BatchNorm1d(128)
+        self.stats_pooling = StatisticsPooling()
+        self.classify = nn.Sequential(
+            nn.Linear(256, 128), nn.ReLU(), nn.BatchNorm1d(128),
+            nn.Linear(128, 64), nn.ReLU(), nn.BatchNorm1d(64),
+            nn.Linear(64, num_classes),
+        )
+
+    def forward(self, input):
+        raise NotImplementedError("TDNNSexClassifier runs fused inside ConvAutoencoder.forward")
+
+
+class ConvAutoencoder(nn.Module):
+    """Drop-in for models.ConvAutoEncoder.ConvAutoencoder (models/ConvAutoEncoder.py:136-200).
+
+    forward(input [B,T,F]) -> (reconstruction [B,T,F], sex log-probs [B,2]).
+    `precision`: "bf16" (tcgen05 tensor cores, <= 1e-2 rel.) or "fp32" (<= 1e-4 rel.);
+    default from $SPANON_PRECISION, else bf16.
+    """
+
+    def __init__(self):
+        super().__init__()
+        self.encoder = nn.Sequential(
+            nn.Conv1d(in_channels=1, out_channels=32, kernel_size=15, stride=1, padding=7), GLU(),
+            nn.Conv1d(in_channels=32, out_channels=64, kernel_size=5, stride=2, padding=2),
+            nn.InstanceNorm1d(num_features=64, affine=True), GLU(),
+            nn.Conv1d(in_channels=64, out_channels=64, kernel_size=5, stride=1, padding=2),
+            nn.InstanceNorm1d(num_features=64, affine=True), GLU(),
+            nn.Conv1d(in_channels=64, out_channels=128, kernel_size=5, stride=2, padding=2),
+            nn.InstanceNorm1d(num_features=128, affine=True), GLU(),
+            nn.Conv1d(in_channels=128, out_channels=128, kernel_size=5, stride=1, padding=2),
+            nn.InstanceNorm1d(num_features=128, affine=True), GLU(),
+        )
+        self.decoder = nn.Sequential(
+            nn.Conv1d(in_channels=128, out_channels=128, kernel_size=5, stride=1, padding=2),
+            nn.ConvTranspose1d(in_channels=128, out_channels=64, kernel_size=5, stride=2, padding=2,
+                               output_padding=1),
+            nn.InstanceNorm1d(num_features=64, affine=True), GLU(),
+            nn.Conv1d(in_channels=64, out_channels=64, kernel_size=5, stride=1, padding=2),
+            nn.ConvTranspose1d(in_channels=64, out_channels=32, kernel_size=5, stride=2, padding=2,
+                               output_padding=1),
+            nn.InstanceNorm1d(num_features=32, affine=True), GLU(),
+            nn.Conv1d(in_channels=32, out_channels=1, kernel_size=15, stride=1, padding=7),
+        )
+        self.sex_classifier = TDNNSexClassifier(2)
+        self.precision = _precision_from_env()
+        self.chunk_utts = 0  # 0 = library default (L2-resident chunks)
+
+    def weight_struct(self):
+        e, d, s = self.encoder, self.decoder, self.sex_classifier
+        w = _lib.ConvAEWeights()
+        for i, k in enumerate((0, 2, 5, 8, 11)):
+            w.enc_w[i], w.enc_b[i] = _p(e[k].weight), _p(e[k].bias)
+        for i, k in enumerate((3, 6, 9, 12)):
+            w.enc_in_w[i], w.enc_in_b[i] = _p(e[k].weight), _p(e[k].bias)
+        for i, k in enumerate((0, 1, 4, 5, 8)):
+            w.dec_w[i], w.dec_b[i] = _p(d[k].weight), _p(d[k].bias)
+        for i, k in enumerate((2, 6)):
+            w.dec_in_w[i], w.dec_in_b[i] = _p(d[k].weight), _p(d[k].bias)
+        w.clf_norm = _bn(s.norm)
+        for i, k in enumerate((0, 3, 6)):
+            w.tdnn_w[i], w.tdnn_b[i] = _p(s.tdnn[k].weight), _p(s.tdnn[k].bias)
+            w.tdnn_bn[i] = _bn(s.tdnn[k + 2])
+        for i, k in enumerate((0, 3, 6)):
+            w.cls_w[i], w.cls_b[i] = _p(s.classify[k].weight), _p(s.classify[k].bias)
+        w.cls_bn[0], w.cls_bn[1] = _bn(s.classify[2]), _bn(s.classify[5])
+        return w
+
+    def opts(self, skip_classifier=False):
+        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_BF16,
+                               int(self.chunk_utts), int(skip_classifier), 0)
+
+    def forward(self, input, pool_noise=None, fused_norm=None):
+        """`pool_noise` [B,128]: the tensor StatisticsPooling adds to the pooled mean (default: drawn
+        like the reference, pooling.py:313-326).  `fused_norm` = (mean [F], std [F], utt_max [B],
+        top_db, T_pad): `input` is then RAW Fbank dB [B,T,F] and clamp + normalisation + zero padding to
+        T_pad run inside the first layer's load (used by AnonymizerPipeline)."""
+        _lib.require_cuda(input, "input")
+        _forward_only_guard(self, input)
+        if input.dim() != 3:
+            raise ValueError("ConvAutoencoder expects [batch, time, features]")
+        x = input.contiguous()
+        B, T_in, F = x.shape
+        T = T_in if fused_norm is None else int(fused_norm[4])
+        if (T * F) % 4 != 0:  # the reference's final reshape fails for these shapes (:197-198)
+            raise RuntimeError("shape '[%d, %d, %d]' is invalid for input of size %d: time*features must be a "
+                               "multiple of 4" % (B, T, F, B * 4 * (-(-T * F // 4))))
+        dev = x.device
+        recon = torch.empty((B, T, F), dtype=torch.float32, device=dev)
+        logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
+        if B == 0:
+            return recon, logp
+        if pool_noise is None:
+            pool_noise = self.sex_classifier.stats_pooling._get_gauss_noise((B, 128), device=dev)
+        pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
+        w = self.weight_struct()
+        opts = self.opts()
+        L = _lib.lib()
+        ws_bytes = L.spanon_convae_workspace_bytes(B, T, F, C.byref(opts))
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        if fused_norm is None:
+            mean = std = umax = None
+            top_db, t_valid = 0.0, T
+        else:
+            mean, std, umax, top_db = fused_norm[0], fused_norm[1], fused_norm[2], float(fused_norm[3])
+            mean = mean.to(device=dev, dtype=torch.float32).contiguous()
+            std = std.to(device=dev, dtype=torch.float32).contiguous()
+            t_valid = T_in
+        with torch.cuda.device(dev):
+            _lib.check(L.spanon_convae_fwd(_lib.ptr(x), C.byref(w), _lib.ptr(pool_noise), _lib.ptr(mean),
+                                           _lib.ptr(std), _lib.ptr(umax), top_db, t_valid, _lib.ptr(recon),
+                                           _lib.ptr(logp), _lib.ptr(ws), ws_bytes, B, T, F, C.byref(opts),
+                                           _lib.stream_ptr(dev)), "convae_fwd")
+        return recon, logp
+
+
+class FullyConnSexClassifier(nn.Module):
+    """models/FullyConnected.py:65-104 (parameter container; computed inside spanon_fcae_fwd)."""
+
+    def __init__(self, num_classes):
+        super().__init__()
+        self.initial = nn.Sequential(nn.Linear(20, 40), nn.ReLU(), nn.Linear(40, 40), nn.ReLU())
+        self.norm = nn.BatchNorm1d(20)
+        self.classify = nn.Sequential(
+            nn.Linear(80, 40), nn.BatchNorm1d(40), nn.ReLU(),
+            nn.Linear(40, 40), nn.ReLU(),
+            nn.Linear(40, 20), nn.BatchNorm1d(20),
+            nn.Linear(20, num_classes),
+        )
+        self.stats_pooling = StatisticsPooling()
+
+    def forward(self, input):
+        raise NotImplementedError("FullyConnSexClassifier runs fused inside FullyConnectedAutoencoder.forward")
+
+
+class FullyConnectedAutoencoder(nn.Module):
+    """Drop-in for models.FullyConnected.FullyConnectedAutoencoder (models/FullyConnected.py:118-159).
+
+    forward(input [B,T,mfcc_feature_dim]) -> (reconstruction [B,T,80], sex log-probs [B,2]); fp32.
+    """
+
+    def __init__(self, mfcc_feature_dim, batch_size):
+        super().__init__()
+        self.mfcc_feature_dim = mfcc_feature_dim
+        self.batch_size = batch_size
+        self.encoder = nn.Sequential(
+            nn.Linear(in_features=self.mfcc_feature_dim, out_features=60), nn.ReLU(),
+            nn.Linear(in_features=60, out_features=40), nn.ReLU(),
+            nn.Linear(in_features=40, out_features=20),
+        )
+        self.decoder = nn.Sequential(
+            nn.Linear(in_features=20, out_features=40), nn.ReLU(),
+            nn.Linear(in_features=40, out_features=60), nn.ReLU(),
+            nn.Linear(in_features=60, out_features=80),
+        )
+        self.sex_classifier = FullyConnSexClassifier(2)
+
+    def weight_struct(self):
+        e, d, s = self.encoder, self.decoder, self.sex_classifier
+        w = _lib.FcaeWeights()
+        w.in_dim = self.mfcc_feature_dim
+        for i, k in enumerate((0, 2, 4)):
+            w.enc_w[i], w.enc_b[i] = _p(e[k].weight), _p(e[k].bias)
+            w.dec_w[i], w.dec_b[i] = _p(d[k].weight), _p(d[k].bias)
+        w.clf_norm = _bn(s.norm)
+        for i, k in enumerate((0, 2)):
+            w.init_w[i], w.init_b[i] = _p(s.initial[k].weight), _p(s.initial[k].bias)
+        for i, k in enumerate((0, 3, 5, 7)):
+            w.cls_w[i], w.cls_b[i] = _p(s.classify[k].weight), _p(s.classify[k].bias)
+        w.cls_bn1, w.cls_bn6 = _bn(s.classify[1]), _bn(s.classify[6])
+        return w
+
+    def forward(self, input, pool_noise=None, fused_norm=None):
+        """`fused_norm` = (mean [F], std [F], utt_max [B], top_db): input is RAW Fbank dB."""
+        _lib.require_cuda(input, "input")
+        _forward_only_guard(self, input)
+        if input.dim() != 3 or input.shape[2] != self.mfcc_feature_dim:
+            raise RuntimeError("mat1 and mat2 shapes cannot be multiplied (expected last dim %d, got %s)"
+                               % (self.mfcc_feature_dim, tuple(input.shape)))
+        if self.mfcc_feature_dim != 80:
+            raise NotImplementedError("the fused FC-AE kernel covers mfcc_feature_dim == 80 (all reference configs)")
+        x = input.contiguous()
+        B, T, F = x.shape
+        dev = x.device
+        recon = torch.empty((B, T, 80), dtype=torch.float32, device=dev)
+        logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
+        if B == 0 or T == 0:
+            return recon, logp
+        if pool_noise is None:
+            pool_noise = self.sex_classifier.stats_pooling._get_gauss_noise((B, 40), device=dev)
+        pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
+        w = self.weight_struct()
+        L = _lib.lib()
+        ws_bytes = L.spanon_fcae_workspace_bytes(B, T)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        if fused_norm is None:
+            mean = std = umax = None
+            top_db = 0.0
+        else:
+            mean = fused_norm[0].to(device=dev, dtype=torch.float32).contiguous()
+            std = fused_norm[1].to(device=dev, dtype=torch.float32).contiguous()
+            umax, top_db = fused_norm[2], float(fused_norm[3])
+        with torch.cuda.device(dev):
+            _lib.check(L.spanon_fcae_fwd(_lib.ptr(x), C.byref(w), _lib.ptr(pool_noise), _lib.ptr(mean), _lib.ptr(std),
+                                         _lib.ptr(umax), top_db, _lib.ptr(recon), _lib.ptr(logp), _lib.ptr(ws),
+                                         ws_bytes, B, T, _lib.stream_ptr(dev)), "fcae_fwd")
+        return recon, logp

@@ -1,0 +1,92 @@
+"""The composed hot path: waveform -> Fbank -> InputNormalization -> (pad T to x36) -> anonymizer.
+
+Mirrors SexAnonymizationTraining.compute_forward (speechbrain_convae_train.py:42-69) and
+GenderBrain.prepare_features (gender_classifier_train_recon.py:84-90).  With frozen (eval-mode,
+initialised) global normalisation statistics the clamp, the normalisation and the padding are
+folded into the anonymizer's first load, so the features cross HBM once.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .features import Fbank, InputNormalization, pad_time
+from .models import ConvAutoencoder, FullyConnectedAutoencoder
+
+
+def shard_range(n_items, rank, world_size):
+    """Contiguous slice [lo, hi) of a batch of independent utterances owned by `rank` (SURVEY 8e:
+    inference shards by utterance with no collective)."""
+    base, rem = divmod(n_items, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class AnonymizerPipeline(torch.nn.Module):
+    def __init__(self, compute_features: Fbank, normalize: InputNormalization, model):
+        super().__init__()
+        self.compute_features = compute_features
+        self.normalize = normalize
+        self.model = model
+        self.is_conv = isinstance(model, ConvAutoencoder)
+        if not self.is_conv and not isinstance(model, FullyConnectedAutoencoder):
+            raise TypeError("model must be a ConvAutoencoder or a FullyConnectedAutoencoder")
+
+    def padded_frames(self, T):
+        return (T + 35) // 36 * 36 if self.is_conv else T  # train.py:62 (skipped for fcae)
+
+    def _frozen_stats(self):
+        n = self.normalize
+        return (n.norm_type == "global" and not n.training and n.mean_norm and n.std_norm
+                and n.glob_mean.dim() == 1 and n.glob_mean.shape[0] == self.compute_features.n_mels)
+
+    @torch.no_grad()
+    def forward(self, wavs, wav_lens=None, epoch=0, pool_noise=None):
+        """wavs [B, n_samples] on the GPU -> (anonymized feats [B, T', F], sex log-probs [B, 2])."""
+        fb = self.compute_features
+        if self._frozen_stats():
+            raw, utt_max = fb.forward_raw(wavs)
+            T = raw.shape[1]
+            n = self.normalize
+            if self.is_conv:
+                fused = (n.glob_mean, n.glob_std, utt_max, fb.top_db, self.padded_frames(T))
+            else:
+                fused = (n.glob_mean, n.glob_std, utt_max, fb.top_db)
+            return self.model(raw, pool_noise=pool_noise, fused_norm=fused)
+        feats = fb(wavs)
+        if wav_lens is None:
+            wav_lens = torch.ones(wavs.shape[0], device=wavs.device)
+        feats = self.normalize(feats, wav_lens, epoch=epoch)
+        if self.is_conv:
+            feats = pad_time(feats)
+        return self.model(feats, pool_noise=pool_noise)
+
+    # -- host-buffer path through the single C entry point (bench.py's e2e leg)
+    def host_workspace(self, B, n_samples, device):
+        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        nbytes = _lib.lib().spanon_anonymize_workspace_bytes(0 if self.is_conv else 1, B, n_samples,
+                                                             self.compute_features.hop_length,
+                                                             self.compute_features.n_mels, C.byref(opts))
+        return torch.empty((nbytes,), dtype=torch.uint8, device=device)
+
+    @torch.no_grad()
+    def anonymize_host(self, pcm_host, recon_host, logp_host, workspace, pool_noise=None):
+        """pcm_host [B, n] (pinned) host fp32 -> recon_host [B, T', F], logp_host [B, 2] host tensors.
+        H2D copy, all kernels, D2H copy and the stream sync happen inside spanon_anonymize_host."""
+        if not self._frozen_stats():
+            raise _lib.SpanonError("anonymize_host needs eval-mode InputNormalization with loaded global statistics")
+        dev = workspace.device
+        fb, n = self.compute_features, self.normalize
+        st = fb._device_state(dev)
+        mean = n.glob_mean.to(device=dev, dtype=torch.float32).contiguous()
+        std = n.glob_std.to(device=dev, dtype=torch.float32).contiguous()
+        w = self.model.weight_struct()
+        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        B, ns = pcm_host.shape
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().spanon_anonymize_host(
+                0 if self.is_conv else 1, _lib.ptr(pcm_host), B, ns, C.byref(st["cfg"]), _lib.ptr(mean),
+                _lib.ptr(std), C.cast(C.byref(w), C.c_void_p), _lib.ptr(pool_noise), C.byref(opts),
+                _lib.ptr(recon_host), _lib.ptr(logp_host), _lib.ptr(workspace), workspace.numel(),
+                _lib.stream_ptr(dev)), "anonymize_host")
+        return recon_host, logp_host

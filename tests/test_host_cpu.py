@@ -1,0 +1,159 @@
+"""CPU-only checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+include/spanon.h declares, argument validation works without a device, and the host-side
+mirror of the reference interface (state_dict keys, filter matrix, samplers, sharding) is right."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import recipe
+import speech_anonymization_b200 as sab
+from speech_anonymization_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "spanon.h")).read()
+    return sorted(set(re.findall(r"SPANON_API[^;(]*?\b(spanon_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared()
+    assert len(names) >= 18
+    handle = C.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(handle, n), n
+    assert sorted(_lib.SIGNATURES) == names          # the ctypes binding covers the whole header
+    assert _lib.lib().spanon_abi_version() == 1
+    assert _lib.lib().spanon_strerror(-4).decode().startswith("workspace")
+
+
+def test_c_abi_argument_validation_without_device():
+    L = _lib.lib()
+    assert L.spanon_num_frames(160000, 160) == 1001
+    assert L.spanon_num_frames(0, 160) == 1
+    assert L.spanon_num_frames(5, 0) == -1
+    assert L.spanon_fbank_f32(None, 1, 10, 10, None, None, None, None) == -2       # NULL cfg
+    cfg = _lib.FbankCfg(400, 400, 160, 80, 1e-10, 10.0, 0.0, 80.0, 0, 0, 0, 0, 0)
+    assert L.spanon_fbank_f32(None, 1, 10, 5, None, None, C.byref(cfg), None) == -1  # stride < n
+    assert L.spanon_fbank_f32(None, 0, 10, 10, None, None, C.byref(cfg), None) == 0  # empty batch
+    assert L.spanon_fbank_f32(None, 1, 10, 10, None, None, C.byref(cfg), None) == -2
+    assert L.spanon_norm_apply(None, None, None, None, 3, None, 80.0, 1, 4, 4, 80, None) == -1
+    opts = _lib.ConvAEOpts(_lib.PREC_BF16, 0, 0, 0)
+    assert L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts)) > 8 * 80640 * 32 * 2
+    assert L.spanon_convae_workspace_bytes(0, 1008, 80, C.byref(opts)) == 0
+    assert L.spanon_convae_fwd(None, None, None, None, None, None, 0.0, 0, None, None, None, 0, 1, 36, 80,
+                               C.byref(opts), None) == -2
+    w = _lib.ConvAEWeights()
+    assert L.spanon_convae_fwd(None, C.byref(w), None, None, None, None, 0.0, 0, None, None, None, 0, 1, 37, 81,
+                               C.byref(opts), None) == -1                            # L % 4 != 0
+    assert L.spanon_knn_mi_stats(None, None, None, 1, 2, 4, 2, 3, None, None, None, None) == -5   # k+1 > N
+    assert L.spanon_anonymize_workspace_bytes(0, 64, 160000, 160, 80, C.byref(opts)) > 64 * 160000 * 4
+
+
+def test_state_dict_keys_match_reference():
+    torch.manual_seed(8886)
+    m = sab.ConvAutoencoder()
+    sd = m.state_dict()
+    assert set(sd) == set(recipe.CONVAE_SHAPES)
+    for k, shp in recipe.CONVAE_SHAPES.items():
+        assert tuple(sd[k].shape) == tuple(shp), k
+    fc = sab.FullyConnectedAutoencoder(80, 8)
+    sd = fc.state_dict()
+    assert set(sd) == set(recipe.FCAE_SHAPES)
+    for k, shp in recipe.FCAE_SHAPES.items():
+        assert tuple(sd[k].shape) == tuple(shp), k
+    assert sum(p.numel() for p in m.parameters()) == 533123
+    m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in recipe.make_weights(recipe.CONVAE_SHAPES, 1).items()})
+
+
+def test_fbank_host_logic(golden):
+    fb = sab.Fbank(n_mels=80)
+    assert (fb.win_length, fb.hop_length, fb.n_stft) == (400, 160, 201)
+    mm = fb.fbank_matrix()
+    assert np.array_equal(mm.numpy(), golden["mel_matrix80"])          # bit-exact filter weights
+    start, length, off, w = fb._taps(mm)
+    assert w.numel() == 387 and int(length.max()) == 13
+    rebuilt = np.zeros((201, 80), np.float32)
+    for m in range(80):
+        s, n, o = int(start[m]), int(length[m]), int(off[m])
+        rebuilt[s:s + n, m] = w[o:o + n].numpy()
+    assert np.array_equal(rebuilt, golden["mel_matrix80"])
+    assert np.array_equal(sab.Fbank().fbank_matrix().numpy(), golden["mel_matrix40"])
+    assert np.array_equal(fb.window.numpy(), torch.hamming_window(400).numpy())
+    for n in (0, 1, 159, 160, 161, 400, 16000, 160000):
+        assert fb.num_frames(n) == 1 + n // 160
+    with pytest.raises(NotImplementedError):
+        sab.Fbank(deltas=True)
+
+
+def test_no_cpu_fallback():
+    fb = sab.Fbank(n_mels=80)
+    with pytest.raises(sab.SpanonError):
+        fb(torch.zeros(1, 800))
+    with pytest.raises(sab.SpanonError):
+        sab.ConvAutoencoder().eval()(torch.zeros(1, 36, 80))
+    with pytest.raises(sab.SpanonError):
+        sab.InputNormalization()(torch.zeros(1, 6, 1), torch.ones(1))
+    with pytest.raises(sab.SpanonError):
+        sab.CosineSimilarityLoss()(torch.zeros(1, 2, 3), torch.zeros(1, 2, 3))
+
+
+def test_group_sampler_matches_pandas_semantics():
+    import pandas as pd
+    groups = ["b", "a", "c", "a", "b", "c", "a", "b"]
+    gs = sab.GroupSampler(groups, 2)
+    ref = {k: np.array(list(v)) for k, v in pd.DataFrame(groups, columns=["groups"]).groupby("groups").groups.items()}
+    assert list(gs.group_samples) == list(ref)
+    for k in ref:
+        assert np.array_equal(gs.group_samples[k], ref[k])
+    np.random.seed(3)
+    a = gs.sample_groups()
+    np.random.seed(3)
+    b = []
+    for g in ref:
+        b.extend(ref[g][np.random.choice(len(ref[g]), 2, replace=False)])
+    assert a == b
+
+
+def test_shard_range_partitions_batch():
+    for n in (0, 1, 7, 8, 64, 360):
+        for ws in (1, 2, 3, 8):
+            spans = [sab.shard_range(n, r, ws) for r in range(ws)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(spans[i][1] == spans[i + 1][0] for i in range(ws - 1))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _gloo_worker(rank, world, port, out):
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    lo, hi = sab.shard_range(13, rank, world)
+    owned = torch.zeros(13)
+    owned[lo:hi] = 1
+    dist.all_reduce(owned)                      # test-only collective: every utterance owned exactly once
+    t = torch.tensor([float(hi - lo) * (rank + 1)])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)    # bench.py's max-over-ranks timing reduction
+    if rank == 0:
+        out.put((owned.tolist(), float(t)))
+    dist.destroy_process_group()
+
+
+def test_two_rank_gloo_sharding():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    owned, tmax = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert owned == [1.0] * 13 and tmax == 12.0
