@@ -129,3 +129,226 @@ class ClockSampler(threading.Thread):
         reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
                 "samples": len(self.rows)}
+
+
+# --------------------------------------------------------------------------- helpers
+# per-utterance algorithmic flops of each conv launch (SURVEY.md 8a / DESIGN.md "Kernels"), L = 80640
+def convae_layer_flops(L=80640):
+    mac = {"first_layer_kernel": L * 15 * 32,
+           "tapgemm:enc2": (L // 2) * 32 * 5 * 64, "tapgemm:enc5": (L // 2) * 64 * 5 * 64,
+           "tapgemm:enc8": (L // 4) * 64 * 5 * 128, "tapgemm:enc11": (L // 4) * 128 * 5 * 128,
+           "tapgemm:tdnn0": (L // 4 - 4) * 128 * 5 * 128, "tapgemm:tdnn3": (L // 4 - 8) * 128 * 3 * 128,
+           "tapgemm:tdnn6": (L // 4 - 14) * 128 * 3 * 128,
+           "tapgemm:dec0": (L // 4) * 128 * 5 * 128, "tapgemm:dec1": (L // 4) * 128 * 5 * 64,
+           "tapgemm:dec4": (L // 2) * 64 * 5 * 64, "tapgemm:dec5": (L // 2) * 64 * 5 * 32,
+           "tapgemm:dec8": L * 32 * 15}
+    return {k: 2.0 * v for k, v in mac.items()}
+
+
+def dist_setup(n_gpus):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    elif n_gpus > 1:
+        raise SystemExit("--gpus %d needs torchrun (one process per GPU)" % n_gpus)
+    return world, rank, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def max_over_ranks(v, world, device):
+    if world == 1:
+        return v
+    import torch.distributed as dist
+    t = torch.tensor([v], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def build_pipeline(workload, precision, device):
+    import recipe
+    import speech_anonymization_b200 as sab
+    mean, std, count = real_norm_stats()
+    fb = sab.Fbank(n_mels=80)
+    norm = sab.InputNormalization(norm_type="global", update_until_epoch=4)
+    norm._load_statistics_dict({"count": count, "glob_mean": torch.from_numpy(mean), "glob_std": torch.from_numpy(std),
+                                "spk_dict_mean": {}, "spk_dict_std": {}, "spk_dict_count": {}})
+    norm = norm.to(device).eval()
+    if workload == "convae":
+        model, shapes = sab.ConvAutoencoder(), recipe.CONVAE_SHAPES
+        model.precision = precision
+    else:
+        model, shapes = sab.FullyConnectedAutoencoder(80, 64), recipe.FCAE_SHAPES
+    w = recipe.make_weights(shapes, 8886)   # random-init weights, seed 8886 (convae.yaml:11)
+    model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in w.items()})
+    model = model.to(device).eval()
+    return sab.AnonymizerPipeline(fb, norm, model)
+
+
+# --------------------------------------------------------------------------- our arm
+def run_ours(a):
+    import recipe
+    import speech_anonymization_b200 as sab
+    from speech_anonymization_b200 import _lib
+    world, rank, local = dist_setup(a.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a CUDA device: there is no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    pk = peaks()
+    pipe = build_pipeline(a.workload, a.precision, dev)
+    B, pool_n = a.batch, max(a.pool, a.batch)
+    n_batches = pool_n // B
+    host_pool = make_wavs(n_batches * B, 1234 + rank).pin_memory()       # SURVEY 8(d) synthetic input
+    dev_pool = host_pool.to(dev)
+    nz = 128 if a.workload == "convae" else 40
+    noise = torch.from_numpy(recipe.make_noise(3, B, nz)).to(dev)
+    T = 1 + N_SAMPLES // 160
+    Tp = pipe.padded_frames(T)
+
+    def step_device(i):
+        k = i % n_batches
+        return pipe(dev_pool[k * B:(k + 1) * B], pool_noise=noise)
+
+    launches0 = _lib.lib().spanon_launch_count()
+    for i in range(a.warmup):
+        step_device(i)
+    torch.cuda.synchronize()
+    launches_w = _lib.lib().spanon_launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier(world)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        out = step_device(a.warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_total = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    barrier(world)
+    gpu_launches = int(_lib.lib().spanon_launch_count() - launches_w)
+    ms_step = ms_total / a.steps
+    value = world * B * UTT_SECONDS / (ms_step * 1e-3)
+
+    # ---- e2e: host PCM in (pinned), host features + log-probs out, through the single C entry point
+    rec_h = torch.empty((B, Tp, 80), dtype=torch.float32).pin_memory()
+    logp_h = torch.empty((B, 2), dtype=torch.float32).pin_memory()
+    ws = pipe.host_workspace(B, N_SAMPLES, dev)
+    for i in range(a.warmup):
+        pipe.anonymize_host(host_pool[(i % n_batches) * B:(i % n_batches + 1) * B], rec_h, logp_h, ws, pool_noise=noise)
+    barrier(world)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(a.steps):
+        k = (a.warmup + i) % n_batches
+        pipe.anonymize_host(host_pool[k * B:(k + 1) * B], rec_h, logp_h, ws, pool_noise=noise)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world, dev) / a.steps
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    e2e = {"value": world * B * UTT_SECONDS / (ms_e2e * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_e2e,
+           "h2d_bytes_per_step": B * N_SAMPLES * 4, "d2h_bytes_per_step": B * Tp * 80 * 4 + B * 8,
+           "api": "spanon_anonymize_host (pinned host buffers in/out, sync inside)"}
+
+    # ---- per-kernel event timing (consecutive CUDA events on the launch stream, 2 extra steps)
+    _lib.profile_begin(dev)
+    n_prof = 2
+    for i in range(n_prof):
+        step_device(a.warmup + a.steps + i)
+    prof = _lib.profile_end()
+    kern = {k: {"launches_per_step": n / n_prof, "ms_per_step": ms / n_prof} for k, (n, ms) in prof.items()}
+    prof_ms = sum(v["ms_per_step"] for v in kern.values())
+    if a.workload == "convae":
+        fl = convae_layer_flops(Tp * 80)
+        conv_ms = sum(v["ms_per_step"] for k, v in kern.items() if k in fl)
+        conv_launches = sum(v["launches_per_step"] for k, v in kern.items() if k in fl)
+        flops_step = sum(fl.values()) * B
+        achieved = flops_step / (conv_ms * 1e-3) / 1e12
+        peak = pk["tf_sust"]
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "conv stack (first_layer + tap-GEMM launches)",
+                "flops_per_launch": flops_step / max(conv_launches, 1), "ms_per_launch": conv_ms / max(conv_launches, 1),
+                "share_of_step": conv_ms / prof_ms, "peak_source": pk["src"] + " bf16 sustained"}
+    else:
+        km = kern.get("fbank400_kernel", {"ms_per_step": float("nan"), "launches_per_step": 1})
+        achieved = BYTES_FBANK_UTT * B / (km["ms_per_step"] / km["launches_per_step"] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
+                "traffic": None, "kernel": "fbank400_kernel", "share_of_step": km["ms_per_step"] / prof_ms,
+                "peak_source": pk["src"]}
+    fb = kern.get("fbank400_kernel")
+    stages = {}
+    if fb:
+        gbs = BYTES_FBANK_UTT * B / (fb["ms_per_step"] * 1e-3) / 1e9
+        stages["fbank"] = {"ms_per_step": fb["ms_per_step"], "GB/s": gbs, "frac_hbm": gbs / pk["hbm"]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        v, dt, cores = time_cpu(a.workload, a.cpu_sample, 2, 1)
+        cpu = {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port",
+               "sample": "%d x 10 s utterances per pass, 1 warm-up + 2 timed passes (%.2f s/pass), oracle/ port of the "
+                         "reference's PyTorch-CPU path" % (a.cpu_sample, dt)}
+    if rank == 0:
+        line = {"metric": "audio-sec/sec anonymized (Fbank+%s fwd)" % ("ConvAE" if a.workload == "convae" else "FC-AE"),
+                "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": a.precision if a.workload == "convae" else "fp32", "data": "synthetic",
+                "config": {"workload": "fbank+%s, %d x 10 s @16 kHz utterances per GPU per step from a resident pool of "
+                                       "%d utterances (1 h) per GPU" % (a.workload, B, n_batches * B),
+                           "batch_per_gpu": B, "pool_per_gpu": n_batches * B, "parallelism": "utterance-sharded x%d" % world,
+                           "l2": "inputs cycle through a %.0f MB pool (> 126 MB L2)" % (n_batches * B * N_SAMPLES * 4 / 1e6),
+                           "weights": "random-init seed 8886", "norm": "global stats from the reference's normalizer.ckpt"},
+                "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roof,
+                "cpu_baseline": cpu, "stages": stages, "kernels": kern}
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------- reference arm
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    n = a.cpu_sample * 2
+    # bound the whole run to a few minutes: probe one pass, shrink the sample if needed
+    v, dt, cores = time_cpu(a.workload, n, 1, 1)
+    budget = 150.0
+    while n > 1 and dt * (a.steps + a.warmup) > budget:
+        n = max(1, n // 2)
+        v, dt, cores = time_cpu(a.workload, n, 1, 0)
+    v, dt, cores = time_cpu(a.workload, n, a.steps, a.warmup)
+    T = 1 + N_SAMPLES // 160
+    line = {"impl": "reference",
+            "metric": "audio-sec/sec anonymized (Fbank+%s fwd)" % ("ConvAE" if a.workload == "convae" else "FC-AE"),
+            "value": v, "unit": "audio-s/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
+            "data": "synthetic",
+            "config": {"workload": "fbank+%s, %d x 10 s @16 kHz utterances per step on the host CPU" % (a.workload, n),
+                       "weights": "random-init seed 8886"},
+            "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port",
+                             "sample": "%d x 10 s utterances per step (oracle/ port of the reference's PyTorch-CPU "
+                                       "path: the reference itself is not on the GPU box)" % n},
+            "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -50,6 +50,18 @@ SPANON_API uint64_t spanon_launch_count(void);
 /* Last CUDA error string seen by the library (empty if none). */
 SPANON_API const char* spanon_last_cuda_error(void);
 
+/* Kernel-time profile (bench.py's roofline leg).  Between _begin(stream) and _end() every kernel
+ * this library launches must be enqueued on `stream`; an event is recorded after each launch and
+ * _end() synchronises, attributes each event-to-event interval to the kernel that ended it,
+ * aggregates by kernel name into `entries` and returns the number of names (or a negative status). */
+typedef struct SpanonKernelTime {
+  char name[56];
+  uint64_t launches;
+  double ms_total;
+} SpanonKernelTime;
+SPANON_API int spanon_profile_begin(void* stream);
+SPANON_API int spanon_profile_end(SpanonKernelTime* entries, int max_entries);
+
 /* ------------------------------------------------------------------------- *
  * Fbank: STFT -> power spectrum -> mel projection -> dB (+ per-utterance max)
  * replaces  Fbank.forward            speechbrain/speechbrain/lobes/features.py:126-143

@@ -59,6 +59,10 @@ class ConvAEOpts(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class KernelTime(C.Structure):
+    _fields_ = [("name", C.c_char * 56), ("launches", C.c_uint64), ("ms_total", C.c_double)]
+
+
 PREC_FP32, PREC_BF16 = 0, 1
 
 # name -> (restype, argtypes); must list EVERY function include/spanon.h declares
@@ -67,6 +71,8 @@ SIGNATURES = {
     "spanon_abi_version": (C.c_int, []),
     "spanon_launch_count": (C.c_uint64, []),
     "spanon_last_cuda_error": (C.c_char_p, []),
+    "spanon_profile_begin": (C.c_int, [C.c_void_p]),
+    "spanon_profile_end": (C.c_int, [C.POINTER(KernelTime), C.c_int]),
     "spanon_num_frames": (C.c_int64, [C.c_int64, C.c_int32]),
     "spanon_fbank_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                    C.POINTER(FbankCfg), C.c_void_p]),
@@ -125,6 +131,19 @@ def check(status, what=""):
         msg = l.spanon_strerror(status).decode()
         extra = l.spanon_last_cuda_error().decode() if status == -6 else ""
         raise SpanonError("libspanon %s failed (%d): %s %s" % (what, status, msg, extra))
+
+
+def profile_begin(device=None):
+    check(lib().spanon_profile_begin(stream_ptr(device)), "profile_begin")
+
+
+def profile_end(max_entries=64):
+    """-> {kernel name: (launches, total ms)} since profile_begin (synchronises the stream)."""
+    arr = (KernelTime * max_entries)()
+    n = lib().spanon_profile_end(arr, max_entries)
+    if n < 0:
+        check(n, "profile_end")
+    return {arr[i].name.decode(): (int(arr[i].launches), float(arr[i].ms_total)) for i in range(n)}
 
 
 def ptr(t):

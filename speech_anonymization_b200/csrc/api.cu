@@ -2,6 +2,8 @@
 #include "common.cuh"
 #include <mutex>
 #include <string>
+#include <string.h>
+#include <vector>
 
 namespace spanon {
 std::atomic<uint64_t> g_launch_count{0};
@@ -11,7 +13,64 @@ void set_last_cuda_error(const char* what, cudaError_t e) {
   std::lock_guard<std::mutex> lk(g_err_mu);
   g_last_err = std::string(what) + ": " + cudaGetErrorString(e);
 }
+
+// ---- kernel-time profile: consecutive-event deltas on one stream, aggregated by kernel name ----
+std::atomic<int> g_profile_on{0};
+namespace {
+struct Mark { const char* what; cudaEvent_t ev; };
+std::mutex g_prof_mu;
+std::vector<Mark> g_marks;
+cudaStream_t g_prof_stream = nullptr;
+}  // namespace
+void profile_mark(const char* what) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (!g_profile_on.load()) return;
+  cudaEvent_t ev;
+  if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, g_prof_stream);
+  g_marks.push_back({what, ev});
+}
 }  // namespace spanon
+
+extern "C" int spanon_profile_begin(void* stream) {
+  using namespace spanon;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& m : g_marks) cudaEventDestroy(m.ev);
+  g_marks.clear();
+  g_prof_stream = as_stream(stream);
+  cudaEvent_t ev;
+  SPANON_CUDA_TRY(cudaEventCreate(&ev));
+  SPANON_CUDA_TRY(cudaEventRecord(ev, g_prof_stream));
+  g_marks.push_back({"<begin>", ev});
+  g_profile_on.store(1);
+  return SPANON_OK;
+}
+
+extern "C" int spanon_profile_end(SpanonKernelTime* entries, int max_entries) {
+  using namespace spanon;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_profile_on.store(0);
+  if (g_marks.empty()) return 0;
+  SPANON_CUDA_TRY(cudaEventSynchronize(g_marks.back().ev));
+  int n = 0;
+  for (size_t i = 1; i < g_marks.size(); ++i) {
+    float ms = 0.f;
+    SPANON_CUDA_TRY(cudaEventElapsedTime(&ms, g_marks[i - 1].ev, g_marks[i].ev));
+    int j = 0;
+    for (; j < n; ++j) if (strncmp(entries[j].name, g_marks[i].what, sizeof(entries[j].name) - 1) == 0) break;
+    if (j == n) {
+      if (!entries || n >= max_entries) continue;
+      memset(&entries[n], 0, sizeof(entries[n]));
+      strncpy(entries[n].name, g_marks[i].what, sizeof(entries[n].name) - 1);
+      ++n;
+    }
+    entries[j].launches += 1;
+    entries[j].ms_total += (double)ms;
+  }
+  for (auto& m : g_marks) cudaEventDestroy(m.ev);
+  g_marks.clear();
+  return n;
+}
 
 extern "C" const char* spanon_strerror(int status) {
   switch (status) {

@@ -10,10 +10,14 @@
 namespace spanon {
 
 extern std::atomic<uint64_t> g_launch_count;
+extern std::atomic<int> g_profile_on;
 void set_last_cuda_error(const char* what, cudaError_t e);
+// Kernel-time profile (spanon_profile_begin/_end): an event after every launch on the profiled stream.
+void profile_mark(const char* what);
 
 inline int check_launch(const char* what) {
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  if (g_profile_on.load(std::memory_order_relaxed)) profile_mark(what);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_cuda_error(what, e);

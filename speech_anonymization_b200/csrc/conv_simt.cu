@@ -194,7 +194,7 @@ int launch_one(const TapGemmParams& p, cudaStream_t st) {
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)ceil_div(p.rows_out, M_T), (unsigned)p.B);
   kern<<<grid, NTHR, smem, st>>>(p, halo_lo, slab_rows);
-  return check_launch("tapgemm_simt_kernel");
+  return check_launch(p.tag ? p.tag : "tapgemm_simt_kernel");
 }
 
 }  // namespace

@@ -255,6 +255,8 @@ struct LayerSpec {
 };
 
 enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, N_LAYERS };
+const char* const kLayerTag[N_LAYERS] = {"tapgemm:enc2", "tapgemm:enc5", "tapgemm:enc8", "tapgemm:enc11", "tapgemm:tdnn0", "tapgemm:tdnn3",
+                                        "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8"};
 
 // tc = this layer runs on the tcgen05 kernel (bf16 UMMA-packed weights, decoder.8 padded to N = 16)
 LayerSpec make_spec(int id, bool tc) {
@@ -381,6 +383,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.stats = io.out_stats >= 0 ? c.ws.stats[io.out_stats] : nullptr;
   p.out_mode = io.out_mode;
   p.B = nb;
+  p.tag = kLayerTag[id];
   if (on_tc) return launch_tapgemm_tc(p, c.n_sm, c.st);
   if (c.tc) return launch_tapgemm_simt<__nv_bfloat16>(p, c.st);
   return launch_tapgemm_simt<float>(p, c.st);

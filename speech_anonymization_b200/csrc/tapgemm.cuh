@@ -46,6 +46,7 @@ struct TapGemmParams {
   double* stats;       // [B][cout_mod][2] or null
   int out_mode;
   int B;
+  const char* tag;     // profile name of this launch ("tapgemm:<layer>")
 };
 
 // fp32 CUDA-core family (conv_fp32.cu).  Packed weights: fp32 [ntaps][cin_v][cout_v].
