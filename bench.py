@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--workload", default="convae", choices=["convae", "fcae"])
     ap.add_argument("--batch", type=int, default=60)
     ap.add_argument("--pool", type=int, default=360)
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=4, help="utterances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

@@ -174,11 +174,13 @@ typedef struct SpanonConvAEWeights {
   SpanonBatchNorm cls_bn[2];
 } SpanonConvAEWeights;
 
-enum { SPANON_PREC_FP32 = 0, SPANON_PREC_BF16 = 1 };
+enum { SPANON_PREC_FP32 = 0, SPANON_PREC_FP16 = 1 };
 
 typedef struct SpanonConvAEOpts {
   int32_t precision;      /* SPANON_PREC_FP32: fp32 activations + CUDA-core FMA (<=1e-4 parity);
-                             SPANON_PREC_BF16: bf16 activations + tcgen05 tensor cores (<=1e-2) */
+                             SPANON_PREC_FP16: fp16 activations/operands + tcgen05 tensor cores with fp32
+                             accumulation (<=1e-2 parity bar of the 16-bit mode; bf16 operands cannot hold
+                             it on this network, see DESIGN.md "Precision") */
   int32_t chunk_utts;     /* utterances per L2-resident chunk; 0 = library default             */
   int32_t skip_classifier;/* 1 = do not run the sex classifier (logp untouched)                */
   int32_t reserved;

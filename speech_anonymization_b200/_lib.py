@@ -63,7 +63,7 @@ class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 56), ("launches", C.c_uint64), ("ms_total", C.c_double)]
 
 
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_FP16 = 0, 1
 
 # name -> (restype, argtypes); must list EVERY function include/spanon.h declares
 SIGNATURES = {

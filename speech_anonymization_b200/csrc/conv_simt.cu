@@ -22,15 +22,15 @@ template <> struct Vec4<float> {
   static __device__ __forceinline__ float4 load(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
   static __device__ __forceinline__ void store(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 };
-template <> struct Vec4<__nv_bfloat16> {
-  static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
+template <> struct Vec4<__half> {
+  static __device__ __forceinline__ float4 load(const __half* p) {
     const uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
-    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&r.x);
-    const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&r.y);
-    return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&r.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&r.y));
+    return make_float4(a.x, a.y, b.x, b.y);
   }
-  static __device__ __forceinline__ void store(__nv_bfloat16* p, float4 v) {
-    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  static __device__ __forceinline__ void store(__half* p, float4 v) {
+    __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
     uint2 r;
     r.x = *reinterpret_cast<uint32_t*>(&a);
     r.y = *reinterpret_cast<uint32_t*>(&b);
@@ -210,6 +210,6 @@ int launch_tapgemm_simt(const TapGemmParams& p, cudaStream_t st) {
   }
 }
 template int launch_tapgemm_simt<float>(const TapGemmParams&, cudaStream_t);
-template int launch_tapgemm_simt<__nv_bfloat16>(const TapGemmParams&, cudaStream_t);
+template int launch_tapgemm_simt<__half>(const TapGemmParams&, cudaStream_t);
 
 }  // namespace spanon

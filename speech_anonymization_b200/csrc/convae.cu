@@ -4,7 +4,7 @@
 // with a single channel (:181,188) and runs ten 1-D convolutions over it; the adversarial
 // TDNN sex classifier (:30-69) reads the 128-channel bottleneck.  Here:
 //   encoder.0 (1->32, k15)            first_layer_kernel   (CUDA cores; K = 15 is too thin for UMMA)
-//   encoder.2..11, decoder.0..8, tdnn tap GEMMs            (tapgemm.cuh; tcgen05 in bf16 mode)
+//   encoder.2..11, decoder.0..8, tdnn tap GEMMs            (tapgemm.cuh; tcgen05 in fp16 mode)
 //   InstanceNorm1d                    statistics in the producer's epilogue, affine + SiLU in
 //                                     the consumer's operand load (instnorm_finalize_kernel
 //                                     turns the sums into per-(b,c) scale/shift)
@@ -16,6 +16,7 @@
 #include "tapgemm.cuh"
 #include <algorithm>
 #include <math.h>
+#include <stdlib.h>
 
 namespace spanon {
 int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
@@ -56,8 +57,8 @@ __global__ void pack_f32_kernel(const float* __restrict__ w, float* __restrict__
   }
 }
 
-// bf16 UMMA K-major core-matrix layout [ntaps][cin_v/8][cout_v][8]
-__global__ void pack_umma_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int mode, int cin,
+// fp16 UMMA K-major core-matrix layout [ntaps][cin_v/8][cout_v][8]
+__global__ void pack_umma_kernel(const float* __restrict__ w, __half* __restrict__ dst, int mode, int cin,
                                  int cout, int k, int ntaps, int cin_v, int cout_v) {
   const int64_t n = (int64_t)ntaps * cin_v * cout_v;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -65,7 +66,7 @@ __global__ void pack_umma_kernel(const float* __restrict__ w, __nv_bfloat16* __r
     const int cov = (int)((i / 8) % cout_v);
     const int kc = (int)((i / (8 * (int64_t)cout_v)) % (cin_v / 8));
     const int tap = (int)(i / ((int64_t)cout_v * cin_v));
-    dst[i] = __float2bfloat16_rn(packed_src(w, mode, cin, cout, k, tap, kc * 8 + e, cov));
+    dst[i] = __float2half_rn(packed_src(w, mode, cin, cout, k, tap, kc * 8 + e, cov));
   }
 }
 
@@ -158,10 +159,10 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
       uint4* o4 = reinterpret_cast<uint4*>(o);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        __nv_bfloat162 h0 = __floats2bfloat162_rn(acc[8 * q + 0], acc[8 * q + 1]);
-        __nv_bfloat162 h1 = __floats2bfloat162_rn(acc[8 * q + 2], acc[8 * q + 3]);
-        __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[8 * q + 4], acc[8 * q + 5]);
-        __nv_bfloat162 h3 = __floats2bfloat162_rn(acc[8 * q + 6], acc[8 * q + 7]);
+        __half2 h0 = __floats2half2_rn(acc[8 * q + 0], acc[8 * q + 1]);
+        __half2 h1 = __floats2half2_rn(acc[8 * q + 2], acc[8 * q + 3]);
+        __half2 h2 = __floats2half2_rn(acc[8 * q + 4], acc[8 * q + 5]);
+        __half2 h3 = __floats2half2_rn(acc[8 * q + 6], acc[8 * q + 7]);
         uint4 r;
         r.x = *reinterpret_cast<uint32_t*>(&h0); r.y = *reinterpret_cast<uint32_t*>(&h1);
         r.z = *reinterpret_cast<uint32_t*>(&h2); r.w = *reinterpret_cast<uint32_t*>(&h3);
@@ -258,7 +259,7 @@ enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_D
 const char* const kLayerTag[N_LAYERS] = {"tapgemm:enc2", "tapgemm:enc5", "tapgemm:enc8", "tapgemm:enc11", "tapgemm:tdnn0", "tapgemm:tdnn3",
                                         "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8"};
 
-// tc = this layer runs on the tcgen05 kernel (bf16 UMMA-packed weights, decoder.8 padded to N = 16)
+// tc = this layer runs on the tcgen05 kernel (fp16 UMMA-packed weights)
 LayerSpec make_spec(int id, bool tc) {
   LayerSpec s{};
   auto taps = [&](std::initializer_list<int> sh) { s.ntaps = 0; for (int v : sh) s.shift[s.ntaps++] = v; };
@@ -326,13 +327,14 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
 struct Ctx {
   const SpanonConvAEWeights* w;
   Workspace ws;
-  bool tc;       // bf16 activations (+ tcgen05 where supported)
+  bool tc;       // fp16 activations (+ tcgen05 where supported)
+  bool tc_off;   // $SPANON_DISABLE_TC: run the fp16 mode on the CUDA-core kernel (cross-check)
   int n_sm;
   int64_t L;
   cudaStream_t st;
 };
 
-bool layer_on_tc(const Ctx& c, int id) { return c.tc && tapgemm_tc_available(); (void)id; }
+bool layer_on_tc(const Ctx& c, int id) { return c.tc && !c.tc_off && id != L_DEC8; }
 
 int pack_layer(const Ctx& c, int id, const float* w) {
   const bool on_tc = layer_on_tc(c, id);
@@ -340,7 +342,7 @@ int pack_layer(const Ctx& c, int id, const float* w) {
   const int64_t n = (int64_t)s.ntaps * s.cin_v * s.cout_v;
   const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n, 256), 1024);
   if (on_tc)
-    pack_umma_kernel<<<grid, 256, 0, c.st>>>(w, (__nv_bfloat16*)c.ws.packed[id], s.mode, s.cin, s.cout, s.k, s.ntaps,
+    pack_umma_kernel<<<grid, 256, 0, c.st>>>(w, (__half*)c.ws.packed[id], s.mode, s.cin, s.cout, s.k, s.ntaps,
                                              s.cin_v, s.cout_v);
   else
     pack_f32_kernel<<<grid, 256, 0, c.st>>>(w, (float*)c.ws.packed[id], s.mode, s.cin, s.cout, s.k, s.ntaps, s.cin_v,
@@ -373,7 +375,13 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.in_bstride = (int64_t)p.rows_in * s.cin_v;
   p.out_bstride = io.out_mode == OUT_CH0_F32 ? (int64_t)p.rows_out : (int64_t)p.rows_out * s.cout_v;
   p.ntaps = s.ntaps;
-  for (int t = 0; t < s.ntaps; ++t) p.shift[t] = s.shift[t];
+  for (int t = 0; t < s.ntaps; ++t) {
+    p.shift[t] = s.shift[t];
+    p.tap_kmax[t] = s.cin_v;
+    p.tap_nmax[t] = s.cout_v;
+  }
+  if (s.mode == PACK_CONV_S2) p.tap_kmax[s.ntaps - 1] = s.cin;   // tap (2*tap+1) = 5 does not exist
+  if (s.mode == PACK_CONVT_S2) p.tap_nmax[0] = s.cout;            // shift -1 only feeds the even phase
   p.w = c.ws.packed[id];
   if (io.in_norm >= 0) { p.t1_scale = c.ws.in_scale[io.in_norm]; p.t1_shift = c.ws.in_shift[io.in_norm]; p.silu = 1; }
   if (io.t2_bn >= 0) { p.t2_scale = c.ws.bn_scale[io.t2_bn]; p.t2_shift = c.ws.bn_shift[io.t2_bn]; }
@@ -385,7 +393,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.B = nb;
   p.tag = kLayerTag[id];
   if (on_tc) return launch_tapgemm_tc(p, c.n_sm, c.st);
-  if (c.tc) return launch_tapgemm_simt<__nv_bfloat16>(p, c.st);
+  if (c.tc) return launch_tapgemm_simt<__half>(p, c.st);
   return launch_tapgemm_simt<float>(p, c.st);
 }
 
@@ -402,9 +410,9 @@ int finalize_in(const Ctx& c, int idx, const float* gamma, const float* beta, in
 using namespace spanon;
 
 static int resolve_opts(const SpanonConvAEOpts* o, int64_t L, bool* tc, int* chunk) {
-  const int prec = o ? o->precision : SPANON_PREC_BF16;
-  if (prec != SPANON_PREC_FP32 && prec != SPANON_PREC_BF16) return SPANON_ERR_UNSUPPORTED;
-  *tc = prec == SPANON_PREC_BF16;
+  const int prec = o ? o->precision : SPANON_PREC_FP16;
+  if (prec != SPANON_PREC_FP32 && prec != SPANON_PREC_FP16) return SPANON_ERR_UNSUPPORTED;
+  *tc = prec == SPANON_PREC_FP16;
   int ch = o ? o->chunk_utts : 0;
   if (ch <= 0) ch = default_chunk(L, *tc ? 2 : 4);
   *chunk = ch;
@@ -448,6 +456,10 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   carve(c.ws, base, chunk, L, c.tc, esize);
   c.w = w; c.L = L; c.st = as_stream(stream);
   {
+    const char* e = getenv("SPANON_DISABLE_TC");
+    c.tc_off = e && e[0] == '1';
+  }
+  {
     int dev = 0;
     SPANON_CUDA_TRY(cudaGetDevice(&dev));
     SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
@@ -487,9 +499,9 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
       const int32_t* um = utt_max ? utt_max + b0 : nullptr;
       if (c.tc)
-        first_layer_kernel<__nv_bfloat16, true><<<grid, FL_NT, 0, c.st>>>(
+        first_layer_kernel<__half, true><<<grid, FL_NT, 0, c.st>>>(
             src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um, top_db, w->enc_w[0], w->enc_b[0],
-            (__nv_bfloat16*)X[0], L * 32);
+            (__half*)X[0], L * 32);
       else
         first_layer_kernel<float, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
                                                                    norm_mean, norm_std, um, top_db, w->enc_w[0],

@@ -17,6 +17,7 @@
 // InstanceNorm (fp64 atomics), optional affine (folded eval-mode BatchNorm), store.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace spanon {
 
@@ -36,6 +37,8 @@ struct TapGemmParams {
   int cin_v, cout_v, cin_mod, cout_mod;
   int ntaps;
   int shift[MAX_TAPS];
+  int tap_kmax[MAX_TAPS];  // input channels (of cin_v) with non-zero weights for this tap (stride-2 view: last tap half)
+  int tap_nmax[MAX_TAPS];  // output columns (of cout_v) with non-zero weights (transposed conv: first tap half)
   const void* w;       // packed weights (layout depends on the kernel family)
   const float* t1_scale; const float* t1_shift;  // [B][cin_mod] or null
   int silu;
@@ -53,9 +56,9 @@ struct TapGemmParams {
 template <typename TAct>
 int launch_tapgemm_simt(const TapGemmParams& p, cudaStream_t st);
 
-// tcgen05 family (conv_tc.cu).  bf16 activations; packed weights: bf16 UMMA core-matrix
+// tcgen05 family (conv_tc.cu).  fp16 activations; packed weights: fp16 UMMA core-matrix
 // layout [ntaps][cin_v/8][cout_v][8].
 int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st);
-bool tapgemm_tc_available();  // false until SPANON_DISABLE_TC is unset and the kernel is built in
+bool tapgemm_tc_supported(const TapGemmParams& p);
 
 }  // namespace spanon

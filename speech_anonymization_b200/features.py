@@ -166,7 +166,7 @@ class Fbank(torch.nn.Module):
         out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=wav.device)
         utt_max = torch.empty((max(B, 1),), dtype=torch.int32, device=wav.device)
         with torch.cuda.device(wav.device):
-            _lib.check(_lib.lib().spanon_fbank_f32(_lib.ptr(wav), B, n, wav.stride(0) if B > 0 else n, _lib.ptr(out),
+            _lib.check(_lib.lib().spanon_fbank_f32(_lib.ptr(wav), B, n, wav.stride(0) if B > 1 else n, _lib.ptr(out),
                                                    _lib.ptr(utt_max), C.byref(st["cfg"]),
                                                    _lib.stream_ptr(wav.device)), "fbank_f32")
         return out, utt_max

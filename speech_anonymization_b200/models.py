@@ -88,9 +88,9 @@ def _forward_only_guard(module, inp):
 
 
 def _precision_from_env():
-    v = os.environ.get("SPANON_PRECISION", "bf16").lower()
-    if v not in ("bf16", "fp32"):
-        raise ValueError("SPANON_PRECISION must be bf16 or fp32")
+    v = os.environ.get("SPANON_PRECISION", "fp16").lower()
+    if v not in ("fp16", "fp32"):
+        raise ValueError("SPANON_PRECISION must be fp16 or fp32")
     return v
 
 
@@ -120,8 +120,8 @@ class ConvAutoencoder(nn.Module):
     """Drop-in for models.ConvAutoEncoder.ConvAutoencoder (models/ConvAutoEncoder.py:136-200).
 
     forward(input [B,T,F]) -> (reconstruction [B,T,F], sex log-probs [B,2]).
-    `precision`: "bf16" (tcgen05 tensor cores, <= 1e-2 rel.) or "fp32" (<= 1e-4 rel.);
-    default from $SPANON_PRECISION, else bf16.
+    `precision`: "fp16" (fp16 operands on the tcgen05 tensor cores, fp32 accumulation; the 16-bit mode
+    with the <= 1e-2 parity bar) or "fp32" (<= 1e-4 rel.); default from $SPANON_PRECISION, else fp16.
     """
 
     def __init__(self):
@@ -173,7 +173,7 @@ class ConvAutoencoder(nn.Module):
         return w
 
     def opts(self, skip_classifier=False):
-        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_BF16,
+        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16,
                                int(self.chunk_utts), int(skip_classifier), 0)
 
     def forward(self, input, pool_noise=None, fused_norm=None):

@@ -43,7 +43,7 @@ def test_c_abi_argument_validation_without_device():
     assert L.spanon_fbank_f32(None, 0, 10, 10, None, None, C.byref(cfg), None) == 0  # empty batch
     assert L.spanon_fbank_f32(None, 1, 10, 10, None, None, C.byref(cfg), None) == -2
     assert L.spanon_norm_apply(None, None, None, None, 3, None, 80.0, 1, 4, 4, 80, None) == -1
-    opts = _lib.ConvAEOpts(_lib.PREC_BF16, 0, 0, 0)
+    opts = _lib.ConvAEOpts(_lib.PREC_FP16, 0, 0, 0)
     assert L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts)) > 8 * 80640 * 32 * 2
     assert L.spanon_convae_workspace_bytes(0, 1008, 80, C.byref(opts)) == 0
     assert L.spanon_convae_fwd(None, None, None, None, None, None, 0.0, 0, None, None, None, 0, 1, 36, 80,
