@@ -2,18 +2,18 @@
 //
 // One persistent CTA per SM walks (utterance, 128-row tile) pairs of one layer:
 //
-//   warps 5..12  PRODUCERS   global fp16 rows -> registers -> (InstanceNorm affine, SiLU, folded BN of the
+//   warps 9..16  PRODUCERS   global fp16 rows -> registers -> (InstanceNorm affine, SiLU, folded BN of the
 //                            producer layer) -> fp16 -> st.shared in the UMMA no-swizzle K-major layout
 //                            [8-channel chunk][slab row][8 ch]; a stage holds 32 input channels of the
 //                            (128 + halo)-row slab.  Rows outside the utterance are written as zeros
 //                            (= the conv's zero padding of the already activated tensor).
-//   warp 4       MMA ISSUER  one thread: for every stage, tap and K=16 step one tcgen05.mma
+//   warp 8       MMA ISSUER  one thread: for every stage, tap and K=16 step one tcgen05.mma
 //                            (M=128, N=cout_v, kind::f16, fp32 accumulate in TMEM).  A conv tap is the SAME
 //                            slab read at a row offset: with rows at a uniform 16-byte pitch (SBO = 128 B)
 //                            a shift by s rows is start_address + 16*s, so the halo is loaded once and
 //                            every tap reuses it.  The layer's whole packed weight tensor is resident in
 //                            shared memory (one cp.async.bulk per CTA).
-//   warps 0..3   EPILOGUE    tcgen05.ld of the accumulator (double-buffered in TMEM, so the next tile's
+//   warps 0..7   EPILOGUE    tcgen05.ld of the accumulator (double-buffered in TMEM, so the next tile's
 //                            MMAs overlap), + bias, ReLU, per-(utterance, channel) sum / sum of squares for
 //                            the next InstanceNorm (butterfly transpose-reduce over the 32 rows of a warp,
 //                            fp64 atomics), folded BatchNorm, fp16 store.
@@ -25,18 +25,21 @@
 #include "tapgemm.cuh"
 #include <cuda_fp16.h>
 #include <algorithm>
+#include <stdlib.h>
+#include <vector>
 
 namespace spanon {
 namespace {
 
 constexpr int TC_M = 128;                 // rows per tile = UMMA M
-constexpr int TC_EPI_WARPS = 4;
+constexpr int TC_EPI_WARPS = 8;           // two warps per TMEM lane quarter, each takes half of the columns
 constexpr int TC_PROD_WARPS = 8;
 constexpr int TC_THREADS = (TC_EPI_WARPS + 1 + TC_PROD_WARPS) * 32;
 constexpr int TC_PROD_THREADS = TC_PROD_WARPS * 32;
 constexpr int TC_STAGE_CH = 32;           // input channels per A stage (two K=16 MMA steps)
 constexpr int TC_MAX_STAGES = 8;
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
+constexpr int TRACE_N = 128;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -140,8 +143,8 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.w_bytes = (uint32_t)ntaps * cin_v * cout_v * 2u;
   L.w = 0;
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
-  L.red = L.epi + 3u * cout_v * 4u;                   // [4 warps][cout_v][2] fp32
-  L.bars = L.red + (uint32_t)TC_EPI_WARPS * cout_v * 2u * 4u;
+  L.red = L.epi + 3u * cout_v * 4u;                   // [4 lane quarters][cout_v][2] fp32
+  L.bars = L.red + 4u * cout_v * 2u * 4u;
   L.a = (L.bars + 256u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
@@ -150,10 +153,11 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   return L;
 }
 
-__device__ __forceinline__ float silu_tanh(float x) {
-  float h = 0.5f * x, t;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
-  return fmaf(h, t, h);
+// SiLU of two values given hh = x/2 as packed fp16:  x*sigmoid(x) = hh + hh*tanh(hh)  (one MUFU per pair)
+__device__ __forceinline__ __half2 silu_from_half(__half2 hh) {
+  uint32_t t, in = *reinterpret_cast<uint32_t*>(&hh);
+  asm("tanh.approx.f16x2 %0, %1;" : "=r"(t) : "r"(in));
+  return __hfma2(hh, *reinterpret_cast<__half2*>(&t), hh);
 }
 
 template <int COUT_V>
@@ -210,107 +214,147 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     const __half* in_base = reinterpret_cast<const __half*>(p.in);
     const bool has_t1 = p.t1_scale != nullptr, has_t2 = p.t2_scale != nullptr, do_silu = p.silu != 0;
     const bool ident = !has_t1 && !has_t2 && !do_silu;
-    uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const float pre = do_silu ? 0.5f : 1.f;             // SiLU works on x/2: fold the 1/2 into the affine
+    const int n_my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const uint32_t n_iter = (uint32_t)(n_my_tiles * n_stage_tile);
+    constexpr int NQ = 3, RSTEP = TC_PROD_THREADS / 4;
+    uint4 raw[NQ], nxt[NQ];
+    uint32_t inb = 0, inb_nxt = 0;
+    auto issue_loads = [&](uint32_t g, uint4* dst, uint32_t& mask) {
+      const int k = (int)(g / (uint32_t)n_stage_tile), s = (int)(g - (uint32_t)k * n_stage_tile);
+      const int tile = (int)blockIdx.x + k * (int)gridDim.x;
       const int b = tile / tiles_per_utt;
       const int m0 = (tile - b * tiles_per_utt) * TC_M;
-      const __half* in = in_base + (int64_t)b * p.in_bstride;
-      for (int s = 0; s < n_stage_tile; ++s, ++it) {
-        const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
-        const int ch = s * TC_STAGE_CH + kcl * 8;
-        // issue the global loads before waiting for the slot
-        uint4 raw[3];
-        bool inb[3];
+      const __half* src = in_base + (int64_t)b * p.in_bstride + s * TC_STAGE_CH + kcl * 8;
+      mask = 0;
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-          const int r = r0 + q * (TC_PROD_THREADS / 4);
-          const int grow = m0 - halo_lo + r;
-          inb[q] = r < slab_used && grow >= 0 && grow < p.rows_in;
-          raw[q] = make_uint4(0u, 0u, 0u, 0u);
-          if (inb[q]) raw[q] = __ldg(reinterpret_cast<const uint4*>(in + (int64_t)grow * p.cin_v + ch));
+      for (int q = 0; q < NQ; ++q) {
+        const int r = r0 + q * RSTEP;
+        const int grow = m0 - halo_lo + r;
+        dst[q] = make_uint4(0u, 0u, 0u, 0u);
+        if (r < slab_used && grow >= 0 && grow < p.rows_in) {
+          dst[q] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)grow * p.cin_v));
+          mask |= 1u << q;
         }
-        float s1[8], h1[8], s2[8], h2[8];
-        if (!ident) {
-          const int cm = ch % p.cin_mod;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            s1[j] = has_t1 ? __ldg(p.t1_scale + (int64_t)b * p.cin_mod + cm + j) : 1.f;
-            h1[j] = has_t1 ? __ldg(p.t1_shift + (int64_t)b * p.cin_mod + cm + j) : 0.f;
-            s2[j] = has_t2 ? __ldg(p.t2_scale + cm + j) : 1.f;
-            h2[j] = has_t2 ? __ldg(p.t2_shift + cm + j) : 0.f;
-          }
-        }
-        mbar_wait(BAR(8 + stage), (use & 1u) ^ 1u);
-        unsigned char* dst = smem + L.a + stage * L.stage_bytes + (uint32_t)kcl * L.lbo_a;
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-          const int r = r0 + q * (TC_PROD_THREADS / 4);
-          if (r >= slab_used) continue;
-          uint4 v = raw[q];
-          if (!ident && inb[q]) {
-            __half2* hv = reinterpret_cast<__half2*>(&v);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float2 f = __half22float2(hv[j]);
-              f.x = fmaf(f.x, s1[2 * j], h1[2 * j]);
-              f.y = fmaf(f.y, s1[2 * j + 1], h1[2 * j + 1]);
-              if (do_silu) { f.x = silu_tanh(f.x); f.y = silu_tanh(f.y); }
-              if (has_t2) {
-                f.x = fmaf(f.x, s2[2 * j], h2[2 * j]);
-                f.y = fmaf(f.y, s2[2 * j + 1], h2[2 * j + 1]);
-              }
-              hv[j] = __floats2half2_rn(f.x, f.y);
-            }
-          }
-          *reinterpret_cast<uint4*>(dst + (uint32_t)r * 16u) = v;
-        }
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(BAR(stage));
       }
+    };
+    if (n_iter > 0) issue_loads(0, nxt, inb_nxt);
+    for (uint32_t it = 0; it < n_iter; ++it) {
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) raw[q] = nxt[q];
+      inb = inb_nxt;
+      if (it + 1 < n_iter) issue_loads(it + 1, nxt, inb_nxt);   // next stage's rows are in flight during this one
+      const int k = (int)(it / (uint32_t)n_stage_tile), s = (int)(it - (uint32_t)k * n_stage_tile);
+      const int b = ((int)blockIdx.x + k * (int)gridDim.x) / tiles_per_utt;
+      const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
+      float s1[8], h1[8];
+      __half2 s2[4], h2[4];
+      if (!ident) {
+        const int cm = (s * TC_STAGE_CH + kcl * 8) % p.cin_mod;
+        if (has_t1) {
+          const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.cin_mod + cm);
+          const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.cin_mod + cm);
+          const float4 a0 = __ldg(sp), a1 = __ldg(sp + 1), c0 = __ldg(hp), c1 = __ldg(hp + 1);
+          s1[0] = a0.x; s1[1] = a0.y; s1[2] = a0.z; s1[3] = a0.w; s1[4] = a1.x; s1[5] = a1.y; s1[6] = a1.z; s1[7] = a1.w;
+          h1[0] = c0.x; h1[1] = c0.y; h1[2] = c0.z; h1[3] = c0.w; h1[4] = c1.x; h1[5] = c1.y; h1[6] = c1.z; h1[7] = c1.w;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { s1[j] = 1.f; h1[j] = 0.f; }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s1[j] *= pre; h1[j] *= pre; }
+        if (has_t2) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
+            h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
+          }
+        }
+      }
+      mbar_wait(BAR(8 + stage), (use & 1u) ^ 1u);
+      unsigned char* dst = smem + L.a + stage * L.stage_bytes + (uint32_t)kcl * L.lbo_a;
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const int r = r0 + q * RSTEP;
+        if (r >= slab_used) continue;
+        uint4 v = raw[q];
+        if (!ident && ((inb >> q) & 1u)) {
+          __half2* hv = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float2 f = __half22float2(hv[j]);
+            f.x = fmaf(f.x, s1[2 * j], h1[2 * j]);             // InstanceNorm affine in fp32 (x/2 if SiLU follows)
+            f.y = fmaf(f.y, s1[2 * j + 1], h1[2 * j + 1]);
+            __half2 y = __floats2half2_rn(f.x, f.y);
+            if (do_silu) y = silu_from_half(y);
+            if (has_t2) y = __hfma2(y, s2[j], h2[j]);          // folded eval-mode BatchNorm
+            hv[j] = y;
+          }
+        }
+        *reinterpret_cast<uint4*>(dst + (uint32_t)r * 16u) = v;
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(BAR(stage));
+      if (p.trace && ptid == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 0) * TRACE_N + it] = clock64();
     }
   } else if (warp == TC_EPI_WARPS) {
     // =========================== MMA ISSUER ===========================
+    // One thread issues; its instruction stream is the critical path (a lone thread retires a dependent
+    // instruction every ~4 cycles), so the per-MMA work is a couple of adds on the descriptors' low words:
+    //   A: + dil (16 B rows) per tap, + 2*LBO per K step;   B: + one [cin_v/8][cout_v] slice per tap.
     if (lane == 0) {
       mbar_wait(BAR(20), 0);
-      const uint32_t lbo_b = (uint32_t)COUT_V * 16u;
-      const int kchunks = p.cin_v / 8;
+      const uint32_t desc_hi = (uint32_t)(umma_desc(0, 0) >> 32);
+      const uint32_t a_lo_const = (uint32_t)umma_desc(0, L.lbo_a);
+      const uint32_t b_lo_const = (uint32_t)umma_desc(s_base + L.w, (uint32_t)COUT_V * 16u);
+      const uint32_t a_kstep = 2u * (L.lbo_a >> 4);              // two 8-channel chunks per K = 16
+      const uint32_t b_kstep = 2u * (uint32_t)COUT_V;            // 16 B units
+      const uint32_t b_tap = (uint32_t)(p.cin_v / 8) * COUT_V;
+      const uint32_t b_stage = (uint32_t)(TC_STAGE_CH / 8) * COUT_V;
+      const uint32_t dil = (uint32_t)p.tap_step;
+      const uint32_t idesc_full = umma_idesc(COUT_V), idesc_tap0 = umma_idesc(p.tap_nmax[0]);
+      const int s_short = p.tap_kmax[p.ntaps - 1] / TC_STAGE_CH;  // stages >= s_short skip the last tap
       uint32_t it = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t buf = tcount & 1u;
         mbar_wait(BAR(18 + buf), ((tcount >> 1) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * (uint32_t)COUT_V;
-        uint32_t accumulate = 0;
         for (int s = 0; s < n_stage_tile; ++s, ++it) {
           const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
+          uint32_t a_lo = a_lo_const + ((s_base + L.a + stage * L.stage_bytes) >> 4);
+          uint32_t b_lo = b_lo_const + (uint32_t)s * b_stage;
+          const int nt = s >= s_short ? p.ntaps - 1 : p.ntaps;
           mbar_wait(BAR(stage), use & 1u);
           tc_fence_after();
-          const uint32_t a_stage = s_base + L.a + stage * L.stage_bytes;
-          for (int tap = 0; tap < p.ntaps; ++tap) {
-            const uint32_t a_tap = a_stage + (uint32_t)(p.shift[tap] + halo_lo) * 16u;
-#pragma unroll
-            for (int j = 0; j < TC_STAGE_CH / 16; ++j) {
-              const int kc = s * (TC_STAGE_CH / 8) + 2 * j;       // first 8-channel chunk of this K=16 step
-              if (kc * 8 >= p.tap_kmax[tap]) continue;            // all-zero weight slice (stride-2 view)
-              const int n = accumulate ? p.tap_nmax[tap] : COUT_V; // first MMA must initialise every column
-              const uint64_t adesc = umma_desc(a_tap + (uint32_t)(2 * j) * L.lbo_a, L.lbo_a);
-              const uint64_t bdesc =
-                  umma_desc(s_base + L.w + (uint32_t)((tap * kchunks + kc) * COUT_V) * 16u, lbo_b);
-              umma_f16(d_tmem, adesc, bdesc, umma_idesc(n), accumulate);
-              accumulate = 1;
-            }
+          // tap 0 (its first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
+          umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
+                   s == 0 ? idesc_full : idesc_tap0, s != 0);
+          umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep), ((uint64_t)desc_hi << 32) | (b_lo + b_kstep),
+                   idesc_tap0, 1u);
+#pragma unroll 1
+          for (int tap = 1; tap < nt; ++tap) {
+            a_lo += dil;
+            b_lo += b_tap;
+            umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc_full, 1u);
+            umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep),
+                     ((uint64_t)desc_hi << 32) | (b_lo + b_kstep), idesc_full, 1u);
           }
           tc_commit(BAR(8 + stage));        // slot free once these MMAs have read it
+          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 1) * TRACE_N + it] = clock64();
         }
         tc_commit(BAR(16 + buf));           // accumulator complete
       }
     }
   } else {
     // =========================== EPILOGUE ===========================
+    // warp w: TMEM lanes (rows) 32*(w%4).., columns [(w/4)*COUT_V/2, +COUT_V/2)
     const float* ec = reinterpret_cast<const float*>(smem + L.epi);
     float* red = reinterpret_cast<float*>(smem + L.red);
-    const int erow = warp * 32 + lane;
+    const int quarter = warp & 3, chalf = warp >> 2;
+    const int erow = quarter * 32 + lane;
+    constexpr int CPW = COUT_V / 2;   // columns per warp
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const int b = tile / tiles_per_utt;
@@ -319,11 +363,12 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       const uint32_t buf = tcount & 1u;
       mbar_wait(BAR(16 + buf), (tcount >> 1) & 1u);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + buf * (uint32_t)COUT_V + ((uint32_t)(warp * 32) << 16);
+      if (p.trace && threadIdx.x == 0 && 2 * tcount < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 2) * TRACE_N + 2 * tcount] = clock64();
+      const uint32_t taddr = tmem_base + buf * (uint32_t)COUT_V + ((uint32_t)(quarter * 32) << 16);
       __half* out_h = reinterpret_cast<__half*>(p.out) + (int64_t)b * p.out_bstride + (int64_t)m * COUT_V;
       float* out_f = reinterpret_cast<float*>(p.out) + (int64_t)b * p.out_bstride;
-#pragma unroll 1
-      for (int cb = 0; cb < COUT_V; cb += 32) {
+#pragma unroll
+      for (int cb = chalf * CPW; cb < (chalf + 1) * CPW; cb += 32) {
         float v[32];
         tmem_ld32(taddr + (uint32_t)cb, v);
 #pragma unroll
@@ -341,8 +386,12 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int c = 8 * q + 2 * j;
-                oh[j] = __floats2half2_rn(fmaf(v[c], ec[COUT_V + cb + c], ec[2 * COUT_V + cb + c]),
-                                          fmaf(v[c + 1], ec[COUT_V + cb + c + 1], ec[2 * COUT_V + cb + c + 1]));
+                float y0 = v[c], y1 = v[c + 1];
+                if (p.e_scale) {
+                  y0 = fmaf(y0, ec[COUT_V + cb + c], ec[2 * COUT_V + cb + c]);
+                  y1 = fmaf(y1, ec[COUT_V + cb + c + 1], ec[2 * COUT_V + cb + c + 1]);
+                }
+                oh[j] = __floats2half2_rn(y0, y1);
               }
               *reinterpret_cast<uint4*>(out_h + cb + 8 * q) = o;
             }
@@ -363,8 +412,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           }
           const float s_sum = warp_transpose_sum(v, lane);
           const float s_sq = warp_transpose_sum(q, lane);
-          red[(warp * COUT_V + cb + lane) * 2 + 0] = s_sum;
-          red[(warp * COUT_V + cb + lane) * 2 + 1] = s_sq;
+          red[(quarter * COUT_V + cb + lane) * 2 + 0] = s_sum;
+          red[(quarter * COUT_V + cb + lane) * 2 + 1] = s_sq;
         }
       }
       tc_fence_before();
@@ -375,7 +424,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_WARPS * 32) {
           float s = 0.f, q = 0.f;
 #pragma unroll
-          for (int w = 0; w < TC_EPI_WARPS; ++w) {
+          for (int w = 0; w < 4; ++w) {
             s += red[(w * COUT_V + c) * 2 + 0];
             q += red[(w * COUT_V + c) * 2 + 1];
           }
@@ -385,7 +434,9 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
         asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");
       }
+      if (p.trace && threadIdx.x == 0 && 2 * tcount + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 2) * TRACE_N + 2 * tcount + 1] = clock64();
     }
+    if (p.stats) __threadfence();
   }
 
   tc_fence_before();
@@ -393,6 +444,36 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   if (warp == TC_EPI_WARPS) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * COUT_V) : "memory");
+  }
+
+  // ---- the last CTA to finish turns the statistics into the next layer's InstanceNorm scale / shift
+  //      (nn.InstanceNorm1d(affine=True): biased variance, eps 1e-5) and clears them for the next chunk
+  if (p.fin_counter) {
+    __shared__ int is_last;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const unsigned ticket = atomicAdd(p.fin_counter, 1u);
+      is_last = ticket == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+      __threadfence();
+      const int n = p.B * p.cout_mod;
+      for (int i = threadIdx.x; i < n; i += TC_THREADS) {
+        const int c = i % p.cout_mod;
+        const double sum = __ldcg(p.stats + 2 * i), sq = __ldcg(p.stats + 2 * i + 1);
+        const double mean = sum / p.fin_count;
+        double var = sq / p.fin_count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float rstd = (float)(1.0 / sqrt(var + 1e-5));
+        const float sc = p.fin_gamma[c] * rstd;
+        p.fin_scale[i] = sc;
+        p.fin_shift[i] = p.fin_beta[c] - (float)mean * sc;
+        p.stats[2 * i] = 0.0;
+        p.stats[2 * i + 1] = 0.0;
+      }
+      if (threadIdx.x == 0) *p.fin_counter = 0u;
+    }
   }
 }
 
@@ -410,15 +491,49 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int tiles_per_utt = (int)ceil_div(p.rows_out, TC_M);
   const int total = tiles_per_utt * p.B;
   const int grid = std::min(total, n_sm);
-  kern<<<grid, TC_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total);
-  return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
+  static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
+  if (!trace_on) {
+    kern<<<grid, TC_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total);
+    return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
+  }
+  // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch
+  static long long* dbuf = nullptr;
+  const size_t tbytes = (size_t)n_sm * 3 * TRACE_N * sizeof(long long);
+  if (!dbuf) SPANON_CUDA_TRY(cudaMalloc(&dbuf, tbytes));
+  SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
+  TapGemmParams q = p;
+  q.trace = dbuf;
+  long long t_begin = 0;
+  kern<<<grid, TC_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total);
+  int rc = check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
+  SPANON_CUDA_TRY(cudaStreamSynchronize(st));
+  std::vector<long long> h((size_t)3 * TRACE_N);
+  SPANON_CUDA_TRY(cudaMemcpy(h.data(), dbuf, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+  const int nst = p.cin_v / TC_STAGE_CH;
+  t_begin = h[0];
+  fprintf(stderr, "[trace %s] grid %d tiles %d stages/tile %d n_stages %d (cycles rel. to first producer stage)\n",
+          p.tag ? p.tag : "?", grid, total, nst, L.n_stages);
+  for (int t = 0; t < 8 && t * nst < TRACE_N; ++t) {
+    fprintf(stderr, "  tile %d: prod", t);
+    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[t * nst + s2] - t_begin);
+    fprintf(stderr, " | mma");
+    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[TRACE_N + t * nst + s2] - t_begin);
+    fprintf(stderr, " | epi %lld..%lld\n", h[2 * TRACE_N + 2 * t] - t_begin, h[2 * TRACE_N + 2 * t + 1] - t_begin);
+  }
+  return rc;
 }
 
 }  // namespace
 
 bool tapgemm_tc_supported(const TapGemmParams& p) {
   if (p.cin_v % TC_STAGE_CH != 0 || (p.cout_v != 64 && p.cout_v != 128)) return false;
-  if (p.out_mode == OUT_CH0_F32 || p.ntaps < 1 || p.ntaps > MAX_TAPS) return false;
+  if (p.out_mode == OUT_CH0_F32 || p.ntaps < 2 || p.ntaps > MAX_TAPS) return false;
+  for (int t = 0; t < p.ntaps; ++t) {   // the issue loop assumes equally spaced taps and the two zero-slice patterns
+    if (p.shift[t] != p.shift[0] + t * p.tap_step) return false;
+    if (t + 1 < p.ntaps && p.tap_kmax[t] != p.cin_v) return false;
+    if (t > 0 && p.tap_nmax[t] != p.cout_v) return false;
+  }
+  if (p.tap_step < 1 || p.tap_kmax[p.ntaps - 1] % TC_STAGE_CH != 0 || p.tap_nmax[0] % 8 != 0) return false;
   return true;
 }
 

@@ -290,6 +290,7 @@ struct Workspace {
   double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
   float* in_scale[6]; float* in_shift[6];      // [chunk][C]
   double* pool;                                // [chunk][128][2]
+  unsigned* counter;                           // last-CTA ticket of the tcgen05 kernel's fused finalize
   void* act[4];                                // activation ring, each chunk*L*32 elements
   float* tdnn_out;                             // [chunk][128][L4-14] fp32
   size_t total;
@@ -315,6 +316,7 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
   // stats are contiguous so one memset clears them
   for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * kInC[i] * 2 * sizeof(double));
   ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
+  ws.counter = (unsigned*)take(256);
   for (int i = 0; i < 6; ++i) {
     ws.in_scale[i] = (float*)take((size_t)chunk * kInC[i] * 4);
     ws.in_shift[i] = (float*)take((size_t)chunk * kInC[i] * 4);
@@ -359,6 +361,9 @@ struct LayerIO {
   int e_bn;           // bn index folded into the epilogue, -1 none
   int out_stats;      // stats index accumulated in the epilogue, -1 none
   int out_mode;
+  const float* fin_gamma = nullptr;  // affine of the InstanceNorm that consumes out_stats
+  const float* fin_beta = nullptr;
+  double fin_count = 0.0;
 };
 
 int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
@@ -380,6 +385,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
     p.tap_kmax[t] = s.cin_v;
     p.tap_nmax[t] = s.cout_v;
   }
+  p.tap_step = s.ntaps > 1 ? s.shift[1] - s.shift[0] : 0;
   if (s.mode == PACK_CONV_S2) p.tap_kmax[s.ntaps - 1] = s.cin;   // tap (2*tap+1) = 5 does not exist
   if (s.mode == PACK_CONVT_S2) p.tap_nmax[0] = s.cout;            // shift -1 only feeds the even phase
   p.w = c.ws.packed[id];
@@ -392,12 +398,19 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.out_mode = io.out_mode;
   p.B = nb;
   p.tag = kLayerTag[id];
+  if (on_tc && io.out_stats >= 0) {  // finalize fused into the producing kernel (last CTA)
+    p.fin_counter = c.ws.counter;
+    p.fin_gamma = io.fin_gamma; p.fin_beta = io.fin_beta;
+    p.fin_scale = c.ws.in_scale[io.out_stats]; p.fin_shift = c.ws.in_shift[io.out_stats];
+    p.fin_count = io.fin_count;
+  }
   if (on_tc) return launch_tapgemm_tc(p, c.n_sm, c.st);
   if (c.tc) return launch_tapgemm_simt<__half>(p, c.st);
   return launch_tapgemm_simt<float>(p, c.st);
 }
 
-int finalize_in(const Ctx& c, int idx, const float* gamma, const float* beta, int nb, double count) {
+int finalize_in(const Ctx& c, int producer, int idx, const float* gamma, const float* beta, int nb, double count) {
+  if (layer_on_tc(c, producer)) return SPANON_OK;  // done by the producing tcgen05 kernel
   const int C = kInC[idx];
   instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * C, 128), 128, 0, c.st>>>(
       c.ws.stats[idx], gamma, beta, nb, C, count, c.ws.in_scale[idx], c.ws.in_shift[idx]);
@@ -488,6 +501,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   const int64_t L2 = L / 2, L4 = L / 4;
   const size_t stats_bytes = reinterpret_cast<char*>(c.ws.pool) + align_up((size_t)chunk * 128 * 2 * sizeof(double), 256) -
                              reinterpret_cast<char*>(c.ws.stats[0]);
+  SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.counter, 0, 256, c.st));
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int nb = (int)std::min<int64_t>(chunk, B - b0);
     SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.stats[0], 0, stats_bytes, c.st));
@@ -509,14 +523,14 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       SPANON_TRY(check_launch("first_layer_kernel"));
     }
     //                         in    out   in_norm t2  bias          relu e_bn stats out_mode
-    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, w->enc_b[1], 0, -1, 0, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, w->enc_b[3], 0, -1, 2, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 2, w->enc_in_w[2], w->enc_in_b[2], nb, (double)L4));
-    SPANON_TRY(run_layer(c, L_ENC11, {X[3], X[0], 2, -1, w->enc_b[4], 0, -1, 3, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 3, w->enc_in_w[3], w->enc_in_b[3], nb, (double)L4));
+    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, w->enc_b[1], 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC2, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC5, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, w->enc_b[3], 0, -1, 2, OUT_CHANNELS_LAST, w->enc_in_w[2], w->enc_in_b[2], (double)L4}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC8, 2, w->enc_in_w[2], w->enc_in_b[2], nb, (double)L4));
+    SPANON_TRY(run_layer(c, L_ENC11, {X[3], X[0], 2, -1, w->enc_b[4], 0, -1, 3, OUT_CHANNELS_LAST, w->enc_in_w[3], w->enc_in_b[3], (double)L4}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC11, 3, w->enc_in_w[3], w->enc_in_b[3], nb, (double)L4));
     // X[0] = raw encoder.11 output; the bottleneck is SiLU(IN(X[0])), applied by both consumers on load
     if (run_clf) {
       SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
@@ -532,11 +546,11 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2}, nb));
+    SPANON_TRY(finalize_in(c, L_DEC1, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
     SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(finalize_in(c, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
+    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L}, nb));
+    SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
     SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
   }
   return SPANON_OK;

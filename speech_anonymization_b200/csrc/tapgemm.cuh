@@ -37,6 +37,7 @@ struct TapGemmParams {
   int cin_v, cout_v, cin_mod, cout_mod;
   int ntaps;
   int shift[MAX_TAPS];
+  int tap_step;            // shift[t] = shift[0] + t*tap_step when the taps are equally spaced (dilation), else 0
   int tap_kmax[MAX_TAPS];  // input channels (of cin_v) with non-zero weights for this tap (stride-2 view: last tap half)
   int tap_nmax[MAX_TAPS];  // output columns (of cout_v) with non-zero weights (transposed conv: first tap half)
   const void* w;       // packed weights (layout depends on the kernel family)
@@ -49,6 +50,11 @@ struct TapGemmParams {
   double* stats;       // [B][cout_mod][2] or null
   int out_mode;
   int B;
+  // tcgen05 kernel only: the last CTA converts `stats` into the consumer's InstanceNorm scale/shift
+  // [B][cout_mod] and zeroes `stats` (fin_counter == nullptr: the caller runs instnorm_finalize_kernel)
+  unsigned* fin_counter; const float* fin_gamma; const float* fin_beta; float* fin_scale; float* fin_shift;
+  double fin_count;
+  long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]
   const char* tag;     // profile name of this launch ("tapgemm:<layer>")
 };
 
