@@ -75,7 +75,9 @@ tapgemm_simt_kernel(TapGemmParams p, int halo_lo, int slab_rows) {
       const int grow = m0 - halo_lo + r;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (grow >= 0 && grow < p.rows_in) {
-        v = Vec4<TAct>::load(in + (int64_t)grow * p.cin_v + kc + c4);
+        const int cc = kc + c4;
+        v = p.in_planar ? Vec4<TAct>::load(in + ((((int64_t)(cc >> 3) * p.rows_in + grow) << 3) + (cc & 7)))
+                        : Vec4<TAct>::load(in + (int64_t)grow * p.cin_v + cc);
         float* e = reinterpret_cast<float*>(&v);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {

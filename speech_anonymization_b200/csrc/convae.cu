@@ -156,9 +156,12 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
 #pragma unroll
       for (int q = 0; q < 8; ++q) o4[q] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
     } else {
-      uint4* o4 = reinterpret_cast<uint4*>(o);
+      // fp16 planes are chunk-planar in the CONSUMER's view: encoder.2 (stride 2) sees row pairs as one row of 64
+      // channels -> plane (l & 1) * 4 + q, row l >> 1  (tapgemm.cuh OUT_PAIR_FOLD)
+      TAct* ob = out + (int64_t)b * out_bstride;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
+        uint4* o4 = reinterpret_cast<uint4*>(ob + (((int64_t)((l & 1) * 4 + q) * (L >> 1) + (l >> 1)) << 3));
         __half2 h0 = __floats2half2_rn(acc[8 * q + 0], acc[8 * q + 1]);
         __half2 h1 = __floats2half2_rn(acc[8 * q + 2], acc[8 * q + 3]);
         __half2 h2 = __floats2half2_rn(acc[8 * q + 4], acc[8 * q + 5]);
@@ -166,7 +169,7 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
         uint4 r;
         r.x = *reinterpret_cast<uint32_t*>(&h0); r.y = *reinterpret_cast<uint32_t*>(&h1);
         r.z = *reinterpret_cast<uint32_t*>(&h2); r.w = *reinterpret_cast<uint32_t*>(&h3);
-        o4[q] = r;
+        *o4 = r;
       }
     }
   }
@@ -330,13 +333,12 @@ struct Ctx {
   const SpanonConvAEWeights* w;
   Workspace ws;
   bool tc;       // fp16 activations (+ tcgen05 where supported)
-  bool tc_off;   // $SPANON_DISABLE_TC: run the fp16 mode on the CUDA-core kernel (cross-check)
   int n_sm;
   int64_t L;
   cudaStream_t st;
 };
 
-bool layer_on_tc(const Ctx& c, int id) { return c.tc && !c.tc_off && id != L_DEC8; }
+bool layer_on_tc(const Ctx& c, int id) { return c.tc && id != L_DEC8; }
 
 int pack_layer(const Ctx& c, int id, const float* w) {
   const bool on_tc = layer_on_tc(c, id);
@@ -364,6 +366,7 @@ struct LayerIO {
   const float* fin_gamma = nullptr;  // affine of the InstanceNorm that consumes out_stats
   const float* fin_beta = nullptr;
   double fin_count = 0.0;
+  int out_fold = OUT_DIRECT;         // fp16 mode: how the consumer views this layer's output planes
 };
 
 int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
@@ -396,6 +399,9 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   if (io.e_bn >= 0) { p.e_scale = c.ws.bn_scale[io.e_bn]; p.e_shift = c.ws.bn_shift[io.e_bn]; }
   p.stats = io.out_stats >= 0 ? c.ws.stats[io.out_stats] : nullptr;
   p.out_mode = io.out_mode;
+  p.out_fold = io.out_fold;
+  p.out_plane_rows = io.out_fold == OUT_PAIR_FOLD ? p.rows_out / 2 : io.out_fold == OUT_PHASE_UNFOLD ? p.rows_out * 2 : p.rows_out;
+  p.in_planar = c.tc ? 1 : 0;
   p.B = nb;
   p.tag = kLayerTag[id];
   if (on_tc && io.out_stats >= 0) {  // finalize fused into the producing kernel (last CTA)
@@ -468,10 +474,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   const size_t esize = c.tc ? 2 : 4;
   carve(c.ws, base, chunk, L, c.tc, esize);
   c.w = w; c.L = L; c.st = as_stream(stream);
-  {
-    const char* e = getenv("SPANON_DISABLE_TC");
-    c.tc_off = e && e[0] == '1';
-  }
+
   {
     int dev = 0;
     SPANON_CUDA_TRY(cudaGetDevice(&dev));
@@ -525,7 +528,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     //                         in    out   in_norm t2  bias          relu e_bn stats out_mode
     SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, w->enc_b[1], 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2}, nb));
     SPANON_TRY(finalize_in(c, L_ENC2, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2}, nb));
+    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
+                                     OUT_PAIR_FOLD}, nb));
     SPANON_TRY(finalize_in(c, L_ENC5, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
     SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, w->enc_b[3], 0, -1, 2, OUT_CHANNELS_LAST, w->enc_in_w[2], w->enc_in_b[2], (double)L4}, nb));
     SPANON_TRY(finalize_in(c, L_ENC8, 2, w->enc_in_w[2], w->enc_in_b[2], nb, (double)L4));
@@ -546,10 +550,12 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2}, nb));
+    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2,
+                                     OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC1, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
     SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L}, nb));
+    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
+                                     OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
     SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
   }

@@ -29,6 +29,14 @@ enum OutMode {
   OUT_CH0_F32              // [B][rows_out] fp32, channel 0 only (decoder.8 -> recon)
 };
 
+// fp16 planes are chunk-planar, [utterance][channel/8][row][8] (see conv_tc.cu); how a layer's output rows/channels
+// map onto the CONSUMER's planes:
+enum OutFold {
+  OUT_DIRECT = 0,        // plane c/8, row m
+  OUT_PAIR_FOLD = 1,     // consumer views row pairs as one row of 2*C channels (stride-2 conv): plane (m&1)*C/8 + c/8, row m>>1
+  OUT_PHASE_UNFOLD = 2   // this layer is a transposed conv computing [even | odd] phases: plane (c % Cout)/8, row 2m + c/Cout
+};
+
 struct TapGemmParams {
   const void* in;
   void* out;
@@ -49,6 +57,9 @@ struct TapGemmParams {
   const float* e_scale; const float* e_shift;    // [cout_mod] or null
   double* stats;       // [B][cout_mod][2] or null
   int out_mode;
+  int out_fold;            // OutFold (tcgen05 kernel, OUT_CHANNELS_LAST)
+  int out_plane_rows;      // rows of one destination plane
+  int in_planar;           // CUDA-core kernel: input is chunk-planar fp16 (decoder.8 reading a tcgen05 layer's output)
   int B;
   // tcgen05 kernel only: the last CTA converts `stats` into the consumer's InstanceNorm scale/shift
   // [B][cout_mod] and zeroes `stats` (fin_counter == nullptr: the caller runs instnorm_finalize_kernel)
