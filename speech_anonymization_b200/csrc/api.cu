@@ -3,6 +3,7 @@
 #include <mutex>
 #include <string>
 #include <string.h>
+#include <stdlib.h>
 #include <vector>
 
 namespace spanon {
@@ -16,6 +17,7 @@ void set_last_cuda_error(const char* what, cudaError_t e) {
 
 // ---- kernel-time profile: consecutive-event deltas on one stream, aggregated by kernel name ----
 std::atomic<int> g_profile_on{0};
+const bool g_debug_sync = getenv("SPANON_DEBUG_SYNC") && getenv("SPANON_DEBUG_SYNC")[0] == '1';
 namespace {
 struct Mark { const char* what; cudaEvent_t ev; };
 std::mutex g_prof_mu;

@@ -12,6 +12,7 @@ namespace spanon {
 
 extern std::atomic<uint64_t> g_launch_count;
 extern std::atomic<int> g_profile_on;
+extern const bool g_debug_sync;
 void set_last_cuda_error(const char* what, cudaError_t e);
 // Kernel-time profile (spanon_profile_begin/_end): an event after every launch on the profiled stream.
 void profile_mark(const char* what);
@@ -20,6 +21,12 @@ inline int check_launch(const char* what) {
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   if (g_profile_on.load(std::memory_order_relaxed)) profile_mark(what);
   cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && g_debug_sync) {   // $SPANON_DEBUG_SYNC=1: synchronise and report after every launch
+    fprintf(stderr, "[spanon] launched %s ... ", what);
+    fflush(stderr);
+    e = cudaDeviceSynchronize();
+    fprintf(stderr, "%s\n", cudaGetErrorString(e));
+  }
   if (e != cudaSuccess) {
     set_last_cuda_error(what, e);
     return SPANON_ERR_CUDA;

@@ -7,18 +7,19 @@
 //
 // One persistent CTA per SM walks (utterance, 128-row tile) pairs of one layer:
 //
-//   warp 17      LOADER      one thread: per stage (32 input channels = 4 chunks) four bulk copies global -> smem,
+//   warp 13      LOADER      one thread: per stage (32 input channels = 4 chunks) four bulk copies global -> smem,
 //                            completion on the stage's `raw` mbarrier (expect_tx).  Runs as far ahead as the ring allows.
-//   warps 8..15  TRANSFORM   in place in shared memory: InstanceNorm affine (fp32) -> SiLU (tanh.approx.f16x2) ->
+//   warps 4..11  TRANSFORM   in place in shared memory: InstanceNorm affine (fp32) -> SiLU (tanh.approx.f16x2) ->
 //                            folded BatchNorm of the PRODUCER layer, zero rows outside the utterance (= the conv's zero
 //                            padding of the already activated tensor); fence.proxy.async, then the `full` mbarrier.
-//   warp 16      MMA ISSUER  one thread: per stage and tap two tcgen05.mma (M=128, N=cout_v, K=16, kind::f16, fp32
+//   warp 12      MMA ISSUER  one thread: per stage and tap two tcgen05.mma (M=128, N=cout_v, K=16, kind::f16, fp32
 //                            accumulate in TMEM).  All of the layer's packed weights are resident in shared memory.
-//   warps 0..7   EPILOGUE    tcgen05.ld of the accumulator (double-buffered in TMEM) -> + bias, ReLU, folded BN -> fp16 ->
-//                            staging tile in shared memory laid out as the CONSUMER's chunk-planar view (direct, pair-folded
-//                            for a stride-2 consumer, phase-unfolded after a transposed conv) -> one bulk store per chunk.
-//                            InstanceNorm statistics (sum, sum of squares per channel) are column sums of the staged tile;
-//                            the last CTA to finish turns them into the consumer's scale/shift.
+//   warps 0..3   EPILOGUE    tcgen05.ld of the accumulator (double-buffered in TMEM) -> + bias, ReLU, folded BN -> fp16 ->
+//                            16-byte stores straight into the CONSUMER's chunk-planar view (direct, pair-folded for a
+//                            stride-2 consumer, phase-unfolded after a transposed conv): a warp's 32 rows of one chunk are
+//                            512 contiguous bytes.  InstanceNorm statistics (sum, sum of squares per channel) come from a
+//                            butterfly transpose-reduce over the warp's rows (31 shuffles per 32 columns); the last CTA to
+//                            finish turns them into the consumer's scale/shift.
 //
 // 16-bit operands are fp16, not bf16: tools/precision_study.py shows bf16 operands + bf16 planes cannot hold the 1e-2
 // parity bar on this network (1.0-1.3e-2); fp16 gives 1.5e-3 at the same tensor-core rate.
@@ -32,8 +33,9 @@ namespace spanon {
 namespace {
 
 constexpr int TC_M = 128;                 // rows per tile = UMMA M
-constexpr int TC_EPI_WARPS = 8;           // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int TC_EPI_WARPS = 4;           // one warp per TMEM lane quarter (448 threads per CTA -> 144 registers per thread)
 constexpr int TC_XF_WARPS = 8;
+constexpr int TC_XF_GROUPS = 4;           // transform groups (two warps each), one stage in flight per group
 constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_XF_WARPS;
 constexpr int TC_LOAD_WARP = TC_MMA_WARP + 1;
 constexpr int TC_THREADS = (TC_LOAD_WARP + 1) * 32;
@@ -77,12 +79,6 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
-__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory"); }
 
 // SWIZZLE_NONE, K-major operand: 8 rows x 16 B core matrices, rows of one 8-channel chunk at a 16 B pitch
@@ -123,6 +119,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// lane l ends up with the sum over the warp's 32 lanes of v[l]  (31 shuffles instead of 32 x 5)
+__device__ __forceinline__ float warp_transpose_sum(float* v, int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
 // SiLU of two values given hh = x/2 as packed fp16:  x*sigmoid(x) = hh + hh*tanh(hh)  (one MUFU per pair)
 __device__ __forceinline__ __half2 silu_from_half(__half2 hh) {
   uint32_t t, in = *reinterpret_cast<uint32_t*>(&hh);
@@ -131,35 +142,28 @@ __device__ __forceinline__ __half2 silu_from_half(__half2 hh) {
 }
 
 struct TcLayout {        // byte offsets inside dynamic shared memory
-  uint32_t w, a, epi, red, bars, stg, total;
-  uint32_t w_bytes, stage_bytes, lbo_a, stg_bytes, stg_pitch;
-  int n_stages, slab, stg_planes, stg_rows;
+  uint32_t w, a, epi, red, bars, total;
+  uint32_t w_bytes, stage_bytes, lbo_a;
+  int n_stages, slab;
 };
 
-// staging tile of the epilogue = the consumer's chunk-planar view of this tile:
-//   OUT_DIRECT       planes = cout_v/8,  rows = 128   (plane c8, row m)
-//   OUT_PAIR_FOLD    planes = cout_v/4,  rows = 64    (plane (m&1)*cout_v/8 + c8, row m>>1)
-//   OUT_PHASE_UNFOLD planes = cout_v/16, rows = 256   (plane c8 % (cout_v/16), row 2m + c8/(cout_v/16))
-__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, int out_fold,
-                                              bool staged) {
+__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used) {
   TcLayout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;              // == 1 (mod 8): chunks start 16 B apart modulo 128 B
   L.lbo_a = (uint32_t)L.slab * 16u;
   L.stage_bytes = (uint32_t)(TC_STAGE_CH / 8) * L.lbo_a;
   L.w_bytes = (uint32_t)ntaps * cin_v * cout_v * 2u;
-  L.stg_planes = out_fold == OUT_PAIR_FOLD ? cout_v / 4 : out_fold == OUT_PHASE_UNFOLD ? cout_v / 16 : cout_v / 8;
-  L.stg_rows = out_fold == OUT_PAIR_FOLD ? TC_M / 2 : out_fold == OUT_PHASE_UNFOLD ? TC_M * 2 : TC_M;
-  L.stg_pitch = (uint32_t)(L.stg_rows + 1) * 16u;
-  L.stg_bytes = staged ? (uint32_t)L.stg_planes * L.stg_pitch : 0u;
   L.w = 0;
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
-  L.red = L.epi + 3u * cout_v * 4u;                   // [cout_v][2] fp32 column sums of the staged tile
-  L.bars = L.red + (uint32_t)cout_v * 2u * 4u;
-  L.stg = (L.bars + 512u + 127u) / 128u * 128u;
-  L.a = (L.stg + L.stg_bytes + 127u) / 128u * 128u;
+  L.red = L.epi + 3u * cout_v * 4u;                   // [2 tile parities][4 lane quarters][cout_v] float2 partial sums
+  L.bars = L.red + 2u * 4u * (uint32_t)cout_v * 8u;
+  L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
   L.n_stages = ns > TC_MAX_STAGES ? TC_MAX_STAGES : ns;
+  // a multiple of the number of transform groups: every ring slot then belongs to ONE group, so each slot's mbarriers
+  // are waited on in order by a single consumer (a waiter two phases behind would alias the parity)
+  L.n_stages = L.n_stages / TC_XF_GROUPS * TC_XF_GROUPS;
   L.total = L.a + (uint32_t)L.n_stages * L.stage_bytes;
   return L;
 }
@@ -172,8 +176,7 @@ template <int COUT_V>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const bool staged = p.out_mode == OUT_CHANNELS_LAST;
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, p.out_fold, staged);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t s_base = smem_u32(smem);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
@@ -187,7 +190,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     if (lane == 0) {
       for (int i = 0; i < L.n_stages; ++i) {
         mbar_init(BAR(B_RAW + i), 1);
-        mbar_init(BAR(B_FULL + i), TC_XF_WARPS);
+        mbar_init(BAR(B_FULL + i), TC_XF_WARPS / TC_XF_GROUPS);
         mbar_init(BAR(B_EMPTY + i), 1);
       }
       for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), TC_EPI_WARPS); }
@@ -206,16 +209,13 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp < TC_EPI_WARPS) {  // epilogue constants, cleared column sums
+  if (warp < TC_EPI_WARPS) {  // epilogue constants
     float* ec = reinterpret_cast<float*>(smem + L.epi);
-    float* red = reinterpret_cast<float*>(smem + L.red);
     for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_THREADS) {
       const int cm = c % p.cout_mod;
       ec[c] = p.bias ? p.bias[cm] : 0.f;
       ec[COUT_V + c] = p.e_scale ? p.e_scale[cm] : 1.f;
       ec[2 * COUT_V + c] = p.e_shift ? p.e_shift[cm] : 0.f;
-      red[2 * c] = 0.f;
-      red[2 * c + 1] = 0.f;
     }
   }
   tc_fence_before();
@@ -226,104 +226,122 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
 
   if (warp == TC_LOAD_WARP) {
     // =========================== LOADER ===========================
-    if (lane == 0) {
+    // lanes 0..3 each own one 8-channel chunk of the stage (one bulk copy per chunk and stage)
+    {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
-      uint32_t it = 0;
+      uint32_t stage = 0, ph = 0;
+      int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
       for (int k = 0; k < n_my_tiles; ++k) {
-        const int tile = (int)blockIdx.x + k * (int)gridDim.x;
-        const int b = tile / tiles_per_utt;
-        const int m0 = (tile - b * tiles_per_utt) * TC_M;
-        const int g0 = m0 - halo_lo;                                   // global row of slab row 0
+        const int g0 = tin * TC_M - halo_lo;                           // global row of slab row 0
         const int lo = g0 < 0 ? -g0 : 0;                               // first valid slab row
         const int hi = min(slab_used, p.rows_in - g0);                 // one past the last valid slab row
         const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
-        const __half* src0 = in_base + ((int64_t)b * planes_in * p.rows_in + (g0 + lo)) * 8;
-        for (int s = 0; s < n_stage_tile; ++s, ++it) {
-          const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
-          mbar_wait(BAR(B_EMPTY + stage), (use & 1u) ^ 1u);
-          const uint32_t dst = s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u;
-          mbar_expect_tx(BAR(B_RAW + stage), bytes * (TC_STAGE_CH / 8));
-          if (bytes) {
-#pragma unroll
-            for (int c = 0; c < TC_STAGE_CH / 8; ++c)
-              bulk_g2s(dst + (uint32_t)c * L.lbo_a, src0 + (int64_t)(s * (TC_STAGE_CH / 8) + c) * p.rows_in * 8, bytes,
-                       BAR(B_RAW + stage));
-          }
+        const __half* src = in_base + (((int64_t)b * planes_in + lane) * p.rows_in + (g0 + lo)) * 8;
+        for (int s = 0; s < n_stage_tile; ++s) {
+          mbar_wait(BAR(B_EMPTY + stage), ph ^ 1u);
+          if (p.trace && lane == 0 && k * n_stage_tile + s < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 3) * TRACE_N + k * n_stage_tile + s] = clock64();
+          if (lane == 0) mbar_expect_tx(BAR(B_RAW + stage), bytes * (TC_STAGE_CH / 8));
+          __syncwarp();
+          if (lane < TC_STAGE_CH / 8 && bytes)
+            bulk_g2s(s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u + (uint32_t)lane * L.lbo_a, src, bytes,
+                     BAR(B_RAW + stage));
+          src += (int64_t)(TC_STAGE_CH / 8) * p.rows_in * 8;
+          if (++stage == (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
         }
+        tin += (int)gridDim.x;
+        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
       }
     }
   } else if (warp >= TC_EPI_WARPS && warp < TC_MMA_WARP) {
     // =========================== TRANSFORM (in place) ===========================
+    // Four groups of two warps; group g owns the stages it == g (mod 4), so four stages are in flight at once and the
+    // per-stage chain (mbarrier wait -> LDS -> math -> STS -> proxy fence -> arrive) is off the critical path.
+    // Inside a group, warp h handles chunks 2h, 2h+1 of the stage; lanes are rows (conflict-free 16 B accesses).
     const int xw = warp - TC_EPI_WARPS;
-    const int chunk = xw & 3;                                  // 8-channel chunk of the stage handled by this warp
-    const int rbase = (xw >> 2) * 32 + lane;                   // rows rbase, rbase + 64, rbase + 128
+    const int grp = xw >> 1, ch0 = (xw & 1) * 2;
     const bool has_t1 = p.t1_scale != nullptr, has_t2 = p.t2_scale != nullptr, do_silu = p.silu != 0;
     const bool ident = !has_t1 && !has_t2 && !do_silu;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
-    uint32_t it = 0;
-    for (int k = 0; k < n_my_tiles; ++k) {
-      const int tile = (int)blockIdx.x + k * (int)gridDim.x;
-      const int b = tile / tiles_per_utt;
-      const int m0 = (tile - b * tiles_per_utt) * TC_M;
-      const int g0 = m0 - halo_lo;
+    const int s_fix = grp % n_stage_tile;                      // stage-in-tile of this group (n_stage_tile is 1, 2 or 4)
+    const int kstep = TC_XF_GROUPS / n_stage_tile;             // tiles between two stages of this group
+    int k = grp / n_stage_tile;
+    uint32_t stage = (uint32_t)grp % (uint32_t)L.n_stages, ph = ((uint32_t)grp / (uint32_t)L.n_stages) & 1u;
+    int tile = (int)blockIdx.x + k * (int)gridDim.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
+    for (; k < n_my_tiles; k += kstep) {
+      const int g0 = tin * TC_M - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
       const int hi = min(slab_used, p.rows_in - g0);
-      for (int s = 0; s < n_stage_tile; ++s, ++it) {
-        const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
-        float s1[8], h1[8];
-        __half2 s2[4], h2[4];
-        if (!ident) {   // per-(utterance, channel) constants: issued before the wait so their latency hides behind it
-          const int cm = (s * TC_STAGE_CH + chunk * 8) % p.cin_mod;
-          if (has_t1) {
-            const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.cin_mod + cm);
-            const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.cin_mod + cm);
-            const float4 a0 = __ldg(sp), a1 = __ldg(sp + 1), c0 = __ldg(hp), c1 = __ldg(hp + 1);
-            s1[0] = a0.x; s1[1] = a0.y; s1[2] = a0.z; s1[3] = a0.w; s1[4] = a1.x; s1[5] = a1.y; s1[6] = a1.z; s1[7] = a1.w;
-            h1[0] = c0.x; h1[1] = c0.y; h1[2] = c0.z; h1[3] = c0.w; h1[4] = c1.x; h1[5] = c1.y; h1[6] = c1.z; h1[7] = c1.w;
-          } else {
+      float s1[16], h1[16];
+      __half2 s2[8], h2[8];
+      if (!ident) {   // constants of this thread's 16 channels; the loads overlap the wait below
+        const int cm = (s_fix * TC_STAGE_CH + ch0 * 8) % p.cin_mod;
+        if (has_t1) {
+          const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.cin_mod + cm);
+          const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.cin_mod + cm);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { s1[j] = 1.f; h1[j] = 0.f; }
+          for (int q = 0; q < 4; ++q) {
+            const float4 a = __ldg(sp + q), c = __ldg(hp + q);
+            s1[4 * q] = a.x * pre; s1[4 * q + 1] = a.y * pre; s1[4 * q + 2] = a.z * pre; s1[4 * q + 3] = a.w * pre;
+            h1[4 * q] = c.x * pre; h1[4 * q + 1] = c.y * pre; h1[4 * q + 2] = c.z * pre; h1[4 * q + 3] = c.w * pre;
           }
+        } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { s1[j] *= pre; h1[j] *= pre; }
-          if (has_t2) {
+          for (int j = 0; j < 16; ++j) { s1[j] = pre; h1[j] = 0.f; }
+        }
+        if (has_t2) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
-              h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
-            }
+          for (int j = 0; j < 8; ++j) {
+            s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
+            h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
           }
         }
-        mbar_wait(BAR(B_RAW + stage), use & 1u);
-        unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)chunk * L.lbo_a;
+      }
+      mbar_wait(BAR(B_RAW + stage), ph);
+      const int it = k * n_stage_tile + s_fix;
+      if (p.trace && (xw & 1) == 0 && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
+      unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)ch0 * L.lbo_a;
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-          const int r = rbase + q * 64;
-          if (r >= slab_used) continue;
-          uint4* ptr = reinterpret_cast<uint4*>(base + (uint32_t)r * 16u);
-          if (r < lo || r >= hi) {                      // outside the utterance: the conv's zero padding
-            *ptr = make_uint4(0u, 0u, 0u, 0u);
-          } else if (!ident) {
-            uint4 v = *ptr;
-            __half2* hv = reinterpret_cast<__half2*>(&v);
+      for (int c = 0; c < 2; ++c) {
+        // branch-free over the five row slots of this lane so the loads / MUFU ops of different rows overlap
+        uint4 v[5];
+        bool act[5], inb[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          const int r = lane + q * 32;
+          act[q] = r < slab_used;
+          inb[q] = act[q] && r >= lo && r < hi;       // rows outside the utterance become the conv's zero padding
+          v[q] = make_uint4(0u, 0u, 0u, 0u);
+          if (inb[q]) v[q] = *reinterpret_cast<const uint4*>(base + (uint32_t)c * L.lbo_a + (uint32_t)r * 16u);
+        }
+        if (!ident) {
+#pragma unroll
+          for (int q = 0; q < 5; ++q) {
+            __half2* hv = reinterpret_cast<__half2*>(&v[q]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               float2 f = __half22float2(hv[j]);
-              f.x = fmaf(f.x, s1[2 * j], h1[2 * j]);             // InstanceNorm affine in fp32 (x/2 if SiLU follows)
-              f.y = fmaf(f.y, s1[2 * j + 1], h1[2 * j + 1]);
+              f.x = fmaf(f.x, s1[8 * c + 2 * j], h1[8 * c + 2 * j]);       // InstanceNorm affine in fp32 (x/2 if SiLU follows)
+              f.y = fmaf(f.y, s1[8 * c + 2 * j + 1], h1[8 * c + 2 * j + 1]);
               __half2 y = __floats2half2_rn(f.x, f.y);
               if (do_silu) y = silu_from_half(y);
-              if (has_t2) y = __hfma2(y, s2[j], h2[j]);          // folded eval-mode BatchNorm
+              if (has_t2) y = __hfma2(y, s2[4 * c + j], h2[4 * c + j]);    // folded eval-mode BatchNorm
               hv[j] = y;
             }
-            *ptr = v;
+            if (!inb[q]) v[q] = make_uint4(0u, 0u, 0u, 0u);
           }
         }
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(BAR(B_FULL + stage));
-        if (p.trace && xw == 0 && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 0) * TRACE_N + it] = clock64();
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+          if (act[q]) *reinterpret_cast<uint4*>(base + (uint32_t)c * L.lbo_a + (uint32_t)(lane + q * 32) * 16u) = v[q];
       }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(BAR(B_FULL + stage));
+      if (p.trace && (xw & 1) == 0 && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
+      stage += TC_XF_GROUPS;
+      while (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
+      tin += kstep * (int)gridDim.x;
+      while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
     }
   } else if (warp == TC_MMA_WARP) {
     // =========================== MMA ISSUER ===========================
@@ -342,19 +360,19 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       const uint32_t dil = (uint32_t)p.tap_step;
       const uint32_t idesc_full = umma_idesc(COUT_V), idesc_tap0 = umma_idesc(p.tap_nmax[0]);
       const int s_short = p.tap_kmax[p.ntaps - 1] / TC_STAGE_CH;  // stages >= s_short skip the last tap
-      uint32_t it = 0;
+      uint32_t it = 0, stage = 0, ph = 0;
       for (int k = 0; k < n_my_tiles; ++k) {
         const uint32_t buf = (uint32_t)k & 1u;
         mbar_wait(BAR(B_TEMPTY + buf), (((uint32_t)k >> 1) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * (uint32_t)COUT_V;
         for (int s = 0; s < n_stage_tile; ++s, ++it) {
-          const uint32_t stage = it % (uint32_t)L.n_stages, use = it / (uint32_t)L.n_stages;
           uint32_t a_lo = a_lo_const + ((s_base + L.a + stage * L.stage_bytes) >> 4);
           uint32_t b_lo = b_lo_const + (uint32_t)s * b_stage;
           const int nt = s >= s_short ? p.ntaps - 1 : p.ntaps;
-          mbar_wait(BAR(B_FULL + stage), use & 1u);
+          mbar_wait(BAR(B_FULL + stage), ph);
           tc_fence_after();
+          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
           // tap 0 (its first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
           umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
                    s == 0 ? idesc_full : idesc_tap0, s != 0);
@@ -369,7 +387,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
                      ((uint64_t)desc_hi << 32) | (b_lo + b_kstep), idesc_full, 1u);
           }
           tc_commit(BAR(B_EMPTY + stage));    // slot free once these MMAs have read it
-          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 1) * TRACE_N + it] = clock64();
+          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
+          if (++stage == (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
         }
         tc_commit(BAR(B_TFULL + buf));        // accumulator complete
       }
@@ -378,31 +397,23 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // =========================== EPILOGUE ===========================
     // warp w: TMEM lanes (rows) 32*(w%4).., columns [(w/4)*COUT_V/2, +COUT_V/2)
     const float* ec = reinterpret_cast<const float*>(smem + L.epi);
-    float* red = reinterpret_cast<float*>(smem + L.red);
-    unsigned char* stg = smem + L.stg;
+    float2* red = reinterpret_cast<float2*>(smem + L.red);
     const int quarter = warp & 3, chalf = warp >> 2;
     const int mloc = quarter * 32 + lane;
-    constexpr int CPW = COUT_V / 2;     // columns per warp
+    constexpr int CPW = COUT_V / (TC_EPI_WARPS / 4);     // columns per warp
     constexpr int NCH = COUT_V / 8;     // output chunks
-    const int out_planes = p.out_fold == OUT_PAIR_FOLD ? 2 * NCH : p.out_fold == OUT_PHASE_UNFOLD ? NCH / 2 : NCH;
-    // column-sum work split: item = (staging plane, channel pair), each thread sums `srows` staged rows of its item
-    const int items = L.stg_planes * 4;
-    const int item = threadIdx.x % items, split = threadIdx.x / items;
-    const int nsplit = TC_EPI_THREADS / items;
-    const int srows = L.stg_rows / nsplit;
-    const int s_plane = item >> 2, s_pair = item & 3;
-    const int s_ch = (s_plane % (p.cout_mod / 8)) * 8 + 2 * s_pair;     // channel (mod cout_mod) of this item
+    const bool cl = p.out_mode == OUT_CHANNELS_LAST;
+    int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
     for (int k = 0; k < n_my_tiles; ++k) {
-      const int tile = (int)blockIdx.x + k * (int)gridDim.x;
-      const int b = tile / tiles_per_utt;
-      const int m0 = (tile - b * tiles_per_utt) * TC_M;
+      const int m0 = tin * TC_M;
       const int m = m0 + mloc;
       const bool valid = m < p.rows_out;
       const uint32_t buf = (uint32_t)k & 1u;
       mbar_wait(BAR(B_TFULL + buf), ((uint32_t)k >> 1) & 1u);
       tc_fence_after();
-      if (p.trace && threadIdx.x == 0 && 2 * k < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 2) * TRACE_N + 2 * k] = clock64();
+      if (p.trace && threadIdx.x == 0 && 2 * k < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k] = clock64();
       const uint32_t taddr = tmem_base + buf * (uint32_t)COUT_V + ((uint32_t)(quarter * 32) << 16);
+      __half* out_h = reinterpret_cast<__half*>(p.out) + (int64_t)b * p.out_bstride;
       float* out_f = reinterpret_cast<float*>(p.out) + (int64_t)b * p.out_bstride;
 #pragma unroll
       for (int cb = chalf * CPW; cb < (chalf + 1) * CPW; cb += 32) {
@@ -426,75 +437,64 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
             v[j + 2] = fmaf(v[j + 2], es.z, eh.z); v[j + 3] = fmaf(v[j + 3], es.w, eh.w);
           }
         }
-        if (staged) {
+        if (cl) {
+          if (valid) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 o = make_uint4(0u, 0u, 0u, 0u);          // rows past the end stage zeros (neutral for the sums)
-            if (valid) {
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
               __half2* oh = reinterpret_cast<__half2*>(&o);
 #pragma unroll
               for (int j = 0; j < 4; ++j) oh[j] = __floats2half2_rn(v[8 * q + 2 * j], v[8 * q + 2 * j + 1]);
+              const int c8 = (cb >> 3) + q;
+              int pl, row;       // destination plane / row in the consumer's view
+              if (p.out_fold == OUT_PAIR_FOLD) { pl = (m & 1) * NCH + c8; row = m >> 1; }
+              else if (p.out_fold == OUT_PHASE_UNFOLD) { pl = c8 % (NCH / 2); row = 2 * m + c8 / (NCH / 2); }
+              else { pl = c8; row = m; }
+              *reinterpret_cast<uint4*>(out_h + (((int64_t)pl * p.out_plane_rows + row) << 3)) = o;
             }
-            const int c8 = (cb >> 3) + q;
-            int pl, sr;
-            if (p.out_fold == OUT_PAIR_FOLD) { pl = (mloc & 1) * NCH + c8; sr = mloc >> 1; }
-            else if (p.out_fold == OUT_PHASE_UNFOLD) { pl = c8 % (NCH / 2); sr = 2 * mloc + c8 / (NCH / 2); }
-            else { pl = c8; sr = mloc; }
-            *reinterpret_cast<uint4*>(stg + (uint32_t)pl * L.stg_pitch + (uint32_t)sr * 16u) = o;
           }
         } else if (valid) {   // OUT_CHANNELS_FIRST_F32: [cout_v][rows_out] fp32, coalesced over the warp's rows
 #pragma unroll
           for (int j = 0; j < 32; ++j) out_f[(int64_t)(cb + j) * p.rows_out + m] = v[j];
         }
+        if (p.stats) {
+          // statistics of the values the consumer will read (fp16-rounded), rows past the end contribute zero
+          float q[32];
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float2 f = __half22float2(__floats2half2_rn(v[j], v[j + 1]));
+            v[j] = valid ? f.x : 0.f;
+            v[j + 1] = valid ? f.y : 0.f;
+            q[j] = v[j] * v[j];
+            q[j + 1] = v[j + 1] * v[j + 1];
+          }
+          const float s_sum = warp_transpose_sum(v, lane);
+          const float s_sq = warp_transpose_sum(q, lane);
+          red[(buf * 4 + quarter) * COUT_V + cb + lane] = make_float2(s_sum, s_sq);
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
-      if (staged) {
-        fence_async_smem();                               // staged tile -> visible to the bulk-copy engine
-        epi_bar();
-        if (threadIdx.x == 0) {
-          // one contiguous piece per destination plane
-          const int rows_valid = min(TC_M, p.rows_out - m0);
-          int prow0, prows;
-          if (p.out_fold == OUT_PAIR_FOLD) { prow0 = m0 >> 1; prows = rows_valid >> 1; }
-          else if (p.out_fold == OUT_PHASE_UNFOLD) { prow0 = 2 * m0; prows = 2 * rows_valid; }
-          else { prow0 = m0; prows = rows_valid; }
-          __half* ob = reinterpret_cast<__half*>(p.out) + (int64_t)b * p.out_bstride;
-          for (int pl = 0; pl < out_planes; ++pl)
-            bulk_s2g(ob + ((int64_t)pl * p.out_plane_rows + prow0) * 8, s_base + L.stg + (uint32_t)pl * L.stg_pitch,
-                     (uint32_t)prows * 16u);
-          bulk_commit();
-        }
-        if (p.stats) {
-          // column sums of the staged (fp16-rounded) tile: 2 channels x `srows` rows per thread
-          const unsigned char* sp = stg + (uint32_t)s_plane * L.stg_pitch + (uint32_t)(split * srows) * 16u + s_pair * 4;
-          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-#pragma unroll 8
-          for (int r = 0; r < srows; ++r) {
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(sp + r * 16));
-            s0 += f.x; s1 += f.y;
-            q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
+      if (p.stats) {
+        epi_bar();   // red[buf] complete; it is rewritten two tiles later, i.e. after the next tile's barrier
+        for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_THREADS) {
+          float s = 0.f, q = 0.f;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const float2 r = red[(buf * 4 + w) * COUT_V + c];
+            s += r.x;
+            q += r.y;
           }
-          atomicAdd(red + 2 * s_ch + 0, s0);
-          atomicAdd(red + 2 * s_ch + 1, q0);
-          atomicAdd(red + 2 * s_ch + 2, s1);
-          atomicAdd(red + 2 * s_ch + 3, q1);
-          epi_bar();
-          for (int c = threadIdx.x; c < p.cout_mod; c += TC_EPI_THREADS) {
-            double* dst = p.stats + ((int64_t)b * p.cout_mod + c) * 2;
-            atomicAdd(dst + 0, (double)red[2 * c]);
-            atomicAdd(dst + 1, (double)red[2 * c + 1]);
-            red[2 * c] = 0.f;
-            red[2 * c + 1] = 0.f;
-          }
+          double* dst = p.stats + ((int64_t)b * p.cout_mod + (c % p.cout_mod)) * 2;
+          atomicAdd(dst + 0, (double)s);
+          atomicAdd(dst + 1, (double)q);
         }
-        if (threadIdx.x == 0) bulk_wait_read0();          // staging may be overwritten by the next tile
-        epi_bar();
       }
-      if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 3 + 2) * TRACE_N + 2 * k + 1] = clock64();
+      if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
+      tin += (int)gridDim.x;
+      while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
     }
-    if (staged && threadIdx.x == 0) bulk_wait0();         // all stores of this CTA are complete (global writes done)
     if (p.stats) __threadfence();
   }
 
@@ -542,10 +542,11 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
   const int halo_lo = -lo;
   const int slab_used = TC_M + halo_lo + hi;
-  if (slab_used > 192) return SPANON_ERR_UNSUPPORTED;
-  const bool staged = p.out_mode == OUT_CHANNELS_LAST;
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, p.out_fold, staged);
-  if (L.n_stages < 2 || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
+  if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
+  const int nst = p.cin_v / TC_STAGE_CH;
+  if (nst != 1 && nst != 2 && nst != 4) return SPANON_ERR_UNSUPPORTED;
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
+  if (L.n_stages < TC_XF_GROUPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc_kernel<COUT_V>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
   const int tiles_per_utt = (int)ceil_div(p.rows_out, TC_M);
@@ -558,7 +559,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   }
   // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch
   static long long* dbuf = nullptr;
-  const size_t tbytes = (size_t)n_sm * 3 * TRACE_N * sizeof(long long);
+  const size_t tbytes = (size_t)n_sm * 6 * TRACE_N * sizeof(long long);
   if (!dbuf) SPANON_CUDA_TRY(cudaMalloc(&dbuf, tbytes));
   SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
   TapGemmParams q = p;
@@ -566,17 +567,18 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   kern<<<grid, TC_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total);
   int rc = check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
-  std::vector<long long> h((size_t)3 * TRACE_N);
+  std::vector<long long> h((size_t)6 * TRACE_N);
   SPANON_CUDA_TRY(cudaMemcpy(h.data(), dbuf, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-  const int nst = p.cin_v / TC_STAGE_CH;
   const long long t_begin = h[0];
   fprintf(stderr, "[trace %s] grid %d tiles %d stages/tile %d n_stages %d smem %u (cycles rel. to first transformed stage)\n",
           p.tag ? p.tag : "?", grid, total, nst, L.n_stages, L.total);
   for (int t = 0; t < 7 && (t + 1) * nst <= TRACE_N && t < (total + grid - 1) / grid - 1; ++t) {
-    fprintf(stderr, "  tile %d: xform", t);
-    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[t * nst + s2] - t_begin);
-    fprintf(stderr, " | mma");
-    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[TRACE_N + t * nst + s2] - t_begin);
+    fprintf(stderr, "  tile %d: load", t);
+    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[3 * TRACE_N + t * nst + s2] - t_begin);
+    fprintf(stderr, " | xform(raw>done)");
+    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld>%lld", h[4 * TRACE_N + t * nst + s2] - t_begin, h[t * nst + s2] - t_begin);
+    fprintf(stderr, " | mma(full>commit)");
+    for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld>%lld", h[5 * TRACE_N + t * nst + s2] - t_begin, h[TRACE_N + t * nst + s2] - t_begin);
     fprintf(stderr, " | epi %lld..%lld\n", h[2 * TRACE_N + 2 * t] - t_begin, h[2 * TRACE_N + 2 * t + 1] - t_begin);
   }
   return rc;
