@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=4, help="utterances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk", type=int, default=0, help="utterances per L2-resident chunk of the conv stack (0 = library default)")
     return ap.parse_args()
 
 
@@ -207,6 +208,8 @@ def run_ours(a):
     torch.cuda.set_device(dev)
     pk = peaks()
     pipe = build_pipeline(a.workload, a.precision, dev)
+    if a.workload == "convae":
+        pipe.model.chunk_utts = a.chunk
     B, pool_n = a.batch, max(a.pool, a.batch)
     n_batches = pool_n // B
     host_pool = make_wavs(n_batches * B, 1234 + rank).pin_memory()       # SURVEY 8(d) synthetic input

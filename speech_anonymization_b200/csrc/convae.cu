@@ -97,6 +97,79 @@ __global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const
   }
 }
 
+// InstanceNorm statistics of a chunk-planar fp16 plane set [B][P][R][8] (tcgen05 layer output) + finalize.
+// The channel of (plane p, element j) is (p % (C/8))*8 + j (pair-folded outputs store each channel in two planes).
+// grid = (row splits, P, B), block = 256: a thread accumulates 8 channels over its rows (one 16 B load per row),
+// the block reduces through shuffles + shared memory and adds to stats[b][c][2] (fp64); the last block to finish
+// converts the sums to scale/shift like instnorm_finalize_kernel and clears them.  HBM/L2-bound: one read of the plane.
+constexpr int ST_NT = 256, ST_ROWS = 16;   // rows per thread
+__global__ void __launch_bounds__(ST_NT)
+instnorm_stats_kernel(const __half* __restrict__ x, int P, int R, int C, double* __restrict__ stats, unsigned* counter,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, double count, int B,
+                      float* __restrict__ scale, float* __restrict__ shift) {
+  __shared__ float red[ST_NT / 32][16];
+  __shared__ int is_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = blockIdx.y, b = blockIdx.z;
+  const uint4* base = reinterpret_cast<const uint4*>(x) + ((int64_t)b * P + p) * R;
+  const int r0 = blockIdx.x * (ST_NT * ST_ROWS);
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
+#pragma unroll 4
+  for (int i = 0; i < ST_ROWS; ++i) {
+    const int r = r0 + i * ST_NT + tid;
+    if (r < R) {
+      const uint4 v = __ldg(base + r);
+      const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __half22float2(h[j]);
+        s[2 * j] += f.x; s[2 * j + 1] += f.y;
+        q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = warp_sum(s[j]); q[j] = warp_sum(q[j]); }
+  if (lane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { red[warp][j] = s[j]; red[warp][8 + j] = q[j]; }
+  }
+  __syncthreads();
+  if (tid < 16) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < ST_NT / 32; ++w) a += red[w][tid];
+    const int c = (p % (C / 8)) * 8 + (tid & 7);
+    atomicAdd(stats + ((int64_t)b * C + c) * 2 + (tid >> 3), (double)a);
+    __threadfence();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+    is_last = atomicAdd(counter, 1u) == total - 1;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    for (int i = tid; i < B * C; i += ST_NT) {
+      const int c = i % C;
+      const double sum = __ldcg(stats + 2 * i), sq = __ldcg(stats + 2 * i + 1);
+      const double mean = sum / count;
+      double var = sq / count - mean * mean;
+      if (var < 0.0) var = 0.0;
+      const float rstd = (float)(1.0 / sqrt(var + 1e-5));
+      const float sc = gamma[c] * rstd;
+      scale[i] = sc;
+      shift[i] = beta[c] - (float)mean * sc;
+      stats[2 * i] = 0.0;
+      stats[2 * i + 1] = 0.0;
+    }
+    if (tid == 0) *counter = 0u;
+  }
+}
+
 // ------------------------------------------------------------------ encoder.0 (1 -> 32, k15, p7) + SiLU
 constexpr int FL_NT = 256;
 template <typename TAct, bool FAST_ACT>
@@ -302,9 +375,12 @@ struct Workspace {
 const int kInC[6] = {64, 64, 128, 128, 64, 32};
 
 int default_chunk(int64_t L, size_t esize) {
-  // keep ~3 live activation planes of a chunk inside L2 (126 MB): chunk * L*32*esize * 3 <= ~96 MB
-  const double per = (double)L * 32.0 * (double)esize;
-  int c = (int)(96.0e6 / (3.0 * per));
+  // Utterances per pass over the layer list.  Measured on B200 (bench.py --chunk, 60 x 10 s): 6 utterances (planes of
+  // a layer pair resident in the 126 MB L2) 7.1 ms/step, 20 -> 5.4, 60 -> 4.8: the kernels are latency- not
+  // bandwidth-bound, so fewer, longer launches (better tile balance over 148 SMs) win over L2 residency.  Cap the
+  // workspace at ~2 GB of activation planes.
+  const double per = (double)L * 32.0 * (double)esize;      // one plane of one utterance
+  int c = (int)(2.0e9 / (6.0 * per));
   return std::max(1, std::min(c, 64));
 }
 
@@ -333,6 +409,7 @@ struct Ctx {
   const SpanonConvAEWeights* w;
   Workspace ws;
   bool tc;       // fp16 activations (+ tcgen05 where supported)
+  bool epi_stats; // $SPANON_EPI_STATS=1: InstanceNorm statistics in the tcgen05 epilogue instead of a separate pass
   int n_sm;
   int64_t L;
   cudaStream_t st;
@@ -404,13 +481,26 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.in_planar = c.tc ? 1 : 0;
   p.B = nb;
   p.tag = kLayerTag[id];
-  if (on_tc && io.out_stats >= 0) {  // finalize fused into the producing kernel (last CTA)
+  const bool split_stats = on_tc && io.out_stats >= 0 && !c.epi_stats;
+  if (on_tc && io.out_stats >= 0 && c.epi_stats) {  // statistics in the epilogue, finalize by the last CTA
     p.fin_counter = c.ws.counter;
     p.fin_gamma = io.fin_gamma; p.fin_beta = io.fin_beta;
     p.fin_scale = c.ws.in_scale[io.out_stats]; p.fin_shift = c.ws.in_shift[io.out_stats];
     p.fin_count = io.fin_count;
   }
-  if (on_tc) return launch_tapgemm_tc(p, c.n_sm, c.st);
+  if (split_stats) p.stats = nullptr;
+  if (on_tc) {
+    SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
+    if (split_stats) {   // one bandwidth-bound pass over the fp16 plane just written (cheaper than reducing in the epilogue)
+      const int P = p.out_fold == OUT_PAIR_FOLD ? s.cout_v / 4 : p.out_fold == OUT_PHASE_UNFOLD ? s.cout_v / 16 : s.cout_v / 8;
+      dim3 grid((unsigned)ceil_div(p.out_plane_rows, ST_NT * ST_ROWS), (unsigned)P, (unsigned)nb);
+      instnorm_stats_kernel<<<grid, ST_NT, 0, c.st>>>((const __half*)io.out, P, p.out_plane_rows, s.cout, c.ws.stats[io.out_stats],
+                                                      c.ws.counter, io.fin_gamma, io.fin_beta, io.fin_count, nb,
+                                                      c.ws.in_scale[io.out_stats], c.ws.in_shift[io.out_stats]);
+      return check_launch("instnorm_stats_kernel");
+    }
+    return SPANON_OK;
+  }
   if (c.tc) return launch_tapgemm_simt<__half>(p, c.st);
   return launch_tapgemm_simt<float>(p, c.st);
 }
@@ -474,6 +564,10 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   const size_t esize = c.tc ? 2 : 4;
   carve(c.ws, base, chunk, L, c.tc, esize);
   c.w = w; c.L = L; c.st = as_stream(stream);
+  {
+    const char* e = getenv("SPANON_EPI_STATS");
+    c.epi_stats = e && e[0] == '1';
+  }
 
   {
     int dev = 0;
