@@ -44,6 +44,9 @@ constexpr int TC_STAGE_CH = 32;           // input channels per A stage (two K=1
 constexpr int TC_MAX_STAGES = 8;
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
+constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
+constexpr int TC_TOEP_STEP = TC_M - (TC_TOEP_TAPS - 1);   // complete outputs per 128-row tile
+__host__ __device__ constexpr int TC_TMEM_COLS(int cout_v) { return 2 * cout_v < 32 ? 32 : 2 * cout_v; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -119,6 +122,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 // lane l ends up with the sum over the warp's 32 lanes of v[l]  (31 shuffles instead of 32 x 5)
 __device__ __forceinline__ float warp_transpose_sum(float* v, int lane) {
 #pragma unroll
@@ -156,7 +171,7 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.w = 0;
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
   L.red = L.epi + 3u * cout_v * 4u;                   // [2 tile parities][4 lane quarters][cout_v] float2 partial sums
-  L.bars = L.red + 2u * 4u * (uint32_t)cout_v * 8u;
+  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : 2u * 4u * (uint32_t)cout_v * 8u);   // (Toeplitz: 2 x [128][17] fp32)
   L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
@@ -174,7 +189,7 @@ enum { B_RAW = 0, B_FULL = 8, B_EMPTY = 16, B_TFULL = 24, B_TEMPTY = 26, B_W = 2
 
 template <int COUT_V>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles) {
+tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
   extern __shared__ __align__(128) unsigned char smem[];
   const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -205,7 +220,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     }
     __syncwarp();
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_ptr_smem)),
-                 "r"(2 * COUT_V)
+                 "r"(TC_TMEM_COLS(COUT_V))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -232,7 +247,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       uint32_t stage = 0, ph = 0;
       int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
       for (int k = 0; k < n_my_tiles; ++k) {
-        const int g0 = tin * TC_M - halo_lo;                           // global row of slab row 0
+        const int g0 = tin * tile_step - halo_lo;                      // global row of slab row 0
         const int lo = g0 < 0 ? -g0 : 0;                               // first valid slab row
         const int hi = min(slab_used, p.rows_in - g0);                 // one past the last valid slab row
         const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
@@ -268,7 +283,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     uint32_t stage = (uint32_t)grp % (uint32_t)L.n_stages, ph = ((uint32_t)grp / (uint32_t)L.n_stages) & 1u;
     int tile = (int)blockIdx.x + k * (int)gridDim.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
     for (; k < n_my_tiles; k += kstep) {
-      const int g0 = tin * TC_M - halo_lo;
+      const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
       const int hi = min(slab_used, p.rows_in - g0);
       float s1[16], h1[16];
@@ -404,8 +419,38 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     constexpr int NCH = COUT_V / 8;     // output chunks
     const bool cl = p.out_mode == OUT_CHANNELS_LAST;
     int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
+    if constexpr (COUT_V == 16) {
+      // ---- Toeplitz epilogue (decoder.8, 32 -> 1 channel, 15 taps): the GEMM produced D[r][t] = sum_c a[r][c] w[c][t]
+      //      for the 128 slab rows; out[l] = bias + sum_t D[l - m0 + t][t]  (slab row 0 = global row m0 - 7)
+      float* dt = reinterpret_cast<float*>(smem + L.red);
+      const float bias0 = ec[0];
+      for (int k = 0; k < n_my_tiles; ++k) {
+        const int m0 = tin * tile_step;
+        const uint32_t buf = (uint32_t)k & 1u;
+        mbar_wait(BAR(B_TFULL + buf), ((uint32_t)k >> 1) & 1u);
+        tc_fence_after();
+        float v[16];
+        tmem_ld16(tmem_base + buf * (uint32_t)COUT_V + ((uint32_t)(quarter * 32) << 16), v);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));
+        float* d = dt + buf * (TC_M * 17);
+#pragma unroll
+        for (int t = 0; t < 16; ++t) d[mloc * 17 + t] = v[t];
+        epi_bar();     // dt[buf] is rewritten two tiles later, i.e. after the next tile's barrier
+        const int m = m0 + mloc;
+        if (mloc < TC_TOEP_STEP && m < p.rows_out) {
+          float acc = bias0;
+#pragma unroll
+          for (int t = 0; t < TC_TOEP_TAPS; ++t) acc += d[(mloc + t) * 17 + t];
+          reinterpret_cast<float*>(p.out)[(int64_t)b * p.out_bstride + m] = acc;
+        }
+        tin += (int)gridDim.x;
+        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+      }
+    } else
     for (int k = 0; k < n_my_tiles; ++k) {
-      const int m0 = tin * TC_M;
+      const int m0 = tin * tile_step;
       const int m = m0 + mloc;
       const bool valid = m < p.rows_out;
       const uint32_t buf = (uint32_t)k & 1u;
@@ -502,7 +547,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   __syncthreads();
   if (warp == TC_MMA_WARP) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * COUT_V) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS(COUT_V)) : "memory");
   }
 
   // ---- the last CTA to finish turns the statistics into the next layer's InstanceNorm scale / shift
@@ -540,8 +585,10 @@ template <int COUT_V>
 int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   int lo = 0, hi = 0;
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
+  const bool toeplitz = COUT_V == 16;
   const int halo_lo = -lo;
-  const int slab_used = TC_M + halo_lo + hi;
+  const int slab_used = toeplitz ? TC_M : TC_M + halo_lo + hi;
+  const int tile_step = toeplitz ? TC_TOEP_STEP : TC_M;
   if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
   const int nst = p.cin_v / TC_STAGE_CH;
   if (nst != 1 && nst != 2 && nst != 4) return SPANON_ERR_UNSUPPORTED;
@@ -549,12 +596,12 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (L.n_stages < TC_XF_GROUPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc_kernel<COUT_V>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-  const int tiles_per_utt = (int)ceil_div(p.rows_out, TC_M);
+  const int tiles_per_utt = (int)ceil_div(p.rows_out, tile_step);
   const int total = tiles_per_utt * p.B;
   const int grid = std::min(total, n_sm);
   static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
   if (!trace_on) {
-    kern<<<grid, TC_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total);
+    kern<<<grid, TC_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step);
     return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   }
   // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch
@@ -564,7 +611,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
   TapGemmParams q = p;
   q.trace = dbuf;
-  kern<<<grid, TC_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total);
+  kern<<<grid, TC_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total, tile_step);
   int rc = check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
   std::vector<long long> h((size_t)6 * TRACE_N);
@@ -587,8 +634,11 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
 }  // namespace
 
 bool tapgemm_tc_supported(const TapGemmParams& p) {
+  if (p.out_mode == OUT_CH0_F32)   // Toeplitz form of a C -> 1 channel conv: one "tap" at shift -(k-1)/2, 16 columns = the taps
+    return p.cin_v == TC_STAGE_CH && p.cout_v == 16 && p.ntaps == 1 && p.shift[0] == -(TC_TOEP_TAPS - 1) / 2 && !p.stats &&
+           p.tap_kmax[0] == p.cin_v && p.tap_nmax[0] == 16;
   if (p.cin_v % TC_STAGE_CH != 0 || (p.cout_v != 64 && p.cout_v != 128)) return false;
-  if (p.out_mode == OUT_CH0_F32 || p.ntaps < 2 || p.ntaps > MAX_TAPS) return false;
+  if (p.ntaps < 2 || p.ntaps > MAX_TAPS) return false;
   for (int t = 0; t < p.ntaps; ++t) {   // the issue loop assumes equally spaced taps and the two zero-slice patterns
     if (p.shift[t] != p.shift[0] + t * p.tap_step) return false;
     if (t + 1 < p.ntaps && p.tap_kmax[t] != p.cin_v) return false;
@@ -602,6 +652,7 @@ bool tapgemm_tc_supported(const TapGemmParams& p) {
 
 int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (!tapgemm_tc_supported(p) || p.B < 1) return SPANON_ERR_UNSUPPORTED;
+  if (p.cout_v == 16) return launch_tc<16>(p, n_sm, st);
   if (p.cout_v == 64) return launch_tc<64>(p, n_sm, st);
   return launch_tc<128>(p, n_sm, st);
 }

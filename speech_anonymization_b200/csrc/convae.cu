@@ -24,7 +24,7 @@ int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 namespace {
 
 // ------------------------------------------------------------------ weight packing
-enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2 };
+enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2, PACK_TOEPLITZ = 3 };
 
 // Source value of packed element (tap, civ, cov); cin/cout/k are the REAL layer sizes.
 __device__ __forceinline__ float packed_src(const float* __restrict__ w, int mode, int cin, int cout, int k,
@@ -37,6 +37,9 @@ __device__ __forceinline__ float packed_src(const float* __restrict__ w, int mod
     const int t = 2 * tap + half;
     if (t >= k) return 0.f;
     return w[((int64_t)cov * cin + ci) * k + t];
+  } else if (mode == PACK_TOEPLITZ) {    // Conv1d weight [1][cin][k] as a [cin] x [k taps (+ zero columns)] matrix
+    if (cov >= k) return 0.f;
+    return w[(int64_t)civ * k + cov];
   } else {                               // ConvTranspose1d weight [cin][cout][k]; cov = phase*cout + co
     const int phase = cov / cout, co = cov - phase * cout;
     const int t = 4 - 2 * tap + phase;   // shifts -1,0,+1 <-> taps (4|-), (2|3), (0|1)
@@ -351,8 +354,10 @@ LayerSpec make_spec(int id, bool tc) {
     case L_DEC1:  s = {PACK_CONVT_S2, 128, 64, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
     case L_DEC4:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
     case L_DEC5:  s = {PACK_CONVT_S2, 64, 32, 5, 64, 64, 0, {}, 2, 0};   taps({-1, 0, 1}); break;
-    case L_DEC8:  s = {PACK_CONV_S1, 32, 1, 15, 32, tc ? 16 : 4, 0, {}, 1, 0};
-                  taps({-7, -6, -5, -4, -3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7}); break;
+    case L_DEC8:
+      if (tc) { s = {PACK_TOEPLITZ, 32, 1, 15, 32, 16, 0, {}, 1, 0}; taps({-7}); }   // Toeplitz GEMM, see conv_tc.cu
+      else { s = {PACK_CONV_S1, 32, 1, 15, 32, 4, 0, {}, 1, 0}; taps({-7, -6, -5, -4, -3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7}); }
+      break;
   }
   return s;
 }
@@ -415,7 +420,7 @@ struct Ctx {
   cudaStream_t st;
 };
 
-bool layer_on_tc(const Ctx& c, int id) { return c.tc && id != L_DEC8; }
+bool layer_on_tc(const Ctx& c, int id) { return c.tc; (void)id; }
 
 int pack_layer(const Ctx& c, int id, const float* w) {
   const bool on_tc = layer_on_tc(c, id);
