@@ -107,6 +107,26 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Warp-converged variants: the whole warp executes them with identical operands and ONE elected lane issues. Keeping the
+// issuer's control flow warp-uniform lets ptxas hold descriptors in uniform registers; the same code under `if (lane == 0)`
+// compiles to an R2UR chain plus an ELECT/BRA.U.ANY loop around every UTCHMMA (~90 cycles per MMA instead of <= 48).
+__device__ __forceinline__ void umma_f16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   uint32_t* r = reinterpret_cast<uint32_t*>(v);
   asm volatile(
@@ -363,7 +383,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // One thread issues; its instruction stream is the critical path (a lone thread retires a dependent
     // instruction every ~4 cycles), so the per-MMA work is a couple of adds on the descriptors' low words:
     //   A: + dil (16 B rows) per tap, + 2*LBO per K step;   B: + one [cin_v/8][cout_v] slice per tap.
-    if (lane == 0) {
+    // All 32 lanes run the loop converged (see umma_f16_elect); waits are warp-wide polls of the same barrier.
+    {
       mbar_wait(BAR(B_W), 0);
       const uint32_t desc_hi = (uint32_t)(umma_desc(0, 0) >> 32);
       const uint32_t a_lo_const = (uint32_t)umma_desc(0, L.lbo_a);
@@ -375,37 +396,38 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       const uint32_t dil = (uint32_t)p.tap_step;
       const uint32_t idesc_full = umma_idesc(COUT_V), idesc_tap0 = umma_idesc(p.tap_nmax[0]);
       const int s_short = p.tap_kmax[p.ntaps - 1] / TC_STAGE_CH;  // stages >= s_short skip the last tap
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
       uint32_t it = 0, stage = 0, ph = 0;
       for (int k = 0; k < n_my_tiles; ++k) {
         const uint32_t buf = (uint32_t)k & 1u;
         mbar_wait(BAR(B_TEMPTY + buf), (((uint32_t)k >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * (uint32_t)COUT_V;
+        const uint32_t d_tmem = tmem_u + buf * (uint32_t)COUT_V;
         for (int s = 0; s < n_stage_tile; ++s, ++it) {
           uint32_t a_lo = a_lo_const + ((s_base + L.a + stage * L.stage_bytes) >> 4);
           uint32_t b_lo = b_lo_const + (uint32_t)s * b_stage;
           const int nt = s >= s_short ? p.ntaps - 1 : p.ntaps;
           mbar_wait(BAR(B_FULL + stage), ph);
           tc_fence_after();
-          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
+          if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
           // tap 0 (its first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
-          umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
-                   s == 0 ? idesc_full : idesc_tap0, s != 0);
-          umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep), ((uint64_t)desc_hi << 32) | (b_lo + b_kstep),
-                   idesc_tap0, 1u);
+          umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
+                         s == 0 ? idesc_full : idesc_tap0, s != 0);
+          umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep), ((uint64_t)desc_hi << 32) | (b_lo + b_kstep),
+                         idesc_tap0, 1u);
 #pragma unroll 1
           for (int tap = 1; tap < nt; ++tap) {
             a_lo += dil;
             b_lo += b_tap;
-            umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc_full, 1u);
-            umma_f16(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep),
-                     ((uint64_t)desc_hi << 32) | (b_lo + b_kstep), idesc_full, 1u);
+            umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc_full, 1u);
+            umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep),
+                           ((uint64_t)desc_hi << 32) | (b_lo + b_kstep), idesc_full, 1u);
           }
-          tc_commit(BAR(B_EMPTY + stage));    // slot free once these MMAs have read it
-          if (p.trace && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
+          tc_commit_elect(BAR(B_EMPTY + stage));    // slot free once these MMAs have read it
+          if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
           if (++stage == (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
         }
-        tc_commit(BAR(B_TFULL + buf));        // accumulator complete
+        tc_commit_elect(BAR(B_TFULL + buf));        // accumulator complete
       }
     }
   } else {
@@ -619,7 +641,9 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const long long t_begin = h[0];
   fprintf(stderr, "[trace %s] grid %d tiles %d stages/tile %d n_stages %d smem %u (cycles rel. to first transformed stage)\n",
           p.tag ? p.tag : "?", grid, total, nst, L.n_stages, L.total);
-  for (int t = 0; t < 7 && (t + 1) * nst <= TRACE_N && t < (total + grid - 1) / grid - 1; ++t) {
+  const int tl[] = {0, 1, 2, 3, 16, 17, 18, 19, 20, 21};
+  for (int t : tl) {
+    if ((t + 1) * nst > TRACE_N || t >= (total + grid - 1) / grid - 1) break;
     fprintf(stderr, "  tile %d: load", t);
     for (int s2 = 0; s2 < nst; ++s2) fprintf(stderr, " %lld", h[3 * TRACE_N + t * nst + s2] - t_begin);
     fprintf(stderr, " | xform(raw>done)");
