@@ -183,7 +183,8 @@ typedef struct SpanonConvAEOpts {
                              it on this network, see DESIGN.md "Precision") */
   int32_t chunk_utts;     /* utterances per L2-resident chunk; 0 = library default             */
   int32_t skip_classifier;/* 1 = do not run the sex classifier (logp untouched)                */
-  int32_t reserved;
+  int32_t weights_prepared;/* 1 = `workspace` still holds the packed weights / folded BatchNorms written by an earlier
+                             call with the same workspace, weights, B, T, F and opts: skip the per-call preparation */
 } SpanonConvAEOpts;
 
 SPANON_API size_t spanon_convae_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts);
@@ -233,6 +234,30 @@ SPANON_API int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B,
                           const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
                           float* recon_host, float* logp_host, void* dev_workspace,
                           size_t dev_workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Streaming form of the above for a long-running service: up to `depth` batches in
+ * flight over three streams (H2D | kernels | D2H), each batch in its own device
+ * workspace (allocated by the pipe), weights packed once per workspace.  The PCIe
+ * copies of neighbouring batches hide behind the kernels of the current one.
+ *   submit: enqueues one batch and returns; blocks only to retire the oldest batch
+ *           when `depth` are already in flight.  Host buffers must stay valid (and
+ *           should be pinned) until the batch is retired.
+ *   wait:   retires the OLDEST batch in flight (its recon/logp are then complete).
+ *   drain:  retires everything.
+ *   weights_changed: drain, optionally replace the weight pointers, re-pack on next use.
+ * norm_mean / norm_std / weight tensors are device pointers the caller keeps alive.
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonPipe SpanonPipe;
+SPANON_API int spanon_pipe_create(SpanonPipe** pipe, int kind, int64_t max_B, int64_t n_samples,
+                       const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                       const void* weights, const SpanonConvAEOpts* opts, int32_t depth);
+SPANON_API int spanon_pipe_submit(SpanonPipe* pipe, const float* pcm_host, int64_t B, const float* pool_noise,
+                       float* recon_host, float* logp_host);
+SPANON_API int spanon_pipe_wait(SpanonPipe* pipe);
+SPANON_API int spanon_pipe_drain(SpanonPipe* pipe);
+SPANON_API int spanon_pipe_weights_changed(SpanonPipe* pipe, const void* weights);
+SPANON_API void spanon_pipe_destroy(SpanonPipe* pipe);
 
 #ifdef __cplusplus
 }

@@ -56,7 +56,7 @@ class ConvAEWeights(C.Structure):
 
 class ConvAEOpts(C.Structure):
     _fields_ = [("precision", C.c_int32), ("chunk_utts", C.c_int32), ("skip_classifier", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("weights_prepared", C.c_int32)]
 
 
 class KernelTime(C.Structure):
@@ -103,6 +103,13 @@ SIGNATURES = {
     "spanon_anonymize_host": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(FbankCfg),
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ConvAEOpts),
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "spanon_pipe_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.POINTER(FbankCfg),
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ConvAEOpts), C.c_int32]),
+    "spanon_pipe_submit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "spanon_pipe_wait": (C.c_int, [C.c_void_p]),
+    "spanon_pipe_drain": (C.c_int, [C.c_void_p]),
+    "spanon_pipe_weights_changed": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "spanon_pipe_destroy": (None, [C.c_void_p]),
 }
 
 _lib = None

@@ -580,6 +580,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
   }
   // ---- per-call weight preparation (weights may have changed since the last call) ----
+  if (!(opts && opts->weights_prepared)) {
   SPANON_TRY(pack_layer(c, L_ENC2, w->enc_w[1]));
   SPANON_TRY(pack_layer(c, L_ENC5, w->enc_w[2]));
   SPANON_TRY(pack_layer(c, L_ENC8, w->enc_w[3]));
@@ -599,6 +600,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       bn_fold_kernel<<<1, 128, 0, c.st>>>(w->tdnn_bn[i], 128, c.ws.bn_scale[1 + i], c.ws.bn_shift[1 + i]);
       SPANON_TRY(check_launch("bn_fold_kernel"));
     }
+  }
   }
   const int64_t L2 = L / 2, L4 = L / 4;
   const size_t stats_bytes = reinterpret_cast<char*>(c.ws.pool) + align_up((size_t)chunk * 128 * 2 * sizeof(double), 256) -

@@ -38,6 +38,39 @@ extern "C" size_t spanon_anonymize_workspace_bytes(int kind, int64_t B, int64_t 
   return carve(nullptr, kind, B, n_samples, hop_length, n_mels, opts).total + 256;
 }
 
+namespace {
+struct Lanes { cudaStream_t h2d, compute, d2h; cudaEvent_t ev_h2d, ev_compute; };   // ev_* NULL when all three are one stream
+
+// Enqueues one batch: H2D on lanes.h2d, kernels on lanes.compute, D2H on lanes.d2h (ordered by the two events).
+int enqueue_batch(int kind, const float* pcm_host, int64_t B, int64_t n_samples, const SpanonFbankCfg* fb,
+                  const float* norm_mean, const float* norm_std, const void* weights, const float* pool_noise,
+                  const SpanonConvAEOpts* opts, float* recon_host, float* logp_host, const Carve& c, const Lanes& ln) {
+  const int64_t T = 1 + n_samples / fb->hop_length, Tp = padded_T(kind, T), F = fb->n_mels;
+  SPANON_CUDA_TRY(cudaMemcpyAsync(c.pcm, pcm_host, (size_t)B * n_samples * 4, cudaMemcpyHostToDevice, ln.h2d));
+  if (ln.ev_h2d) {
+    SPANON_CUDA_TRY(cudaEventRecord(ln.ev_h2d, ln.h2d));
+    SPANON_CUDA_TRY(cudaStreamWaitEvent(ln.compute, ln.ev_h2d, 0));
+  }
+  SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, ln.compute));
+  float* logp_dev = logp_host ? c.logp : nullptr;
+  if (kind == 0) {
+    SPANON_TRY(spanon_convae_fwd(c.fb, (const SpanonConvAEWeights*)weights, pool_noise, norm_mean, norm_std,
+                                 c.utt_max, fb->top_db, T, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, Tp, F, opts,
+                                 ln.compute));
+  } else {
+    SPANON_TRY(spanon_fcae_fwd(c.fb, (const SpanonFcaeWeights*)weights, pool_noise, norm_mean, norm_std, c.utt_max,
+                               fb->top_db, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, T, ln.compute));
+  }
+  if (ln.ev_compute) {
+    SPANON_CUDA_TRY(cudaEventRecord(ln.ev_compute, ln.compute));
+    SPANON_CUDA_TRY(cudaStreamWaitEvent(ln.d2h, ln.ev_compute, 0));
+  }
+  SPANON_CUDA_TRY(cudaMemcpyAsync(recon_host, c.recon, (size_t)B * Tp * F * 4, cudaMemcpyDeviceToHost, ln.d2h));
+  if (logp_host) SPANON_CUDA_TRY(cudaMemcpyAsync(logp_host, c.logp, (size_t)B * 2 * 4, cudaMemcpyDeviceToHost, ln.d2h));
+  return SPANON_OK;
+}
+}  // namespace
+
 extern "C" int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B, int64_t n_samples,
                                      const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
                                      const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
@@ -52,20 +85,124 @@ extern "C" int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B,
   char* base = reinterpret_cast<char*>(up256(reinterpret_cast<uintptr_t>(dev_workspace)));
   Carve c = carve(base, kind, B, n_samples, fb->hop_length, fb->n_mels, opts);
   cudaStream_t st = as_stream(stream);
-  const int64_t T = 1 + n_samples / fb->hop_length, Tp = padded_T(kind, T), F = fb->n_mels;
-  SPANON_CUDA_TRY(cudaMemcpyAsync(c.pcm, pcm_host, (size_t)B * n_samples * 4, cudaMemcpyHostToDevice, st));
-  SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, stream));
-  float* logp_dev = logp_host ? c.logp : nullptr;
-  if (kind == 0) {
-    SPANON_TRY(spanon_convae_fwd(c.fb, (const SpanonConvAEWeights*)weights, pool_noise, norm_mean, norm_std,
-                                 c.utt_max, fb->top_db, T, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, Tp, F, opts,
-                                 stream));
-  } else {
-    SPANON_TRY(spanon_fcae_fwd(c.fb, (const SpanonFcaeWeights*)weights, pool_noise, norm_mean, norm_std, c.utt_max,
-                               fb->top_db, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, T, stream));
-  }
-  SPANON_CUDA_TRY(cudaMemcpyAsync(recon_host, c.recon, (size_t)B * Tp * F * 4, cudaMemcpyDeviceToHost, st));
-  if (logp_host) SPANON_CUDA_TRY(cudaMemcpyAsync(logp_host, c.logp, (size_t)B * 2 * 4, cudaMemcpyDeviceToHost, st));
+  const Lanes ln{st, st, st, nullptr, nullptr};
+  SPANON_TRY(enqueue_batch(kind, pcm_host, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
+                           logp_host, c, ln));
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
+  return SPANON_OK;
+}
+
+// ------------------------------------------------------------------ streaming pipe
+// `depth` batches in flight over three streams (H2D | kernels | D2H), each batch with its own device workspace, so
+// the PCIe copies of neighbouring batches hide behind the kernels of the current one.
+struct SpanonPipe {
+  int kind = 0, depth = 0, device = 0;
+  int64_t max_B = 0, n_samples = 0;
+  SpanonFbankCfg fb{};
+  SpanonConvAEOpts opts{};
+  union { SpanonConvAEWeights conv; SpanonFcaeWeights fc; } w;
+  const float* norm_mean = nullptr; const float* norm_std = nullptr;
+  cudaStream_t h2d = nullptr, compute = nullptr, d2h = nullptr;
+  size_t ws_bytes = 0;
+  struct Slot { void* ws = nullptr; cudaEvent_t ev_h2d = nullptr, ev_compute = nullptr, ev_done = nullptr; bool busy = false; int64_t prepared_B = -1; };
+  Slot* slots = nullptr;
+  int64_t submitted = 0, retired = 0;
+};
+
+extern "C" void spanon_pipe_destroy(SpanonPipe* p) {
+  if (!p) return;
+  if (p->slots) {
+    for (int i = 0; i < p->depth; ++i) {
+      SpanonPipe::Slot& s = p->slots[i];
+      if (s.ev_done && s.busy) cudaEventSynchronize(s.ev_done);
+      if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
+      if (s.ev_compute) cudaEventDestroy(s.ev_compute);
+      if (s.ev_done) cudaEventDestroy(s.ev_done);
+      if (s.ws) cudaFree(s.ws);
+    }
+    delete[] p->slots;
+  }
+  if (p->h2d) cudaStreamDestroy(p->h2d);
+  if (p->compute) cudaStreamDestroy(p->compute);
+  if (p->d2h) cudaStreamDestroy(p->d2h);
+  delete p;
+}
+
+extern "C" int spanon_pipe_create(SpanonPipe** out, int kind, int64_t max_B, int64_t n_samples, const SpanonFbankCfg* fb,
+                                  const float* norm_mean, const float* norm_std, const void* weights,
+                                  const SpanonConvAEOpts* opts, int32_t depth) {
+  if (!out || !fb || !weights || !norm_mean || !norm_std) return SPANON_ERR_NULL_POINTER;
+  if (kind != 0 && kind != 1) return SPANON_ERR_UNSUPPORTED;
+  if (max_B <= 0 || n_samples < 0 || fb->hop_length <= 0 || depth < 1 || depth > 8) return SPANON_ERR_BAD_SHAPE;
+  SpanonPipe* p = new SpanonPipe();
+  p->kind = kind; p->depth = depth; p->max_B = max_B; p->n_samples = n_samples; p->fb = *fb;
+  if (opts) p->opts = *opts;
+  if (kind == 0) p->w.conv = *(const SpanonConvAEWeights*)weights; else p->w.fc = *(const SpanonFcaeWeights*)weights;
+  p->norm_mean = norm_mean; p->norm_std = norm_std;
+  p->ws_bytes = spanon_anonymize_workspace_bytes(kind, max_B, n_samples, fb->hop_length, fb->n_mels, &p->opts);
+  int rc = SPANON_OK;
+  auto ok = [&](cudaError_t e) { if (e != cudaSuccess && rc == SPANON_OK) { set_last_cuda_error("spanon_pipe_create", e); rc = SPANON_ERR_CUDA; } return e == cudaSuccess; };
+  ok(cudaGetDevice(&p->device));
+  if (p->ws_bytes == 0) rc = SPANON_ERR_BAD_SHAPE;
+  if (rc == SPANON_OK) {
+    ok(cudaStreamCreateWithFlags(&p->h2d, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&p->compute, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&p->d2h, cudaStreamNonBlocking));
+    p->slots = new SpanonPipe::Slot[depth];
+    for (int i = 0; i < depth && rc == SPANON_OK; ++i) {
+      SpanonPipe::Slot& s = p->slots[i];
+      ok(cudaMalloc(&s.ws, p->ws_bytes));
+      ok(cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
+      ok(cudaEventCreateWithFlags(&s.ev_compute, cudaEventDisableTiming));
+      ok(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
+    }
+  }
+  if (rc != SPANON_OK) { spanon_pipe_destroy(p); return rc; }
+  *out = p;
+  return SPANON_OK;
+}
+
+extern "C" int spanon_pipe_wait(SpanonPipe* p) {   // retires the oldest batch in flight (no-op when none is)
+  if (!p) return SPANON_ERR_NULL_POINTER;
+  if (p->retired == p->submitted) return SPANON_OK;
+  SpanonPipe::Slot& s = p->slots[p->retired % p->depth];
+  SPANON_CUDA_TRY(cudaEventSynchronize(s.ev_done));
+  s.busy = false;
+  ++p->retired;
+  return SPANON_OK;
+}
+
+extern "C" int spanon_pipe_drain(SpanonPipe* p) {
+  if (!p) return SPANON_ERR_NULL_POINTER;
+  while (p->retired < p->submitted) SPANON_TRY(spanon_pipe_wait(p));
+  return SPANON_OK;
+}
+
+extern "C" int spanon_pipe_submit(SpanonPipe* p, const float* pcm_host, int64_t B, const float* pool_noise,
+                                  float* recon_host, float* logp_host) {
+  if (!p || !pcm_host || !recon_host) return SPANON_ERR_NULL_POINTER;
+  if (B <= 0 || B > p->max_B) return SPANON_ERR_BAD_SHAPE;
+  if (p->submitted - p->retired >= p->depth) SPANON_TRY(spanon_pipe_wait(p));   // the slot we are about to reuse
+  SpanonPipe::Slot& s = p->slots[p->submitted % p->depth];
+  char* base = reinterpret_cast<char*>(up256(reinterpret_cast<uintptr_t>(s.ws)));
+  SpanonConvAEOpts o = p->opts;
+  o.weights_prepared = (p->kind == 0 && s.prepared_B == B) ? 1 : 0;   // this slot already holds the packed weights
+  Carve c = carve(base, p->kind, B, p->n_samples, p->fb.hop_length, p->fb.n_mels, &o);
+  const Lanes ln{p->h2d, p->compute, p->d2h, s.ev_h2d, s.ev_compute};
+  const void* w = p->kind == 0 ? (const void*)&p->w.conv : (const void*)&p->w.fc;
+  SPANON_TRY(enqueue_batch(p->kind, pcm_host, B, p->n_samples, &p->fb, p->norm_mean, p->norm_std, w, pool_noise, &o,
+                           recon_host, logp_host, c, ln));
+  SPANON_CUDA_TRY(cudaEventRecord(s.ev_done, p->d2h));
+  s.busy = true;
+  s.prepared_B = B;
+  ++p->submitted;
+  return SPANON_OK;
+}
+
+extern "C" int spanon_pipe_weights_changed(SpanonPipe* p, const void* weights) {
+  if (!p) return SPANON_ERR_NULL_POINTER;
+  SPANON_TRY(spanon_pipe_drain(p));
+  if (weights) { if (p->kind == 0) p->w.conv = *(const SpanonConvAEWeights*)weights; else p->w.fc = *(const SpanonFcaeWeights*)weights; }
+  for (int i = 0; i < p->depth; ++i) p->slots[i].prepared_B = -1;
   return SPANON_OK;
 }

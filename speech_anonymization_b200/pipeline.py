@@ -90,3 +90,58 @@ class AnonymizerPipeline(torch.nn.Module):
                 _lib.ptr(recon_host), _lib.ptr(logp_host), _lib.ptr(workspace), workspace.numel(),
                 _lib.stream_ptr(dev)), "anonymize_host")
         return recon_host, logp_host
+
+    def stream_pipe(self, max_batch, n_samples, device, depth=2):
+        """A StreamPipe (spanon_pipe_*) bound to this pipeline's frozen features, statistics and weights."""
+        return StreamPipe(self, max_batch, n_samples, device, depth)
+
+
+class StreamPipe:
+    """`depth` batches in flight over H2D | kernel | D2H streams (include/spanon.h, spanon_pipe_*).
+
+    submit() enqueues a batch of pinned host PCM and returns; wait() retires the oldest batch, after which its
+    recon / logp host tensors are complete.  The device workspaces belong to the pipe."""
+
+    def __init__(self, pipeline, max_batch, n_samples, device, depth=2):
+        if not pipeline._frozen_stats():
+            raise _lib.SpanonError("StreamPipe needs eval-mode InputNormalization with loaded global statistics")
+        fb, n = pipeline.compute_features, pipeline.normalize
+        self.device = torch.device(device)
+        self._keep = []          # host / device tensors referenced by batches in flight or by the pipe itself
+        st = fb._device_state(self.device)
+        self._mean = n.glob_mean.to(device=self.device, dtype=torch.float32).contiguous()
+        self._std = n.glob_std.to(device=self.device, dtype=torch.float32).contiguous()
+        self._w = pipeline.model.weight_struct()
+        opts = pipeline.model.opts() if pipeline.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().spanon_pipe_create(
+                C.byref(self._h), 0 if pipeline.is_conv else 1, max_batch, n_samples, C.byref(st["cfg"]),
+                _lib.ptr(self._mean), _lib.ptr(self._std), C.cast(C.byref(self._w), C.c_void_p), C.byref(opts), depth),
+                "pipe_create")
+        self.depth = depth
+
+    def submit(self, pcm_host, recon_host, logp_host, pool_noise=None):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().spanon_pipe_submit(self._h, _lib.ptr(pcm_host), pcm_host.shape[0],
+                                                     _lib.ptr(pool_noise), _lib.ptr(recon_host), _lib.ptr(logp_host)),
+                       "pipe_submit")
+        self._keep.append((pcm_host, recon_host, logp_host, pool_noise))
+        del self._keep[:-self.depth]
+
+    def wait(self):
+        _lib.check(_lib.lib().spanon_pipe_wait(self._h), "pipe_wait")
+
+    def drain(self):
+        _lib.check(_lib.lib().spanon_pipe_drain(self._h), "pipe_drain")
+
+    def close(self):
+        if self._h:
+            _lib.lib().spanon_pipe_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

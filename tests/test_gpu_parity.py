@@ -269,6 +269,21 @@ def test_pipeline_fused_equals_modular_equals_oracle(golden, kind):
     pipe.anonymize_host(pcm, rec_h, logp_h, ws, pool_noise=cu(noise))
     assert rel_max(rec_h.numpy(), rec_f.cpu().numpy()) < 1e-6
     assert float((logp_h - logp_f.cpu()).abs().max()) < 1e-6
+    # streaming pipe (three streams, two batches in flight, weights packed once per slot) == the one-shot call,
+    # including ragged batch sizes and slot reuse
+    torch.cuda.synchronize()
+    sp = pipe.stream_pipe(4, 16000, torch.device(DEV), depth=2)
+    outs = []
+    for i, nb in enumerate([4, 3, 4, 1, 4]):
+        r = torch.full((nb,) + tuple(rec_f.shape[1:]), float("nan"), dtype=torch.float32).pin_memory()
+        l = torch.full((nb, 2), float("nan"), dtype=torch.float32).pin_memory()
+        sp.submit(pcm[:nb], r, l, pool_noise=cu(noise)[:nb].contiguous())
+        outs.append((nb, r, l))
+    sp.drain()
+    for nb, r, l in outs:
+        assert rel_max(r.numpy(), rec_h.numpy()[:nb]) < 1e-6      # (fp64 atomics: summation order may differ)
+        assert float(np.abs(l.numpy() - logp_h.numpy()[:nb]).max()) < 1e-6
+    sp.close()
 
 
 # ------------------------------------------------------------------ losses
