@@ -326,17 +326,24 @@ def run_ours(a):
                 "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": a.precision if a.workload == "convae" else "fp32", "data": "synthetic",
-                "config": {"workload": "fbank+%s, %d x 10 s @16 kHz utterances per GPU per step from a resident pool of "
-                                       "%d utterances (1 h) per GPU" % (a.workload, B, n_batches * B),
-                           "batch_per_gpu": B, "pool_per_gpu": n_batches * B, "parallelism": "utterance-sharded x%d" % world,
-                           "l2": "inputs cycle through a %.0f MB pool (> 126 MB L2)" % (n_batches * B * N_SAMPLES * 4 / 1e6),
-                           "weights": "random-init seed 8886", "norm": "global stats from the reference's normalizer.ckpt"},
+                "config": workload_config(a, world),
                 "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roof,
                 "cpu_baseline": cpu, "stages": stages, "kernels": kern}
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+
+
+def workload_config(a, world):
+    """The workload both arms are quoted on (BASELINE.json configs[4], the throughput sweep)."""
+    B = a.batch
+    n_batches = max(1, a.pool // B)
+    return {"workload": "fbank+%s, %d x 10 s @16 kHz utterances per GPU per step from a resident pool of "
+                        "%d utterances (1 h) per GPU" % (a.workload, B, n_batches * B),
+            "batch_per_gpu": B, "pool_per_gpu": n_batches * B, "parallelism": "utterance-sharded x%d" % world,
+            "l2": "inputs cycle through a %.0f MB pool (> 126 MB L2)" % (n_batches * B * N_SAMPLES * 4 / 1e6),
+            "weights": "random-init seed 8886", "norm": "global stats from the reference's normalizer.ckpt"}
 
 
 # --------------------------------------------------------------------------- reference arm
@@ -359,8 +366,8 @@ def run_reference(a):
             "value": v, "unit": "audio-s/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
             "data": "synthetic",
-            "config": {"workload": "fbank+%s, %d x 10 s @16 kHz utterances per step on the host CPU" % (a.workload, n),
-                       "weights": "random-init seed 8886"},
+            "config": dict(workload_config(a, world), cpu_sample="each step = %d x 10 s utterances of that workload on the "
+                           "host CPU (throughput is per audio-second, so the sample size does not bias it)" % n),
             "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port",
                              "sample": "%d x 10 s utterances per step (oracle/ port of the reference's PyTorch-CPU "
                                        "path: the reference itself is not on the GPU box)" % n},
