@@ -103,35 +103,71 @@ __global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const
 // InstanceNorm statistics of a chunk-planar fp16 plane set [B][P][R][8] (tcgen05 layer output) + finalize.
 // The channel of (plane p, element j) is (p % (C/8))*8 + j (pair-folded outputs store each channel in two planes).
 // grid = (row splits, P, B), block = 256: a thread accumulates 8 channels over its rows (one 16 B load per row),
-// the block reduces through shuffles + shared memory and adds to stats[b][c][2] (fp64); the last block to finish
-// converts the sums to scale/shift like instnorm_finalize_kernel and clears them.  HBM/L2-bound: one read of the plane.
-constexpr int ST_NT = 256, ST_ROWS = 16;   // rows per thread
+// the block reduces through shuffles + shared memory and adds to stats[b][c][2] (fp64); instnorm_finalize_kernel then
+// converts the sums to scale/shift.  HBM/L2-bound: one read of the plane.
+constexpr int ST_NT = 256, ST_ROWS = 32;   // rows per thread
+
+// D += A * B for one m16n8k16 fp16 tile with fp32 accumulation (legacy warp-level MMA; the tensor pipe is idle here)
+__device__ __forceinline__ void mma16816(float* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// The per-element work of the obvious loop (2 cvt + add + fma per value) made this pass issue-bound at ~50 % of HBM
+// speed, so the sums are formed on the tensor pipe instead.  A lane holds two rows (16 B = 4 channel pairs each).
+// For channel pair q the two 32-bit words (wA, wB) are used, unmoved, as the B fragment (k = this lane's 4 values,
+// n = lane/4) AND as the A fragment (rows lane/4: low halves only; rows lane/4+8: high halves only).  Then
+//   D[g][g]   = sum over the group's 8 values of lo^2  (even channel),  D[g+8][g] = sum of hi^2 (odd channel),
+// which lane (g, t = g/2) holds in c[g&1] / c[2+(g&1)].  A second MMA with a constant 0/1 A fragment gives the plain
+// sums: row 0 = even k (low halves), row 1 = odd k.  Products of fp16 values are exact in fp32; accumulation is fp32.
 __global__ void __launch_bounds__(ST_NT)
-instnorm_stats_kernel(const __half* __restrict__ x, int P, int R, int C, double* __restrict__ stats, unsigned* counter,
-                      const float* __restrict__ gamma, const float* __restrict__ beta, double count, int B,
-                      float* __restrict__ scale, float* __restrict__ shift) {
+instnorm_stats_kernel(const __half* __restrict__ x, int P, int R, int C, double* __restrict__ stats) {
   __shared__ float red[ST_NT / 32][16];
-  __shared__ int is_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int p = blockIdx.y, b = blockIdx.z;
   const uint4* base = reinterpret_cast<const uint4*>(x) + ((int64_t)b * P + p) * R;
   const int r0 = blockIdx.x * (ST_NT * ST_ROWS);
-  float s[8], q[8];
+  const int g = lane >> 2, t = lane & 3;
+  const uint32_t one_a = g == 0 ? 0x00003C00u : g == 1 ? 0x3C000000u : 0u;   // (1,0) for row 0, (0,1) for row 1
+  float sq[4][4], sm[4][4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
-#pragma unroll 4
-  for (int i = 0; i < ST_ROWS; ++i) {
-    const int r = r0 + i * ST_NT + tid;
-    if (r < R) {
-      const uint4 v = __ldg(base + r);
-      const __half2* h = reinterpret_cast<const __half2*>(&v);
+  for (int q = 0; q < 4; ++q)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 f = __half22float2(h[j]);
-        s[2 * j] += f.x; s[2 * j + 1] += f.y;
-        q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
+    for (int j = 0; j < 4; ++j) { sq[q][j] = 0.f; sm[q][j] = 0.f; }
+  constexpr int ST_BATCH = 8;   // 16 B loads in flight per thread (issued back to back before any use)
+#pragma unroll 1
+  for (int i0 = 0; i0 < ST_ROWS; i0 += ST_BATCH) {
+    uint4 v[ST_BATCH];
+#pragma unroll
+    for (int u = 0; u < ST_BATCH; ++u) {
+      const int r = r0 + (i0 + u) * ST_NT + tid;
+      // volatile asm keeps the whole batch of loads ahead of the MMAs (the compiler otherwise sinks them next to
+      // their first use, leaving two loads in flight per thread)
+      const uint4* src = base + (r < R ? r : 0);
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src));
+      if (r >= R) v[u] = make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < ST_BATCH; u += 2) {
+      const uint32_t wa[4] = {v[u].x, v[u].y, v[u].z, v[u].w}, wb[4] = {v[u + 1].x, v[u + 1].y, v[u + 1].z, v[u + 1].w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        mma16816(sq[q], wa[q] & 0x0000FFFFu, wa[q] & 0xFFFF0000u, wb[q] & 0x0000FFFFu, wb[q] & 0xFFFF0000u, wa[q], wb[q]);
+        mma16816(sm[q], one_a, 0u, one_a, 0u, wa[q], wb[q]);
       }
     }
+  }
+  float s[8], q[8];
+  const bool diag = t == (g >> 1);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    q[2 * k] = diag ? ((g & 1) ? sq[k][1] : sq[k][0]) : 0.f;
+    q[2 * k + 1] = diag ? ((g & 1) ? sq[k][3] : sq[k][2]) : 0.f;
+    s[2 * k] = g == 0 ? sm[k][0] + sm[k][1] : 0.f;
+    s[2 * k + 1] = g == 1 ? sm[k][0] + sm[k][1] : 0.f;
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = warp_sum(s[j]); q[j] = warp_sum(q[j]); }
@@ -145,31 +181,7 @@ instnorm_stats_kernel(const __half* __restrict__ x, int P, int R, int C, double*
 #pragma unroll
     for (int w = 0; w < ST_NT / 32; ++w) a += red[w][tid];
     const int c = (p % (C / 8)) * 8 + (tid & 7);
-    atomicAdd(stats + ((int64_t)b * C + c) * 2 + (tid >> 3), (double)a);
-    __threadfence();
-  }
-  __syncthreads();
-  if (tid == 0) {
-    const unsigned total = gridDim.x * gridDim.y * gridDim.z;
-    is_last = atomicAdd(counter, 1u) == total - 1;
-  }
-  __syncthreads();
-  if (is_last) {
-    __threadfence();
-    for (int i = tid; i < B * C; i += ST_NT) {
-      const int c = i % C;
-      const double sum = __ldcg(stats + 2 * i), sq = __ldcg(stats + 2 * i + 1);
-      const double mean = sum / count;
-      double var = sq / count - mean * mean;
-      if (var < 0.0) var = 0.0;
-      const float rstd = (float)(1.0 / sqrt(var + 1e-5));
-      const float sc = gamma[c] * rstd;
-      scale[i] = sc;
-      shift[i] = beta[c] - (float)mean * sc;
-      stats[2 * i] = 0.0;
-      stats[2 * i + 1] = 0.0;
-    }
-    if (tid == 0) *counter = 0u;
+    atomicAdd(stats + ((int64_t)b * C + c) * 2 + (tid >> 3), (double)a);   // fire and forget: the block retires at once
   }
 }
 
@@ -320,6 +332,59 @@ clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise
     const float m = fmaxf(s3[0], s3[1]);
     const float lse = m + logf(expf(s3[0] - m) + expf(s3[1] - m));
     logp[(int64_t)b * 2 + tid] = s3[tid] - lse;
+  }
+}
+
+// Same pooling for the tcgen05 path, whose tdnn.6 output is the chunk-planar fp16 layout [B][P][R][8] (plane p =
+// channels 8p..8p+7): element (c, l) of the channels-first image has flat index c*R + l and is pooled into column
+// (c*R + l) % 128.  grid = (row splits, P, B); a block's first row is a multiple of 128, so row % 128 == tid % 128
+// for every row a thread reads and its eight (channel -> column) bins are fixed: register accumulators, then an
+// eight-round conflict-free shared-memory fold and one fp64 atomic pair per column.
+constexpr int PL_NT = 256, PL_ROWS = 32;
+__global__ void __launch_bounds__(PL_NT)
+pool_planar_kernel(const __half* __restrict__ x, int P, int R, double* __restrict__ pool) {
+  __shared__ float part[2][8][128];
+  __shared__ float bins[2][128];
+  const int tid = threadIdx.x, p = blockIdx.y, b = blockIdx.z;
+  const uint4* base = reinterpret_cast<const uint4*>(x) + ((int64_t)b * P + p) * R;
+  const int r0 = blockIdx.x * (PL_NT * PL_ROWS);
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
+#pragma unroll 8
+  for (int i = 0; i < PL_ROWS; ++i) {
+    const int r = r0 + i * PL_NT + tid;
+    if (r < R) {
+      const uint4 v = __ldg(base + r);
+      const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __half22float2(h[j]);
+        s[2 * j] += f.x; s[2 * j + 1] += f.y;
+        q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
+      }
+    }
+  }
+  if (tid >= 128) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { part[0][j][tid - 128] = s[j]; part[1][j][tid - 128] = q[j]; }
+  } else {
+    bins[0][tid] = 0.f; bins[1][tid] = 0.f;
+  }
+  __syncthreads();
+  const int Rm = R & 127;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (tid < 128) {   // for a fixed j, tid -> bin is a bijection on [0,128)
+      const int bin = ((8 * p + j) * Rm + tid) & 127;
+      bins[0][bin] += s[j] + part[0][j][tid];
+      bins[1][bin] += q[j] + part[1][j][tid];
+    }
+    __syncthreads();
+  }
+  if (tid < 128) {
+    atomicAdd(pool + ((int64_t)b * 128 + tid) * 2 + 0, (double)bins[0][tid]);
+    atomicAdd(pool + ((int64_t)b * 128 + tid) * 2 + 1, (double)bins[1][tid]);
   }
 }
 
@@ -499,10 +564,14 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
     if (split_stats) {   // one bandwidth-bound pass over the fp16 plane just written (cheaper than reducing in the epilogue)
       const int P = p.out_fold == OUT_PAIR_FOLD ? s.cout_v / 4 : p.out_fold == OUT_PHASE_UNFOLD ? s.cout_v / 16 : s.cout_v / 8;
       dim3 grid((unsigned)ceil_div(p.out_plane_rows, ST_NT * ST_ROWS), (unsigned)P, (unsigned)nb);
-      instnorm_stats_kernel<<<grid, ST_NT, 0, c.st>>>((const __half*)io.out, P, p.out_plane_rows, s.cout, c.ws.stats[io.out_stats],
-                                                      c.ws.counter, io.fin_gamma, io.fin_beta, io.fin_count, nb,
-                                                      c.ws.in_scale[io.out_stats], c.ws.in_shift[io.out_stats]);
-      return check_launch("instnorm_stats_kernel");
+      instnorm_stats_kernel<<<grid, ST_NT, 0, c.st>>>((const __half*)io.out, P, p.out_plane_rows, s.cout,
+                                                      c.ws.stats[io.out_stats]);
+      SPANON_TRY(check_launch("instnorm_stats_kernel"));
+      // (a separate tiny launch instead of a last-block-done counter: blocks then end without waiting on an atomic)
+      instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * s.cout, 128), 128, 0, c.st>>>(
+          c.ws.stats[io.out_stats], io.fin_gamma, io.fin_beta, nb, s.cout, io.fin_count, c.ws.in_scale[io.out_stats],
+          c.ws.in_shift[io.out_stats]);
+      return check_launch("instnorm_finalize_kernel");
     }
     return SPANON_OK;
   }
@@ -640,11 +709,17 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     if (run_clf) {
       SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
       SPANON_TRY(run_layer(c, L_TD3, {X[1], X[2], -1, -1, w->tdnn_b[1], 1, 2, -1, OUT_CHANNELS_LAST}, nb));
-      SPANON_TRY(run_layer(c, L_TD6, {X[2], c.ws.tdnn_out, -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_FIRST_F32}, nb));
       const int64_t L3 = L4 - 14;
-      const int64_t n_el = 128 * L3;
-      dim3 pg((unsigned)std::min<int64_t>(ceil_div(n_el, 256 * 16), 256), (unsigned)nb);
-      pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
+      if (c.tc) {   // fp16 planes (X[3] is free here), pooled by the planar kernel: half the bytes of the fp32 image
+        SPANON_TRY(run_layer(c, L_TD6, {X[2], X[3], -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_LAST}, nb));
+        dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);
+        pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, c.ws.pool);
+      } else {
+        SPANON_TRY(run_layer(c, L_TD6, {X[2], c.ws.tdnn_out, -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_FIRST_F32}, nb));
+        const int64_t n_el = 128 * L3;
+        dim3 pg((unsigned)std::min<int64_t>(ceil_div(n_el, 256 * 16), 256), (unsigned)nb);
+        pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
+      }
       SPANON_TRY(check_launch("pool_kernel"));
       clf_head_kernel<<<(unsigned)nb, 128, 0, c.st>>>(c.ws.pool, pool_noise ? pool_noise + b0 * 128 : nullptr, L3, *w,
                                                       logp + b0 * 2);

@@ -172,6 +172,11 @@ class ConvAutoencoder(nn.Module):
         w.cls_bn[0], w.cls_bn[1] = _bn(s.classify[2]), _bn(s.classify[5])
         return w
 
+    def __getstate__(self):   # the cached device workspace is not part of the module's state
+        d = dict(self.__dict__)
+        d.pop("_ws_cache", None)
+        return d
+
     def opts(self, skip_classifier=False):
         return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16,
                                int(self.chunk_utts), int(skip_classifier), 0)
@@ -203,7 +208,17 @@ class ConvAutoencoder(nn.Module):
         opts = self.opts()
         L = _lib.lib()
         ws_bytes = L.spanon_convae_workspace_bytes(B, T, F, C.byref(opts))
-        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        # The workspace is kept between calls so that the packed (UMMA-layout) weights in it can be reused while no
+        # parameter changed: key = every parameter/buffer's (storage pointer, in-place version counter) + the shapes.
+        key = (B, T, F, opts.precision, opts.chunk_utts, str(dev),
+               tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers())))
+        cache = self.__dict__.get("_ws_cache")
+        if cache is None or cache[0].numel() != ws_bytes or cache[0].device != dev:
+            cache = [torch.empty((ws_bytes,), dtype=torch.uint8, device=dev), None]
+            self.__dict__["_ws_cache"] = cache
+        ws = cache[0]
+        opts.weights_prepared = 1 if cache[1] == key else 0
+        cache[1] = key
         if fused_norm is None:
             mean = std = umax = None
             top_db, t_valid = 0.0, T

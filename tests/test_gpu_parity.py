@@ -286,6 +286,25 @@ def test_pipeline_fused_equals_modular_equals_oracle(golden, kind):
     sp.close()
 
 
+def test_convae_sees_weight_updates():
+    """The module keeps its workspace (with the packed weights) between calls; an in-place parameter update must
+    invalidate that cache (key = storage pointer + version counter of every parameter and buffer)."""
+    m, w = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES)
+    x = cu(recipe.make_feats(31, 2, 36))
+    noise = cu(recipe.make_noise(31, 2, 128))
+    with torch.no_grad():
+        r0, _ = m(x, pool_noise=noise)
+        r1, _ = m(x, pool_noise=noise)                    # second call reuses the packed weights
+        assert rel_max(r1.cpu().numpy(), r0.cpu().numpy()) < 1e-6
+        m.decoder[8].weight.mul_(2.0)                     # recon = conv(...) + bias: doubles the conv part
+        r2, _ = m(x, pool_noise=noise)
+        bias = float(m.decoder[8].bias[0])
+        assert rel_max((r2 - bias).cpu().numpy(), (2.0 * (r0 - bias)).cpu().numpy()) < 2e-3
+        m.sex_classifier.tdnn[2].running_mean.add_(0.5)   # a buffer (folded BatchNorm) changes the log-probs only
+        r3, l3 = m(x, pool_noise=noise)
+        assert rel_max(r3.cpu().numpy(), r2.cpu().numpy()) < 1e-6
+
+
 # ------------------------------------------------------------------ losses
 def test_cosine_loss(golden):
     g = np.random.Generator(np.random.PCG64(11))
