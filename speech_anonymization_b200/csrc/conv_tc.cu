@@ -74,9 +74,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
@@ -97,15 +94,6 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
 // kind::f16 instruction descriptor: fp16 A/B (format 0), fp32 D, both K-major, M = 128.
 __device__ __forceinline__ uint32_t umma_idesc(int n) {
   return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                         uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
 }
 // Warp-converged variants: the whole warp executes them with identical operands and ONE elected lane issues. Keeping the
 // issuer's control flow warp-uniform lets ptxas hold descriptors in uniform registers; the same code under `if (lane == 0)`
@@ -152,21 +140,6 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
       : "r"(taddr)
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// lane l ends up with the sum over the warp's 32 lanes of v[l]  (31 shuffles instead of 32 x 5)
-__device__ __forceinline__ float warp_transpose_sum(float* v, int lane) {
-#pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
-    const bool up = (lane & off) != 0;
-#pragma unroll
-    for (int i = 0; i < off; ++i) {
-      const float send = up ? v[i] : v[i + off];
-      const float keep = up ? v[i + off] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-    }
-  }
-  return v[0];
 }
 
 // SiLU of two values given hh = x/2 as packed fp16:  x*sigmoid(x) = hh + hh*tanh(hh)  (one MUFU per pair)
@@ -434,7 +407,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // =========================== EPILOGUE ===========================
     // warp w: TMEM lanes (rows) 32*(w%4).., columns [(w/4)*COUT_V/2, +COUT_V/2)
     const float* ec = reinterpret_cast<const float*>(smem + L.epi);
-    float2* red = reinterpret_cast<float2*>(smem + L.red);
     const int quarter = warp & 3, chalf = warp >> 2;
     const int mloc = quarter * 32 + lane;
     constexpr int CPW = COUT_V / (TC_EPI_WARPS / 4);     // columns per warp
@@ -481,8 +453,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       if (p.trace && threadIdx.x == 0 && 2 * k < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k] = clock64();
       const uint32_t taddr = tmem_base + buf * (uint32_t)COUT_V + ((uint32_t)(quarter * 32) << 16);
       __half* out_h = reinterpret_cast<__half*>(p.out) + (int64_t)b * p.out_bstride;
-      float* out_f = reinterpret_cast<float*>(p.out) + (int64_t)b * p.out_bstride;
-#pragma unroll
+      // (rolled: the kernel's roles share a small instruction cache)
+#pragma unroll 1
       for (int cb = chalf * CPW; cb < (chalf + 1) * CPW; cb += 32) {
         float v[32];
         tmem_ld32(taddr + (uint32_t)cb, v);
@@ -520,49 +492,15 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
               *reinterpret_cast<uint4*>(out_h + (((int64_t)pl * p.out_plane_rows + row) << 3)) = o;
             }
           }
-        } else if (valid) {   // OUT_CHANNELS_FIRST_F32: [cout_v][rows_out] fp32, coalesced over the warp's rows
-#pragma unroll
-          for (int j = 0; j < 32; ++j) out_f[(int64_t)(cb + j) * p.rows_out + m] = v[j];
-        }
-        if (p.stats) {
-          // statistics of the values the consumer will read (fp16-rounded), rows past the end contribute zero
-          float q[32];
-#pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            const float2 f = __half22float2(__floats2half2_rn(v[j], v[j + 1]));
-            v[j] = valid ? f.x : 0.f;
-            v[j + 1] = valid ? f.y : 0.f;
-            q[j] = v[j] * v[j];
-            q[j + 1] = v[j + 1] * v[j + 1];
-          }
-          const float s_sum = warp_transpose_sum(v, lane);
-          const float s_sq = warp_transpose_sum(q, lane);
-          red[(buf * 4 + quarter) * COUT_V + cb + lane] = make_float2(s_sum, s_sq);
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
-      if (p.stats) {
-        epi_bar();   // red[buf] complete; it is rewritten two tiles later, i.e. after the next tile's barrier
-        for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_THREADS) {
-          float s = 0.f, q = 0.f;
-#pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            const float2 r = red[(buf * 4 + w) * COUT_V + c];
-            s += r.x;
-            q += r.y;
-          }
-          double* dst = p.stats + ((int64_t)b * p.cout_mod + (c % p.cout_mod)) * 2;
-          atomicAdd(dst + 0, (double)s);
-          atomicAdd(dst + 1, (double)q);
-        }
-      }
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
       tin += (int)gridDim.x;
       while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
     }
-    if (p.stats) __threadfence();
   }
 
   tc_fence_before();
@@ -572,35 +510,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_TMEM_COLS(COUT_V)) : "memory");
   }
 
-  // ---- the last CTA to finish turns the statistics into the next layer's InstanceNorm scale / shift
-  //      (nn.InstanceNorm1d(affine=True): biased variance, eps 1e-5) and clears them for the next chunk
-  if (p.fin_counter) {
-    __shared__ int is_last;
-    if (threadIdx.x == 0) {
-      __threadfence();
-      const unsigned ticket = atomicAdd(p.fin_counter, 1u);
-      is_last = ticket == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (is_last) {
-      __threadfence();
-      const int n = p.B * p.cout_mod;
-      for (int i = threadIdx.x; i < n; i += TC_THREADS) {
-        const int c = i % p.cout_mod;
-        const double sum = __ldcg(p.stats + 2 * i), sq = __ldcg(p.stats + 2 * i + 1);
-        const double mean = sum / p.fin_count;
-        double var = sq / p.fin_count - mean * mean;
-        if (var < 0.0) var = 0.0;
-        const float rstd = (float)(1.0 / sqrt(var + 1e-5));
-        const float sc = p.fin_gamma[c] * rstd;
-        p.fin_scale[i] = sc;
-        p.fin_shift[i] = p.fin_beta[c] - (float)mean * sc;
-        p.stats[2 * i] = 0.0;
-        p.stats[2 * i + 1] = 0.0;
-      }
-      if (threadIdx.x == 0) *p.fin_counter = 0u;
-    }
-  }
 }
 
 template <int COUT_V>
@@ -670,7 +579,8 @@ bool tapgemm_tc_supported(const TapGemmParams& p) {
   }
   if (p.tap_step < 1 || p.tap_kmax[p.ntaps - 1] % TC_STAGE_CH != 0 || p.tap_nmax[0] % 8 != 0) return false;
   if (p.out_fold == OUT_PAIR_FOLD && (p.rows_out & 1)) return false;
-  if (p.stats && p.out_mode != OUT_CHANNELS_LAST) return false;
+  if (p.stats || p.fin_counter) return false;               // statistics are a separate pass (instnorm_stats_kernel)
+  if (p.out_mode != OUT_CHANNELS_LAST) return false;        // fp16 chunk-planar output only
   return true;
 }
 

@@ -479,7 +479,6 @@ struct Ctx {
   const SpanonConvAEWeights* w;
   Workspace ws;
   bool tc;       // fp16 activations (+ tcgen05 where supported)
-  bool epi_stats; // $SPANON_EPI_STATS=1: InstanceNorm statistics in the tcgen05 epilogue instead of a separate pass
   int n_sm;
   int64_t L;
   cudaStream_t st;
@@ -551,13 +550,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.in_planar = c.tc ? 1 : 0;
   p.B = nb;
   p.tag = kLayerTag[id];
-  const bool split_stats = on_tc && io.out_stats >= 0 && !c.epi_stats;
-  if (on_tc && io.out_stats >= 0 && c.epi_stats) {  // statistics in the epilogue, finalize by the last CTA
-    p.fin_counter = c.ws.counter;
-    p.fin_gamma = io.fin_gamma; p.fin_beta = io.fin_beta;
-    p.fin_scale = c.ws.in_scale[io.out_stats]; p.fin_shift = c.ws.in_shift[io.out_stats];
-    p.fin_count = io.fin_count;
-  }
+  const bool split_stats = on_tc && io.out_stats >= 0;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
@@ -638,10 +631,6 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   const size_t esize = c.tc ? 2 : 4;
   carve(c.ws, base, chunk, L, c.tc, esize);
   c.w = w; c.L = L; c.st = as_stream(stream);
-  {
-    const char* e = getenv("SPANON_EPI_STATS");
-    c.epi_stats = e && e[0] == '1';
-  }
 
   {
     int dev = 0;
