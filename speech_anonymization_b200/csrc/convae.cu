@@ -83,6 +83,14 @@ __global__ void bn_fold_kernel(SpanonBatchNorm bn, int C, float* __restrict__ sc
   }
 }
 
+// D += A * B for one m16n8k16 fp16 tile with fp32 accumulation (legacy warp-level MMA; the tensor pipe is idle here)
+__device__ __forceinline__ void mma16816(float* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
 // nn.InstanceNorm1d(affine=True): biased variance over the sequence, eps 1e-5
 __global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
                                          const float* __restrict__ beta, int B, int C, double count,
@@ -106,14 +114,6 @@ __global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const
 // the block reduces through shuffles + shared memory and adds to stats[b][c][2] (fp64); instnorm_finalize_kernel then
 // converts the sums to scale/shift.  HBM/L2-bound: one read of the plane.
 constexpr int ST_NT = 256, ST_ROWS = 32;   // rows per thread
-
-// D += A * B for one m16n8k16 fp16 tile with fp32 accumulation (legacy warp-level MMA; the tensor pipe is idle here)
-__device__ __forceinline__ void mma16816(float* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
-                                         uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
 
 // The per-element work of the obvious loop (2 cvt + add + fma per value) made this pass issue-bound at ~50 % of HBM
 // speed, so the sums are formed on the tensor pipe instead.  A lane holds two rows (16 B = 4 channel pairs each).
@@ -258,6 +258,84 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
         r.x = *reinterpret_cast<uint32_t*>(&h0); r.y = *reinterpret_cast<uint32_t*>(&h1);
         r.z = *reinterpret_cast<uint32_t*>(&h2); r.w = *reinterpret_cast<uint32_t*>(&h3);
         *o4 = r;
+      }
+    }
+  }
+}
+
+// Tensor-pipe form of encoder.0 for the fp16 path.  The CUDA-core kernel above issues 480 FMAs per output row and is
+// issue-bound at ~1.5 TB/s of output; here a warp computes 32 rows x 32 channels with warp-level MMAs over a Toeplitz
+// view of the signal:  A[i][t] = x[l + i + t - 7]  (16 x 16, tap 15 is a zero weight),  B[t][c] = w[c][t] / 2.
+// Because consecutive taps are consecutive samples, an A fragment register is just two neighbouring samples: three
+// 32-bit shared-memory loads per 16 rows (a second copy of the signal shifted by one sample keeps odd rows aligned).
+// The accumulators start at bias/2, so the MMA result is h = y/2 and SiLU(y) = h + h*tanh(h) (one MUFU per value).
+__global__ void __launch_bounds__(FL_NT)
+first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64_t n_valid, int L, int F,
+                       const float* __restrict__ norm_mean, const float* __restrict__ norm_std,
+                       const int32_t* __restrict__ utt_max, float top_db, const float* __restrict__ w /*[32][1][15]*/,
+                       const float* __restrict__ bias, __half* __restrict__ out, int64_t out_bstride) {
+  __shared__ __align__(16) __half sh[2][FL_NT + 32];    // sh[0][i] = x[l0 - 7 + i], sh[1][i] = x[l0 - 6 + i]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, b = blockIdx.y;
+  const int l0 = blockIdx.x * FL_NT;
+  const float* x = feats + (int64_t)b * feats_bstride;
+  const float floor_db = utt_max ? key_to_float(utt_max[b]) - top_db : -INFINITY;
+  for (int i = tid; i < FL_NT + 32; i += FL_NT) {
+    const int l = l0 - 7 + i;
+    float v = 0.f;
+    if (l >= 0 && l < L && (int64_t)l < n_valid) {
+      v = __ldg(x + l);
+      if (norm_mean) {
+        const int f = l % F;
+        v = (fmaxf(v, floor_db) - __ldg(norm_mean + f)) / __ldg(norm_std + f);
+      }
+    }
+    const __half hv = __float2half_rn(v);
+    sh[0][i] = hv;
+    if (i > 0) sh[1][i - 1] = hv;
+  }
+  const int g = lane >> 2, t4 = lane & 3;
+  uint32_t bw[4][2];       // B fragments: channel 8*nt + g, taps (2*t4, 2*t4+1) and (2*t4+8, 2*t4+9)
+  float bz[4][2];          // bias/2 of channels 8*nt + 2*t4, +1 (accumulator columns)
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    const float* wc = w + (8 * nt + g) * 15;
+    const int ta = 2 * t4, tb = 2 * t4 + 8;
+    const __half2 lo = __floats2half2_rn(0.5f * __ldg(wc + ta), 0.5f * __ldg(wc + ta + 1));
+    const __half2 hi = __floats2half2_rn(0.5f * __ldg(wc + tb), tb + 1 < 15 ? 0.5f * __ldg(wc + tb + 1) : 0.f);
+    bw[nt][0] = *reinterpret_cast<const uint32_t*>(&lo);
+    bw[nt][1] = *reinterpret_cast<const uint32_t*>(&hi);
+    bz[nt][0] = 0.5f * __ldg(bias + 8 * nt + 2 * t4);
+    bz[nt][1] = 0.5f * __ldg(bias + 8 * nt + 2 * t4 + 1);
+  }
+  __syncthreads();
+  __half* ob = out + (int64_t)b * out_bstride;
+  const int64_t plane_rows = L >> 1;
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+    const int base = warp * 32 + mt * 16;              // first row of this 16-row tile inside the block
+    const int e = base + g + 2 * t4;                   // sample index of (row g, tap 2*t4)
+    const uint32_t* src = reinterpret_cast<const uint32_t*>((e & 1) ? &sh[1][e - 1] : &sh[0][e]);
+    const uint32_t a0 = src[0], a12 = src[4], a3 = src[8];   // samples e.., e+8.., e+16..
+    float acc[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      acc[nt][0] = bz[nt][0]; acc[nt][1] = bz[nt][1]; acc[nt][2] = bz[nt][0]; acc[nt][3] = bz[nt][1];
+      mma16816(acc[nt], a0, a12, a12, a3, bw[nt][0], bw[nt][1]);
+    }
+#pragma unroll
+    for (int hr = 0; hr < 2; ++hr) {                   // rows g and g + 8
+      const int l = l0 + base + g + 8 * hr;
+      if (l < L) {
+        // fp16 planes are chunk-planar in the CONSUMER's view (encoder.2, stride 2): plane (l & 1) * 4 + q, row l >> 1
+        __half* o = ob + ((((int64_t)(l & 1) * 4) * plane_rows + (l >> 1)) << 3) + 2 * t4;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          __half2 hh = __floats2half2_rn(acc[nt][2 * hr], acc[nt][2 * hr + 1]);
+          uint32_t th, in = *reinterpret_cast<uint32_t*>(&hh);
+          asm("tanh.approx.f16x2 %0, %1;" : "=r"(th) : "r"(in));
+          hh = __hfma2(hh, *reinterpret_cast<__half2*>(&th), hh);
+          *reinterpret_cast<__half2*>(o + ((int64_t)nt * plane_rows << 3)) = hh;
+        }
       }
     }
   }
@@ -675,9 +753,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
       const int32_t* um = utt_max ? utt_max + b0 : nullptr;
       if (c.tc)
-        first_layer_kernel<__half, true><<<grid, FL_NT, 0, c.st>>>(
-            src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um, top_db, w->enc_w[0], w->enc_b[0],
-            (__half*)X[0], L * 32);
+        first_layer_mma_kernel<<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um,
+                                                         top_db, w->enc_w[0], w->enc_b[0], (__half*)X[0], L * 32);
       else
         first_layer_kernel<float, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
                                                                    norm_mean, norm_std, um, top_db, w->enc_w[0],
