@@ -299,10 +299,21 @@ def run_ours(a):
         flops_step = sum(fl.values()) * B
         achieved = flops_step / (conv_ms * 1e-3) / 1e12
         peak = pk["tf_sust"]
+        traffic, tsrc = None, None       # DRAM bytes per launch from the committed ncu --set full capture (batch 60)
+        tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
+        if os.path.exists(tp):
+            tj = json.load(open(tp))
+            traffic = tj["conv_stack"]["traffic_mb_per_launch"] * 1e6 * B / 60.0
+            tsrc = "profiles/r01_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, avg over the 13 conv launches)"
+        ms_launch = conv_ms / max(conv_launches, 1)
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "conv stack (first_layer + tap-GEMM launches)",
-                "flops_per_launch": flops_step / max(conv_launches, 1), "ms_per_launch": conv_ms / max(conv_launches, 1),
-                "share_of_step": conv_ms / prof_ms, "peak_source": pk["src"] + " bf16 sustained"}
+                "traffic": traffic, "traffic_source": tsrc, "kernel": "conv stack (first_layer + tap-GEMM launches)",
+                "flops_per_launch": flops_step / max(conv_launches, 1), "ms_per_launch": ms_launch,
+                "share_of_step": conv_ms / prof_ms, "peak_source": pk["src"] + " bf16 sustained",
+                # the fp16 planes of a 60-utterance chunk do not fit L2, so every launch also streams them through HBM
+                "hbm_cross_check": None if traffic is None else {
+                    "GB/s": traffic / (ms_launch * 1e-3) / 1e9, "peak": pk["hbm"],
+                    "frac": traffic / (ms_launch * 1e-3) / 1e9 / pk["hbm"]}}
     else:
         km = kern.get("fbank400_kernel", {"ms_per_step": float("nan"), "launches_per_step": 1})
         achieved = BYTES_FBANK_UTT * B / (km["ms_per_step"] / km["launches_per_step"] * 1e-3) / 1e9
