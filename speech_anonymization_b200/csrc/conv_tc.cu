@@ -267,8 +267,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // Inside a group, warp h handles chunks 2h, 2h+1 of the stage; lanes are rows (conflict-free 16 B accesses).
     const int xw = warp - TC_EPI_WARPS;
     const int grp = xw >> 1, ch0 = (xw & 1) * 2;
-    const bool has_t1 = p.t1_scale != nullptr, has_t2 = p.t2_scale != nullptr, do_silu = p.silu != 0;
-    const bool ident = !has_t1 && !has_t2 && !do_silu;
+    const bool has_t1 = p.t1_scale != nullptr, has_t2 = p.t2_scale != nullptr, do_silu = p.silu == 1, do_relu = p.silu == 2;
+    const bool ident = !has_t1 && !has_t2 && !do_silu && !do_relu;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
     const int s_fix = grp % n_stage_tile;                      // stage-in-tile of this group (n_stage_tile is 1, 2 or 4)
     const int kstep = TC_XF_GROUPS / n_stage_tile;             // tiles between two stages of this group
@@ -284,8 +284,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       if (!ident) {   // constants of this thread's 16 channels; the loads overlap the wait below
         const int cm = (s_fix * TC_STAGE_CH + ch0 * 8) % p.cin_mod;
         if (has_t1) {
-          const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.cin_mod + cm);
-          const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.cin_mod + cm);
+          const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.t1_bstride + cm);
+          const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.t1_bstride + cm);
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const float4 a = __ldg(sp + q), c = __ldg(hp + q);
@@ -332,6 +332,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
               f.y = fmaf(f.y, s1[8 * c + 2 * j + 1], h1[8 * c + 2 * j + 1]);
               __half2 y = __floats2half2_rn(f.x, f.y);
               if (do_silu) y = silu_from_half(y);
+              if (do_relu) y = __hmax2(y, __float2half2_rn(0.f));
               if (has_t2) y = __hfma2(y, s2[4 * c + j], h2[4 * c + j]);    // folded eval-mode BatchNorm
               hv[j] = y;
             }
@@ -458,10 +459,12 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       for (int cb = chalf * CPW; cb < (chalf + 1) * CPW; cb += 32) {
         float v[32];
         tmem_ld32(taddr + (uint32_t)cb, v);
+        if (p.bias) {   // (a bias in front of an InstanceNorm is a no-op and is dropped by the caller)
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 bz = *reinterpret_cast<const float4*>(ec + cb + j);
-          v[j] += bz.x; v[j + 1] += bz.y; v[j + 2] += bz.z; v[j + 3] += bz.w;
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bz = *reinterpret_cast<const float4*>(ec + cb + j);
+            v[j] += bz.x; v[j + 1] += bz.y; v[j + 2] += bz.z; v[j + 3] += bz.w;
+          }
         }
         if (p.relu) {
 #pragma unroll

@@ -420,15 +420,19 @@ clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise
 // eight-round conflict-free shared-memory fold and one fp64 atomic pair per column.
 constexpr int PL_NT = 256, PL_ROWS = 32;
 __global__ void __launch_bounds__(PL_NT)
-pool_planar_kernel(const __half* __restrict__ x, int P, int R, double* __restrict__ pool) {
+pool_planar_kernel(const __half* __restrict__ x, int P, int R, const float* __restrict__ bias,
+                   const float* __restrict__ bn_scale, const float* __restrict__ bn_shift, double* __restrict__ pool) {
   __shared__ float part[2][8][128];
   __shared__ float bins[2][128];
   const int tid = threadIdx.x, p = blockIdx.y, b = blockIdx.z;
   const uint4* base = reinterpret_cast<const uint4*>(x) + ((int64_t)b * P + p) * R;
   const int r0 = blockIdx.x * (PL_NT * PL_ROWS);
-  float s[8], q[8];
+  float s[8], q[8], cb[8], cs[8], ch[8];   // the plane holds the raw tdnn.6 conv: ReLU(x + bias) * bn_scale + bn_shift here
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
+  for (int j = 0; j < 8; ++j) {
+    s[j] = 0.f; q[j] = 0.f;
+    cb[j] = __ldg(bias + 8 * p + j); cs[j] = __ldg(bn_scale + 8 * p + j); ch[j] = __ldg(bn_shift + 8 * p + j);
+  }
 #pragma unroll 8
   for (int i = 0; i < PL_ROWS; ++i) {
     const int r = r0 + i * PL_NT + tid;
@@ -437,7 +441,9 @@ pool_planar_kernel(const __half* __restrict__ x, int P, int R, double* __restric
       const __half2* h = reinterpret_cast<const __half2*>(&v);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 f = __half22float2(h[j]);
+        float2 f = __half22float2(h[j]);
+        f.x = fmaf(fmaxf(f.x + cb[2 * j], 0.f), cs[2 * j], ch[2 * j]);
+        f.y = fmaf(fmaxf(f.y + cb[2 * j + 1], 0.f), cs[2 * j + 1], ch[2 * j + 1]);
         s[2 * j] += f.x; s[2 * j + 1] += f.y;
         q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
       }
@@ -511,6 +517,7 @@ struct Workspace {
   // carved in this order from the caller's buffer (all 256-byte aligned)
   void* packed[N_LAYERS];
   float* bn_scale[4]; float* bn_shift[4];      // clf norm, tdnn bn 0..2
+  float* ones;                                 // [128] 1.0f (unit scale of a bias-only affine on load)
   double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
   float* in_scale[6]; float* in_shift[6];      // [chunk][C]
   double* pool;                                // [chunk][128][2]
@@ -540,6 +547,7 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
     ws.packed[i] = take((size_t)s.ntaps * s.cin_v * std::max(s.cout_v, 16) * 4);
   }
   for (int i = 0; i < 4; ++i) { ws.bn_scale[i] = (float*)take(128 * 4); ws.bn_shift[i] = (float*)take(128 * 4); }
+  ws.ones = (float*)take(128 * 4);
   // stats are contiguous so one memset clears them
   for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * kInC[i] * 2 * sizeof(double));
   ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
@@ -591,6 +599,9 @@ struct LayerIO {
   const float* fin_beta = nullptr;
   double fin_count = 0.0;
   int out_fold = OUT_DIRECT;         // fp16 mode: how the consumer views this layer's output planes
+  const float* t1s = nullptr;        // tcgen05 path: per-channel affine on load (overrides in_norm), e.g. the
+  const float* t1h = nullptr;        //   producer's bias as (ones, bias)
+  int act = -1;                      // activation on load (TapGemmParams::silu); -1 = SiLU iff in_norm >= 0
 };
 
 int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
@@ -616,7 +627,10 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   if (s.mode == PACK_CONV_S2) p.tap_kmax[s.ntaps - 1] = s.cin;   // tap (2*tap+1) = 5 does not exist
   if (s.mode == PACK_CONVT_S2) p.tap_nmax[0] = s.cout;            // shift -1 only feeds the even phase
   p.w = c.ws.packed[id];
+  p.t1_bstride = s.cin;
   if (io.in_norm >= 0) { p.t1_scale = c.ws.in_scale[io.in_norm]; p.t1_shift = c.ws.in_shift[io.in_norm]; p.silu = 1; }
+  if (io.t1s) { p.t1_scale = io.t1s; p.t1_shift = io.t1h; p.t1_bstride = 0; }
+  if (io.act >= 0) p.silu = io.act;
   if (io.t2_bn >= 0) { p.t2_scale = c.ws.bn_scale[io.t2_bn]; p.t2_shift = c.ws.bn_shift[io.t2_bn]; }
   p.bias = io.bias;
   p.relu = io.relu;
@@ -730,6 +744,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_TRY(pack_layer(c, L_TD0, w->tdnn_w[0]));
     SPANON_TRY(pack_layer(c, L_TD3, w->tdnn_w[1]));
     SPANON_TRY(pack_layer(c, L_TD6, w->tdnn_w[2]));
+    SPANON_TRY(fill_i32(reinterpret_cast<int32_t*>(c.ws.ones), 128, 0x3F800000, c.st));   // 1.0f
     bn_fold_kernel<<<1, 128, 0, c.st>>>(w->clf_norm, 128, c.ws.bn_scale[0], c.ws.bn_shift[0]);
     SPANON_TRY(check_launch("bn_fold_kernel"));
     for (int i = 0; i < 3; ++i) {
@@ -761,26 +776,39 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
                                                                    w->enc_b[0], (float*)X[0], L * 32);
       SPANON_TRY(check_launch("first_layer_kernel"));
     }
+    // A bias in front of an InstanceNorm only moves the mean the norm removes again: the tcgen05 path drops it (nb_).
+    // Its TDNN layers store the raw convolution; bias + ReLU + BatchNorm run in the CONSUMER's operand transform
+    // (eight otherwise idle warps) instead of the four epilogue warps.
+    const bool tcp = c.tc;
+    auto nb_ = [&](const float* bias) { return tcp ? nullptr : bias; };
     //                         in    out   in_norm t2  bias          relu e_bn stats out_mode
-    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, w->enc_b[1], 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2}, nb));
+    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, nb_(w->enc_b[1]), 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2}, nb));
     SPANON_TRY(finalize_in(c, L_ENC2, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, w->enc_b[2], 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
+    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, nb_(w->enc_b[2]), 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
                                      OUT_PAIR_FOLD}, nb));
     SPANON_TRY(finalize_in(c, L_ENC5, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, w->enc_b[3], 0, -1, 2, OUT_CHANNELS_LAST, w->enc_in_w[2], w->enc_in_b[2], (double)L4}, nb));
+    SPANON_TRY(run_layer(c, L_ENC8, {X[2], X[3], 1, -1, nb_(w->enc_b[3]), 0, -1, 2, OUT_CHANNELS_LAST, w->enc_in_w[2], w->enc_in_b[2], (double)L4}, nb));
     SPANON_TRY(finalize_in(c, L_ENC8, 2, w->enc_in_w[2], w->enc_in_b[2], nb, (double)L4));
-    SPANON_TRY(run_layer(c, L_ENC11, {X[3], X[0], 2, -1, w->enc_b[4], 0, -1, 3, OUT_CHANNELS_LAST, w->enc_in_w[3], w->enc_in_b[3], (double)L4}, nb));
+    SPANON_TRY(run_layer(c, L_ENC11, {X[3], X[0], 2, -1, nb_(w->enc_b[4]), 0, -1, 3, OUT_CHANNELS_LAST, w->enc_in_w[3], w->enc_in_b[3], (double)L4}, nb));
     SPANON_TRY(finalize_in(c, L_ENC11, 3, w->enc_in_w[3], w->enc_in_b[3], nb, (double)L4));
     // X[0] = raw encoder.11 output; the bottleneck is SiLU(IN(X[0])), applied by both consumers on load
     if (run_clf) {
-      SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
-      SPANON_TRY(run_layer(c, L_TD3, {X[1], X[2], -1, -1, w->tdnn_b[1], 1, 2, -1, OUT_CHANNELS_LAST}, nb));
       const int64_t L3 = L4 - 14;
-      if (c.tc) {   // fp16 planes (X[3] is free here), pooled by the planar kernel: half the bytes of the fp32 image
-        SPANON_TRY(run_layer(c, L_TD6, {X[2], X[3], -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_LAST}, nb));
-        dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);
-        pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, c.ws.pool);
+      if (c.tc) {
+        LayerIO t0{X[0], X[1], 3, 0, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
+        SPANON_TRY(run_layer(c, L_TD0, t0, nb));
+        LayerIO t3{X[1], X[2], -1, 1, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
+        t3.t1s = c.ws.ones; t3.t1h = w->tdnn_b[0]; t3.act = 2;     // ReLU(x + b0) -> BatchNorm 1
+        SPANON_TRY(run_layer(c, L_TD3, t3, nb));
+        LayerIO t6{X[2], X[3], -1, 2, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};   // fp16 planes (X[3] is free here)
+        t6.t1s = c.ws.ones; t6.t1h = w->tdnn_b[1]; t6.act = 2;     // ReLU(x + b1) -> BatchNorm 2
+        SPANON_TRY(run_layer(c, L_TD6, t6, nb));
+        dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);   // ReLU(x + b2) -> BatchNorm 3 -> pooling
+        pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, w->tdnn_b[2], c.ws.bn_scale[3],
+                                                   c.ws.bn_shift[3], c.ws.pool);
       } else {
+        SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
+        SPANON_TRY(run_layer(c, L_TD3, {X[1], X[2], -1, -1, w->tdnn_b[1], 1, 2, -1, OUT_CHANNELS_LAST}, nb));
         SPANON_TRY(run_layer(c, L_TD6, {X[2], c.ws.tdnn_out, -1, -1, w->tdnn_b[2], 1, 3, -1, OUT_CHANNELS_FIRST_F32}, nb));
         const int64_t n_el = 128 * L3;
         dim3 pg((unsigned)std::min<int64_t>(ceil_div(n_el, 256 * 16), 256), (unsigned)nb);
@@ -792,11 +820,11 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, w->dec_b[1], 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2,
+    SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, nb_(w->dec_b[1]), 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2,
                                      OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC1, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
     SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, w->dec_b[3], 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
+    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, nb_(w->dec_b[3]), 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
                                      OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
     SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));

@@ -50,7 +50,8 @@ struct TapGemmParams {
   int tap_nmax[MAX_TAPS];  // output columns (of cout_v) with non-zero weights (transposed conv: first tap half)
   const void* w;       // packed weights (layout depends on the kernel family)
   const float* t1_scale; const float* t1_shift;  // [B][cin_mod] or null
-  int silu;
+  int64_t t1_bstride;  // tcgen05 kernel: elements between utterances of t1_* (0 = per-channel constants shared by all)
+  int silu;                // activation on load: 0 none, 1 SiLU, 2 ReLU (2: tcgen05 kernel only)
   const float* t2_scale; const float* t2_shift;  // [cin_mod] or null
   const float* bias;   // [cout_mod]
   int relu;
