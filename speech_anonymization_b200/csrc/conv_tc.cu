@@ -34,14 +34,16 @@ namespace {
 
 constexpr int TC_M = 128;                 // rows per tile = UMMA M
 constexpr int TC_EPI_WARPS = 4;           // one warp per TMEM lane quarter (448 threads per CTA -> 144 registers per thread)
-constexpr int TC_XF_WARPS = 8;
-constexpr int TC_XF_GROUPS = 4;           // transform groups (two warps each), one stage in flight per group
+constexpr int TC_XF_WARPS = 8;            // transform warps; warp w owns the stages it == w (mod 8), one stage in flight each
 constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_XF_WARPS;
 constexpr int TC_LOAD_WARP = TC_MMA_WARP + 1;
-constexpr int TC_THREADS = (TC_LOAD_WARP + 1) * 32;
+constexpr int TC_LOAD_WARPS = 2;          // loader l issues the stages it == l (mod 2): a lone warp needs ~300 cycles per stage
+constexpr int TC_THREADS = (TC_LOAD_WARP + TC_LOAD_WARPS) * 32;
 constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32;
-constexpr int TC_STAGE_CH = 32;           // input channels per A stage (two K=16 MMA steps)
-constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
+constexpr int TC_MAX_STAGES = 16;
+// operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
+enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4 };
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
 constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
@@ -78,6 +80,23 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
+}
+// Warp-converged forms (one elected lane issues, operands warp-uniform so they stay in uniform registers; a lane-dependent
+// UBLKCP compiles to a serialising loop over the active lanes, ~250 cycles per copy)
+__device__ __forceinline__ void bulk_g2s_elect(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_elect(uint32_t bar, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes)
+      : "memory");
 }
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory"); }
 
@@ -163,24 +182,24 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.w_bytes = (uint32_t)ntaps * cin_v * cout_v * 2u;
   L.w = 0;
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
-  L.red = L.epi + 3u * cout_v * 4u;                   // [2 tile parities][4 lane quarters][cout_v] float2 partial sums
-  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : 2u * 4u * (uint32_t)cout_v * 8u);   // (Toeplitz: 2 x [128][17] fp32)
+  L.red = L.epi + 3u * cout_v * 4u;                   // Toeplitz epilogue only: 2 x [128][17] fp32 copies of the tile
+  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : 0u);
   L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
   L.n_stages = ns > TC_MAX_STAGES ? TC_MAX_STAGES : ns;
-  // a multiple of the number of transform groups: every ring slot then belongs to ONE group, so each slot's mbarriers
+  // a multiple of the number of transform warps: every ring slot then belongs to ONE warp, so each slot's mbarriers
   // are waited on in order by a single consumer (a waiter two phases behind would alias the parity)
-  L.n_stages = L.n_stages / TC_XF_GROUPS * TC_XF_GROUPS;
+  L.n_stages = L.n_stages / TC_XF_WARPS * TC_XF_WARPS;
   L.total = L.a + (uint32_t)L.n_stages * L.stage_bytes;
   return L;
 }
 
-// barrier slots (8 B each): [0,8) raw (bulk copy landed), [8,16) full (transformed), [16,24) empty (MMAs read it),
-// [24,26) tmem_full, [26,28) tmem_empty, 28 weights; 30 = TMEM base pointer
-enum { B_RAW = 0, B_FULL = 8, B_EMPTY = 16, B_TFULL = 24, B_TEMPTY = 26, B_W = 28, B_TPTR = 30 };
+// barrier slots (8 B each): [0,16) raw (bulk copy landed), [16,32) full (transformed), [32,48) empty (MMAs read it),
+// [48,50) tmem_full, [50,52) tmem_empty, 52 weights; 54 = TMEM base pointer
+enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54 };
 
-template <int COUT_V>
+template <int COUT_V, int XF>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -191,14 +210,17 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   const uint32_t bar0 = s_base + L.bars;
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(bars + B_TPTR);
-  const int n_stage_tile = p.cin_v / TC_STAGE_CH;
-  const int n_my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int n_stage_tile = p.cin_v / TC_STAGE_CH;     // 2, 4 or 8
+  // contiguous run of tiles per CTA: consecutive tiles of one utterance share halo rows (L2) and the per-utterance
+  // InstanceNorm constants, which a transform warp then reloads only when the utterance changes
+  const int t_begin = (int)((int64_t)blockIdx.x * total_tiles / (int64_t)gridDim.x);
+  const int n_my_tiles = (int)((int64_t)(blockIdx.x + 1) * total_tiles / (int64_t)gridDim.x) - t_begin;
 
   if (warp == TC_MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < L.n_stages; ++i) {
         mbar_init(BAR(B_RAW + i), 1);
-        mbar_init(BAR(B_FULL + i), TC_XF_WARPS / TC_XF_GROUPS);
+        mbar_init(BAR(B_FULL + i), 1);
         mbar_init(BAR(B_EMPTY + i), 1);
       }
       for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), TC_EPI_WARPS); }
@@ -232,140 +254,142 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int planes_in = p.cin_v / 8;
 
-  if (warp == TC_LOAD_WARP) {
+  if (warp >= TC_LOAD_WARP) {
     // =========================== LOADER ===========================
-    // lanes 0..3 each own one 8-channel chunk of the stage (one bulk copy per chunk and stage)
+    // two bulk copies per stage (one per 8-channel chunk), issued by one elected lane of the converged warp
     {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
-      uint32_t stage = 0, ph = 0;
-      int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
+      const int lw = warp - TC_LOAD_WARP;
+      uint32_t stage = (uint32_t)lw, ph = 0;
+      int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
       for (int k = 0; k < n_my_tiles; ++k) {
         const int g0 = tin * tile_step - halo_lo;                      // global row of slab row 0
         const int lo = g0 < 0 ? -g0 : 0;                               // first valid slab row
         const int hi = min(slab_used, p.rows_in - g0);                 // one past the last valid slab row
         const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
-        const __half* src = in_base + (((int64_t)b * planes_in + lane) * p.rows_in + (g0 + lo)) * 8;
-        for (int s = 0; s < n_stage_tile; ++s) {
+        const int64_t plane_stride = (int64_t)p.rows_in * 8;
+        const __half* src = in_base + (((int64_t)b * planes_in + lw * (TC_STAGE_CH / 8)) * p.rows_in + (g0 + lo)) * 8;
+        for (int s = lw; s < n_stage_tile; s += TC_LOAD_WARPS) {
           mbar_wait(BAR(B_EMPTY + stage), ph ^ 1u);
           if (p.trace && lane == 0 && k * n_stage_tile + s < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 3) * TRACE_N + k * n_stage_tile + s] = clock64();
-          if (lane == 0) mbar_expect_tx(BAR(B_RAW + stage), bytes * (TC_STAGE_CH / 8));
-          __syncwarp();
-          if (lane < TC_STAGE_CH / 8 && bytes)
-            bulk_g2s(s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u + (uint32_t)lane * L.lbo_a, src, bytes,
-                     BAR(B_RAW + stage));
-          src += (int64_t)(TC_STAGE_CH / 8) * p.rows_in * 8;
-          if (++stage == (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
+          mbar_expect_tx_elect(BAR(B_RAW + stage), bytes * (TC_STAGE_CH / 8));
+          if (bytes) {
+            const uint32_t dst = s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u;
+            bulk_g2s_elect(dst, src, bytes, BAR(B_RAW + stage));
+            bulk_g2s_elect(dst + L.lbo_a, src + plane_stride, bytes, BAR(B_RAW + stage));
+          }
+          src += (int64_t)(TC_LOAD_WARPS * TC_STAGE_CH / 8) * plane_stride;
+          stage += TC_LOAD_WARPS;
+          if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
         }
-        tin += (int)gridDim.x;
-        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+        if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
     }
   } else if (warp >= TC_EPI_WARPS && warp < TC_MMA_WARP) {
     // =========================== TRANSFORM (in place) ===========================
-    // Four groups of two warps; group g owns the stages it == g (mod 4), so four stages are in flight at once and the
-    // per-stage chain (mbarrier wait -> LDS -> math -> STS -> proxy fence -> arrive) is off the critical path.
-    // Inside a group, warp h handles chunks 2h, 2h+1 of the stage; lanes are rows (conflict-free 16 B accesses).
+    // Eight warps; warp w owns the stages it == w (mod 8) (16 channels = two 8-channel chunks x slab rows), so eight
+    // stages are in flight and the per-stage chain (mbarrier wait -> LDS -> math -> STS -> proxy fence -> arrive) is
+    // off the critical path.  Lanes are rows (conflict-free 16 B accesses).  All arithmetic is packed fp16:
+    //   y = x*s1 + h1 (InstanceNorm affine, halved when SiLU follows)  ->  SiLU: y + y*tanh(y)  |  ReLU
+    //   -> y*s2 + h2 (folded eval-mode BatchNorm of the producer)
+    // i.e. per 8 elements 4 HFMA2 + 4 MUFU + 4 HFMA2 (+ 4 HFMA2).  Rows outside the utterance (= the conv's zero
+    // padding of the already activated tensor) exist only in an utterance's first / last tile and are zeroed there.
     const int xw = warp - TC_EPI_WARPS;
-    const int grp = xw >> 1, ch0 = (xw & 1) * 2;
-    const bool has_t1 = p.t1_scale != nullptr, has_t2 = p.t2_scale != nullptr, do_silu = p.silu == 1, do_relu = p.silu == 2;
-    const bool ident = !has_t1 && !has_t2 && !do_silu && !do_relu;
+    constexpr bool do_silu = (XF & 3) == XF_SILU, do_relu = (XF & 3) == XF_RELU, has_t2 = (XF & XF_T2) != 0;
+    constexpr bool ident = XF == XF_IDENT;
+    const bool has_t1 = p.t1_scale != nullptr;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
-    const int s_fix = grp % n_stage_tile;                      // stage-in-tile of this group (n_stage_tile is 1, 2 or 4)
-    const int kstep = TC_XF_GROUPS / n_stage_tile;             // tiles between two stages of this group
-    int k = grp / n_stage_tile;
-    uint32_t stage = (uint32_t)grp % (uint32_t)L.n_stages, ph = ((uint32_t)grp / (uint32_t)L.n_stages) & 1u;
-    int tile = (int)blockIdx.x + k * (int)gridDim.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
+    const int s_fix = xw % n_stage_tile;                       // stage-in-tile of this warp (n_stage_tile is 2, 4 or 8)
+    const int kstep = TC_XF_WARPS / n_stage_tile;              // tiles between two stages of this warp
+    int k = xw / n_stage_tile;
+    uint32_t stage = (uint32_t)xw, ph = 0;                     // n_stages is 8 or 16
+    int b = (t_begin + k) / tiles_per_utt, tin = (t_begin + k) - b * tiles_per_utt;
+    const int cm = (s_fix * TC_STAGE_CH) % p.cin_mod;          // this warp's 16 channels
+    __half2 s1[8], h1[8], s2[8], h2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s1[j] = __float2half2_rn(pre); h1[j] = __float2half2_rn(0.f); s2[j] = s1[j]; h2[j] = h1[j]; }
+    if (has_t2) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
+        h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
+      }
+    }
+    int b_const = -1;                                          // utterance whose t1 constants are in registers
     for (; k < n_my_tiles; k += kstep) {
       const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
       const int hi = min(slab_used, p.rows_in - g0);
-      float s1[16], h1[16];
-      __half2 s2[8], h2[8];
-      if (!ident) {   // constants of this thread's 16 channels; the loads overlap the wait below
-        const int cm = (s_fix * TC_STAGE_CH + ch0 * 8) % p.cin_mod;
-        if (has_t1) {
-          const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.t1_bstride + cm);
-          const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.t1_bstride + cm);
+      if (!ident && has_t1 && b_const != b && (b_const < 0 || p.t1_bstride != 0)) {
+        const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.t1_bstride + cm);
+        const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.t1_bstride + cm);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 a = __ldg(sp + q), c = __ldg(hp + q);
-            s1[4 * q] = a.x * pre; s1[4 * q + 1] = a.y * pre; s1[4 * q + 2] = a.z * pre; s1[4 * q + 3] = a.w * pre;
-            h1[4 * q] = c.x * pre; h1[4 * q + 1] = c.y * pre; h1[4 * q + 2] = c.z * pre; h1[4 * q + 3] = c.w * pre;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) { s1[j] = pre; h1[j] = 0.f; }
+        for (int q = 0; q < 4; ++q) {
+          const float4 a = __ldg(sp + q), c = __ldg(hp + q);
+          s1[2 * q] = __floats2half2_rn(a.x * pre, a.y * pre); s1[2 * q + 1] = __floats2half2_rn(a.z * pre, a.w * pre);
+          h1[2 * q] = __floats2half2_rn(c.x * pre, c.y * pre); h1[2 * q + 1] = __floats2half2_rn(c.z * pre, c.w * pre);
         }
-        if (has_t2) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
-            h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
-          }
-        }
+        b_const = b;
       }
       mbar_wait(BAR(B_RAW + stage), ph);
       const int it = k * n_stage_tile + s_fix;
-      if (p.trace && (xw & 1) == 0 && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
-      unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)ch0 * L.lbo_a;
+      if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
+      unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)lane * 16u;
+      if (!ident) {
+        const bool tail = lane + 128 < slab_used;    // the halo rows beyond the first 128 (slab_used <= 160)
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        // branch-free over the five row slots of this lane so the loads / MUFU ops of different rows overlap
-        uint4 v[5];
-        bool act[5], inb[5];
+        for (int c = 0; c < 2; ++c) {
+          unsigned char* cb = base + (uint32_t)c * L.lbo_a;
+          uint4 v[5];
 #pragma unroll
-        for (int q = 0; q < 5; ++q) {
-          const int r = lane + q * 32;
-          act[q] = r < slab_used;
-          inb[q] = act[q] && r >= lo && r < hi;       // rows outside the utterance become the conv's zero padding
-          v[q] = make_uint4(0u, 0u, 0u, 0u);
-          if (inb[q]) v[q] = *reinterpret_cast<const uint4*>(base + (uint32_t)c * L.lbo_a + (uint32_t)r * 16u);
-        }
-        if (!ident) {
+          for (int q = 0; q < 4; ++q) v[q] = *reinterpret_cast<const uint4*>(cb + q * 512);
+          v[4] = make_uint4(0u, 0u, 0u, 0u);
+          if (tail) v[4] = *reinterpret_cast<const uint4*>(cb + 4 * 512);
 #pragma unroll
           for (int q = 0; q < 5; ++q) {
             __half2* hv = reinterpret_cast<__half2*>(&v[q]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              float2 f = __half22float2(hv[j]);
-              f.x = fmaf(f.x, s1[8 * c + 2 * j], h1[8 * c + 2 * j]);       // InstanceNorm affine in fp32 (x/2 if SiLU follows)
-              f.y = fmaf(f.y, s1[8 * c + 2 * j + 1], h1[8 * c + 2 * j + 1]);
-              __half2 y = __floats2half2_rn(f.x, f.y);
+              __half2 y = __hfma2(hv[j], s1[4 * c + j], h1[4 * c + j]);
               if (do_silu) y = silu_from_half(y);
               if (do_relu) y = __hmax2(y, __float2half2_rn(0.f));
-              if (has_t2) y = __hfma2(y, s2[4 * c + j], h2[4 * c + j]);    // folded eval-mode BatchNorm
+              if (has_t2) y = __hfma2(y, s2[4 * c + j], h2[4 * c + j]);
               hv[j] = y;
             }
-            if (!inb[q]) v[q] = make_uint4(0u, 0u, 0u, 0u);
           }
-        }
 #pragma unroll
-        for (int q = 0; q < 5; ++q)
-          if (act[q]) *reinterpret_cast<uint4*>(base + (uint32_t)c * L.lbo_a + (uint32_t)(lane + q * 32) * 16u) = v[q];
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(cb + q * 512) = v[q];
+          if (tail) *reinterpret_cast<uint4*>(cb + 4 * 512) = v[4];
+        }
+      }
+      if (lo > 0 || hi < slab_used) {               // first / last tile of an utterance: rows outside it are zeros
+        for (int r = lane; r < slab_used; r += 32)
+          if (r < lo || r >= hi) {
+            *reinterpret_cast<uint4*>(base + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(base + L.lbo_a + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+          }
       }
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_FULL + stage));
-      if (p.trace && (xw & 1) == 0 && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
-      stage += TC_XF_GROUPS;
-      while (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
-      tin += kstep * (int)gridDim.x;
+      if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
+      stage += TC_XF_WARPS;
+      if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
+      tin += kstep;
       while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
     }
   } else if (warp == TC_MMA_WARP) {
     // =========================== MMA ISSUER ===========================
     // One thread issues; its instruction stream is the critical path (a lone thread retires a dependent
     // instruction every ~4 cycles), so the per-MMA work is a couple of adds on the descriptors' low words:
-    //   A: + dil (16 B rows) per tap, + 2*LBO per K step;   B: + one [cin_v/8][cout_v] slice per tap.
+    //   A: + dil (16 B rows) per tap;   B: + one [cin_v/8][cout_v] slice per tap, + two chunks per stage.
     // All 32 lanes run the loop converged (see umma_f16_elect); waits are warp-wide polls of the same barrier.
     {
       mbar_wait(BAR(B_W), 0);
       const uint32_t desc_hi = (uint32_t)(umma_desc(0, 0) >> 32);
       const uint32_t a_lo_const = (uint32_t)umma_desc(0, L.lbo_a);
       const uint32_t b_lo_const = (uint32_t)umma_desc(s_base + L.w, (uint32_t)COUT_V * 16u);
-      const uint32_t a_kstep = 2u * (L.lbo_a >> 4);              // two 8-channel chunks per K = 16
-      const uint32_t b_kstep = 2u * (uint32_t)COUT_V;            // 16 B units
-      const uint32_t b_tap = (uint32_t)(p.cin_v / 8) * COUT_V;
+      const uint32_t b_tap = (uint32_t)(p.cin_v / 8) * COUT_V;      // 16 B units
       const uint32_t b_stage = (uint32_t)(TC_STAGE_CH / 8) * COUT_V;
       const uint32_t dil = (uint32_t)p.tap_step;
       const uint32_t idesc_full = umma_idesc(COUT_V), idesc_tap0 = umma_idesc(p.tap_nmax[0]);
@@ -384,18 +408,14 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           mbar_wait(BAR(B_FULL + stage), ph);
           tc_fence_after();
           if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
-          // tap 0 (its first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
+          // tap 0 (the first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
           umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
                          s == 0 ? idesc_full : idesc_tap0, s != 0);
-          umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep), ((uint64_t)desc_hi << 32) | (b_lo + b_kstep),
-                         idesc_tap0, 1u);
 #pragma unroll 1
           for (int tap = 1; tap < nt; ++tap) {
             a_lo += dil;
             b_lo += b_tap;
             umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc_full, 1u);
-            umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + a_kstep),
-                           ((uint64_t)desc_hi << 32) | (b_lo + b_kstep), idesc_full, 1u);
           }
           tc_commit_elect(BAR(B_EMPTY + stage));    // slot free once these MMAs have read it
           if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
@@ -413,7 +433,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     constexpr int CPW = COUT_V / (TC_EPI_WARPS / 4);     // columns per warp
     constexpr int NCH = COUT_V / 8;     // output chunks
     const bool cl = p.out_mode == OUT_CHANNELS_LAST;
-    int tile = (int)blockIdx.x, b = tile / tiles_per_utt, tin = tile - b * tiles_per_utt;
+    int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
     if constexpr (COUT_V == 16) {
       // ---- Toeplitz epilogue (decoder.8, 32 -> 1 channel, 15 taps): the GEMM produced D[r][t] = sum_c a[r][c] w[c][t]
       //      for the 128 slab rows; out[l] = bias + sum_t D[l - m0 + t][t]  (slab row 0 = global row m0 - 7)
@@ -440,8 +460,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           for (int t = 0; t < TC_TOEP_TAPS; ++t) acc += d[(mloc + t) * 17 + t];
           reinterpret_cast<float*>(p.out)[(int64_t)b * p.out_bstride + m] = acc;
         }
-        tin += (int)gridDim.x;
-        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+        if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
     } else
     for (int k = 0; k < n_my_tiles; ++k) {
@@ -501,8 +520,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
-      tin += (int)gridDim.x;
-      while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+      if (++tin == tiles_per_utt) { tin = 0; ++b; }
     }
   }
 
@@ -515,7 +533,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
 
 }
 
-template <int COUT_V>
+template <int COUT_V, int XF>
 int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   int lo = 0, hi = 0;
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
@@ -525,10 +543,10 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int tile_step = toeplitz ? TC_TOEP_STEP : TC_M;
   if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
   const int nst = p.cin_v / TC_STAGE_CH;
-  if (nst != 1 && nst != 2 && nst != 4) return SPANON_ERR_UNSUPPORTED;
+  if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
   const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
-  if (L.n_stages < TC_XF_GROUPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
-  auto kern = tapgemm_tc_kernel<COUT_V>;
+  if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
+  auto kern = tapgemm_tc_kernel<COUT_V, XF>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
   const int tiles_per_utt = (int)ceil_div(p.rows_out, tile_step);
   const int total = tiles_per_utt * p.B;
@@ -571,7 +589,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
 
 bool tapgemm_tc_supported(const TapGemmParams& p) {
   if (p.out_mode == OUT_CH0_F32)   // Toeplitz form of a C -> 1 channel conv: one "tap" at shift -(k-1)/2, 16 columns = the taps
-    return p.cin_v == TC_STAGE_CH && p.cout_v == 16 && p.ntaps == 1 && p.shift[0] == -(TC_TOEP_TAPS - 1) / 2 && !p.stats &&
+    return p.cin_v == 32 && p.cout_v == 16 && p.ntaps == 1 && p.shift[0] == -(TC_TOEP_TAPS - 1) / 2 && !p.stats &&
            p.tap_kmax[0] == p.cin_v && p.tap_nmax[0] == 16;
   if (p.cin_v % TC_STAGE_CH != 0 || (p.cout_v != 64 && p.cout_v != 128)) return false;
   if (p.ntaps < 2 || p.ntaps > MAX_TAPS) return false;
@@ -589,9 +607,18 @@ bool tapgemm_tc_supported(const TapGemmParams& p) {
 
 int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (!tapgemm_tc_supported(p) || p.B < 1) return SPANON_ERR_UNSUPPORTED;
-  if (p.cout_v == 16) return launch_tc<16>(p, n_sm, st);
-  if (p.cout_v == 64) return launch_tc<64>(p, n_sm, st);
-  return launch_tc<128>(p, n_sm, st);
+  // one instantiation per (columns, operand transform) the layer lists use
+  const int act = p.silu == 1 ? XF_SILU : p.silu == 2 ? XF_RELU : XF_IDENT;
+  const int xf = act | (p.t2_scale ? XF_T2 : 0);
+  if (act == XF_IDENT && (p.t1_scale || p.t2_scale)) return SPANON_ERR_UNSUPPORTED;
+  if (p.cout_v == 16 && xf == XF_SILU) return launch_tc<16, XF_SILU>(p, n_sm, st);
+  if (p.cout_v == 64 && xf == XF_IDENT) return launch_tc<64, XF_IDENT>(p, n_sm, st);
+  if (p.cout_v == 64 && xf == XF_SILU) return launch_tc<64, XF_SILU>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == XF_IDENT) return launch_tc<128, XF_IDENT>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == XF_SILU) return launch_tc<128, XF_SILU>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == (XF_SILU | XF_T2)) return launch_tc<128, XF_SILU | XF_T2>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == (XF_RELU | XF_T2)) return launch_tc<128, XF_RELU | XF_T2>(p, n_sm, st);
+  return SPANON_ERR_UNSUPPORTED;
 }
 
 }  // namespace spanon
