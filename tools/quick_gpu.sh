@@ -1,8 +1,8 @@
 #!/bin/bash
 # quick GPU iteration: parity tests, a short bench with the per-kernel table, optionally a role trace (TRACE=1)
 OUT=${1:-gpurun_out/quick.json}
-timeout 300 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
-timeout 200 python bench.py --no-cpu-baseline --steps ${STEPS:-30} --warmup 5 > $OUT 2> $OUT.err || tail -5 $OUT.err
+timeout ${TEST_TIMEOUT:-150} python -m pytest tests -m gpu -q -x 2>&1 | tail -3
+timeout ${BENCH_TIMEOUT:-120} python bench.py --no-cpu-baseline --steps ${STEPS:-30} --warmup 5 > $OUT 2> $OUT.err || tail -5 $OUT.err
 python - <<PY
 import json
 d=json.load(open("$OUT"))
