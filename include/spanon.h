@@ -96,6 +96,12 @@ SPANON_API int64_t spanon_num_frames(int64_t n_samples, int32_t hop_length);
 SPANON_API int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
                      float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream);
 
+/* Same with int16 PCM (the FLAC/WAV payload): sample = x / 32768, exactly what the reference's read_audio
+ * (torchaudio.load, normalised; speechbrain_convae_train.py:483-485, speechbrain/dataio/dataio.py read_audio) hands to
+ * Fbank, so the result is bit-identical to spanon_fbank_f32 on the converted samples at half the input bytes. */
+SPANON_API int spanon_fbank_i16(const int16_t* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
+                     float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream);
+
 /* x = max(x, max_b - top_db) in place on [B, T, n_mels]  (features.py:706-710). */
 SPANON_API int spanon_fbank_clamp(float* feats, const int32_t* utt_max, int64_t B, int64_t T,
                        int64_t n_mels, float top_db, void* stream);
@@ -198,6 +204,26 @@ SPANON_API int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
                       const SpanonConvAEOpts* opts, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * ConvReconstruction forward (the "endtoend" anonymizer variant)
+ * replaces  ConvReconstruction.forward  models/EndToEnd.py:65-87 up to the reshape at :78
+ *           (layers: models/EndToEnd.py:40-54; the external pretrained sex classifier of :57-61,81 is a separate module)
+ * Same options / precision modes / workspace rules as spanon_convae_fwd.
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonConvReconWeights {
+  /* encoder.{0,3,6,9,12}: Conv1d weight [Cout,Cin,k] (encoder.9: ConvTranspose1d [Cin,Cout,k]), bias [Cout] */
+  const float* conv_w[5]; const float* conv_b[5];
+  /* encoder.{1,4,7,10}: InstanceNorm1d affine weight / bias */
+  const float* in_w[4]; const float* in_b[4];
+} SpanonConvReconWeights;
+
+SPANON_API size_t spanon_convrecon_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts);
+/* feats [B,T,F] fp32 with (T*F) % 2 == 0 -> recon [B,T,F] fp32.  Fused-normalisation inputs as in spanon_convae_fwd. */
+SPANON_API int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWeights* w, const float* norm_mean,
+                         const float* norm_std, const int32_t* utt_max, float top_db, int64_t T_valid,
+                         float* recon, void* workspace, size_t workspace_bytes, int64_t B, int64_t T,
+                         int64_t F, const SpanonConvAEOpts* opts, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Loss statistics
  * replaces  CosineSimilarityLoss.forward   utils/cosine_similarity_loss.py:53-56
  *           _pairwise_dists / ClusterMI._mutual_information  utils/ClusterMI.py:12-63,88-121
@@ -235,6 +261,13 @@ SPANON_API int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B,
                           float* recon_host, float* logp_host, void* dev_workspace,
                           size_t dev_workspace_bytes, void* stream);
 
+/* int16 PCM on the wire (see spanon_fbank_i16): half the host-to-device bytes. */
+SPANON_API int spanon_anonymize_host_i16(int kind, const int16_t* pcm_host, int64_t B, int64_t n_samples,
+                          const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                          const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                          float* recon_host, float* logp_host, void* dev_workspace,
+                          size_t dev_workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * Streaming form of the above for a long-running service: up to `depth` batches in
  * flight over three streams (H2D | kernels | D2H), each batch in its own device
@@ -253,6 +286,8 @@ SPANON_API int spanon_pipe_create(SpanonPipe** pipe, int kind, int64_t max_B, in
                        const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
                        const void* weights, const SpanonConvAEOpts* opts, int32_t depth);
 SPANON_API int spanon_pipe_submit(SpanonPipe* pipe, const float* pcm_host, int64_t B, const float* pool_noise,
+                       float* recon_host, float* logp_host);
+SPANON_API int spanon_pipe_submit_i16(SpanonPipe* pipe, const int16_t* pcm_host, int64_t B, const float* pool_noise,
                        float* recon_host, float* logp_host);
 SPANON_API int spanon_pipe_wait(SpanonPipe* pipe);
 SPANON_API int spanon_pipe_drain(SpanonPipe* pipe);

@@ -6,6 +6,7 @@ dicts keyed like the reference's ``state_dict()``) of the two anonymizers:
   ConvAutoencoder.forward          models/ConvAutoEncoder.py:178-200 (layers :141-172)
   TDNNSexClassifier.forward        models/ConvAutoEncoder.py:57-69   (layers :33-55)
   GLU (= x*sigmoid(x))             models/ConvAutoEncoder.py:113-120
+  ConvReconstruction.forward       models/EndToEnd.py:65-78           (layers :40-54)
   FullyConnectedAutoencoder        models/FullyConnected.py:127-159
   FullyConnSexClassifier.forward   models/FullyConnected.py:90-104   (layers :68-86)
   StatisticsPooling.forward        speechbrain/speechbrain/nnet/pooling.py:263-312
@@ -116,6 +117,25 @@ def convae_forward(feats, weights, noise=None, dtype=torch.float32, bn_training=
     logp = tdnn_sex_classifier(enc, w, noise, bn_training)
     rec = convae_decoder(enc, w).squeeze(1).reshape(B, T, Fd)
     return rec, logp
+
+
+def convrecon_forward(feats, weights, dtype=torch.float32):
+    """models/EndToEnd.py:65-78 (layers :40-54): the "endtoend" anonymizer without its external pretrained
+    classifier.  feats [B,T,F] (T*F even) -> recon [B,T,F]."""
+    w = _t(weights, dtype)
+    feats = torch.as_tensor(feats).to(dtype)
+    B, T, Fd = feats.shape
+    x = feats.reshape(B, T * Fd).unsqueeze(1)
+    x = F.conv1d(x, w["encoder.0.weight"], w["encoder.0.bias"], stride=1, padding=7)
+    x = silu_glu(instance_norm(x, w, "encoder.1"))
+    x = F.conv1d(x, w["encoder.3.weight"], w["encoder.3.bias"], stride=2, padding=2)
+    x = silu_glu(instance_norm(x, w, "encoder.4"))
+    x = F.conv1d(x, w["encoder.6.weight"], w["encoder.6.bias"], stride=1, padding=2)
+    x = silu_glu(instance_norm(x, w, "encoder.7"))
+    x = F.conv_transpose1d(x, w["encoder.9.weight"], w["encoder.9.bias"], stride=2, padding=2, output_padding=1)
+    x = silu_glu(instance_norm(x, w, "encoder.10"))
+    x = F.conv1d(x, w["encoder.12.weight"], w["encoder.12.bias"], stride=1, padding=7)
+    return x.squeeze(1).reshape(B, T, Fd)
 
 
 def fc_sex_classifier(z, w, noise=None, bn_training=False, p="sex_classifier."):

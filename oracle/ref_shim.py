@@ -56,7 +56,16 @@ def load():
     # models/ConvAutoEncoder.py:6 imports EncoderClassifier only for the dead
     # CycleGAN variants; a stub keeps the import side-effect free.
     pre = types.ModuleType("speechbrain.pretrained")
-    pre.EncoderClassifier = object
+
+    class _EncoderClassifierStub:
+        """models/EndToEnd.py:57-61 loads a pretrained classifier from an absolute path of the authors' machine at
+        construction time; the stub makes the class constructible (its classifier is never called by the shim)."""
+
+        @classmethod
+        def from_hparams(cls, *a, **k):
+            return None
+
+    pre.EncoderClassifier = _EncoderClassifierStub
     sys.modules["speechbrain.pretrained"] = pre
     sb.pretrained = pre
 
@@ -69,6 +78,7 @@ def load():
     ref_utils = _ns("spanon_ref_utils", os.path.join(REF_ROOT, "utils"))
     convae = importlib.import_module("spanon_ref_models.ConvAutoEncoder")
     fc = importlib.import_module("spanon_ref_models.FullyConnected")
+    e2e = importlib.import_module("spanon_ref_models.EndToEnd")
     cos = importlib.import_module("spanon_ref_utils.cosine_similarity_loss")
     cmi = importlib.import_module("spanon_ref_utils.ClusterMI")
     gmi = importlib.import_module("spanon_ref_utils.GroupSamplingMI")
@@ -83,6 +93,7 @@ def load():
         StatisticsPooling=pooling.StatisticsPooling,
         ConvAutoencoder=convae.ConvAutoencoder,
         TDNNSexClassifier=convae.TDNNSexClassifier,
+        ConvReconstruction=e2e.ConvReconstruction,
         FullyConnectedAutoencoder=fc.FullyConnectedAutoencoder,
         FullyConnSexClassifier=fc.FullyConnSexClassifier,
         CosineSimilarityLoss=cos.CosineSimilarityLoss,

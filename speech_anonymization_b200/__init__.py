@@ -8,9 +8,9 @@ from ._lib import SpanonError, lib  # noqa: F401
 from .features import Fbank, InputNormalization, pad_time  # noqa: F401
 from .losses import (ClusterMI, CosineSimilarityLoss, GroupSampler, GroupSamplingMI, MILoss,  # noqa: F401
                      SimilarityMetricsStats, cosine_distance_2d, knn_mi)
-from .models import (GLU, ConvAutoencoder, FullyConnectedAutoencoder, FullyConnSexClassifier,  # noqa: F401
+from .models import (GLU, ConvAutoencoder, ConvReconstruction, FullyConnectedAutoencoder, FullyConnSexClassifier,  # noqa: F401
                      GradReverse, StatisticsPooling, TDNNSexClassifier)
 from .pipeline import AnonymizerPipeline, StreamPipe, shard_range  # noqa: F401
 
-__all__ = ["Fbank", "InputNormalization", "ConvAutoencoder", "FullyConnectedAutoencoder", "CosineSimilarityLoss",
+__all__ = ["Fbank", "InputNormalization", "ConvAutoencoder", "ConvReconstruction", "FullyConnectedAutoencoder", "CosineSimilarityLoss",
            "MILoss", "ClusterMI", "GroupSamplingMI", "AnonymizerPipeline", "StreamPipe", "shard_range", "pad_time", "lib"]

@@ -54,6 +54,11 @@ class ConvAEWeights(C.Structure):
                 ("cls_bn", BatchNorm * 2)]
 
 
+class ConvReconWeights(C.Structure):
+    _fields_ = [("conv_w", C.c_void_p * 5), ("conv_b", C.c_void_p * 5),
+                ("in_w", C.c_void_p * 4), ("in_b", C.c_void_p * 4)]
+
+
 class ConvAEOpts(C.Structure):
     _fields_ = [("precision", C.c_int32), ("chunk_utts", C.c_int32), ("skip_classifier", C.c_int32),
                 ("weights_prepared", C.c_int32)]
@@ -76,6 +81,8 @@ SIGNATURES = {
     "spanon_num_frames": (C.c_int64, [C.c_int64, C.c_int32]),
     "spanon_fbank_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                    C.POINTER(FbankCfg), C.c_void_p]),
+    "spanon_fbank_i16": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                   C.POINTER(FbankCfg), C.c_void_p]),
     "spanon_fbank_clamp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_float,
                                      C.c_void_p]),
     "spanon_norm_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
@@ -92,6 +99,10 @@ SIGNATURES = {
                                     C.c_void_p, C.c_float, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.POINTER(ConvAEOpts),
                                     C.c_void_p]),
+    "spanon_convrecon_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64, C.POINTER(ConvAEOpts)]),
+    "spanon_convrecon_fwd": (C.c_int, [C.c_void_p, C.POINTER(ConvReconWeights), C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_float, C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64, C.c_int64,
+                                       C.c_int64, C.POINTER(ConvAEOpts), C.c_void_p]),
     "spanon_cosine_loss": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_float,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "spanon_cosine_loss_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
@@ -103,9 +114,13 @@ SIGNATURES = {
     "spanon_anonymize_host": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(FbankCfg),
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ConvAEOpts),
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "spanon_anonymize_host_i16": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.POINTER(FbankCfg),
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ConvAEOpts),
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "spanon_pipe_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.POINTER(FbankCfg),
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(ConvAEOpts), C.c_int32]),
     "spanon_pipe_submit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "spanon_pipe_submit_i16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "spanon_pipe_wait": (C.c_int, [C.c_void_p]),
     "spanon_pipe_drain": (C.c_int, [C.c_void_p]),
     "spanon_pipe_weights_changed": (C.c_int, [C.c_void_p, C.c_void_p]),

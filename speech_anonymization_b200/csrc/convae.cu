@@ -185,9 +185,35 @@ instnorm_stats_kernel(const __half* __restrict__ x, int P, int R, int C, double*
   }
 }
 
+// InstanceNorm statistics of an fp32 channels-last tensor [B][R][32] (ConvReconstruction's encoder.0 output on the fp32
+// path): grid = (row splits, B), block 256 = 8 rows x 32 channels per step.
+__global__ void __launch_bounds__(256)
+instnorm_stats_f32c32_kernel(const float* __restrict__ x, int R, double* __restrict__ stats) {
+  __shared__ float red[2][8][32];
+  const int tid = threadIdx.x, c = tid & 31, rr = tid >> 5, b = blockIdx.y;
+  const float* base = x + (int64_t)b * R * 32;
+  const int rows_per_block = (R + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(R, r0 + rows_per_block);
+  float s = 0.f, q = 0.f;
+  for (int r = r0 + rr; r < r1; r += 8) {
+    const float v = __ldg(base + (int64_t)r * 32 + c);
+    s += v; q = fmaf(v, v, q);
+  }
+  red[0][rr][c] = s; red[1][rr][c] = q;
+  __syncthreads();
+  if (tid < 64) {
+    const int k = tid >> 5;
+    double a = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += (double)red[k][w][c];
+    atomicAdd(stats + ((int64_t)b * 32 + c) * 2 + k, a);
+  }
+}
+
 // ------------------------------------------------------------------ encoder.0 (1 -> 32, k15, p7) + SiLU
 constexpr int FL_NT = 256;
-template <typename TAct, bool FAST_ACT>
+// ACT = false stores the raw convolution (ConvReconstruction puts an InstanceNorm between encoder.0 and its "GLU")
+template <typename TAct, bool FAST_ACT, bool ACT = true>
 __global__ void __launch_bounds__(FL_NT)
 first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64_t n_valid /*valid elems*/, int L,
                    int F, const float* __restrict__ norm_mean, const float* __restrict__ norm_std,
@@ -238,7 +264,7 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
   if (l < L) {
     TAct* o = out + (int64_t)b * out_bstride + (int64_t)l * 32;
 #pragma unroll
-    for (int c = 0; c < 32; ++c) acc[c] = FAST_ACT ? silu_fast(acc[c]) : silu_precise(acc[c]);
+    for (int c = 0; c < 32; ++c) acc[c] = !ACT ? acc[c] : FAST_ACT ? silu_fast(acc[c]) : silu_precise(acc[c]);
     if (sizeof(TAct) == 4) {
       float4* o4 = reinterpret_cast<float4*>(o);
 #pragma unroll
@@ -269,6 +295,7 @@ first_layer_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64
 // Because consecutive taps are consecutive samples, an A fragment register is just two neighbouring samples: three
 // 32-bit shared-memory loads per 16 rows (a second copy of the signal shifted by one sample keeps odd rows aligned).
 // The accumulators start at bias/2, so the MMA result is h = y/2 and SiLU(y) = h + h*tanh(h) (one MUFU per value).
+template <bool ACT>
 __global__ void __launch_bounds__(FL_NT)
 first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, int64_t n_valid, int L, int F,
                        const float* __restrict__ norm_mean, const float* __restrict__ norm_std,
@@ -300,12 +327,13 @@ first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, i
   for (int nt = 0; nt < 4; ++nt) {
     const float* wc = w + (8 * nt + g) * 15;
     const int ta = 2 * t4, tb = 2 * t4 + 8;
-    const __half2 lo = __floats2half2_rn(0.5f * __ldg(wc + ta), 0.5f * __ldg(wc + ta + 1));
-    const __half2 hi = __floats2half2_rn(0.5f * __ldg(wc + tb), tb + 1 < 15 ? 0.5f * __ldg(wc + tb + 1) : 0.f);
+    constexpr float kh = ACT ? 0.5f : 1.f;     // SiLU runs on y/2; the raw store (ACT = false) keeps y
+    const __half2 lo = __floats2half2_rn(kh * __ldg(wc + ta), kh * __ldg(wc + ta + 1));
+    const __half2 hi = __floats2half2_rn(kh * __ldg(wc + tb), tb + 1 < 15 ? kh * __ldg(wc + tb + 1) : 0.f);
     bw[nt][0] = *reinterpret_cast<const uint32_t*>(&lo);
     bw[nt][1] = *reinterpret_cast<const uint32_t*>(&hi);
-    bz[nt][0] = 0.5f * __ldg(bias + 8 * nt + 2 * t4);
-    bz[nt][1] = 0.5f * __ldg(bias + 8 * nt + 2 * t4 + 1);
+    bz[nt][0] = kh * __ldg(bias + 8 * nt + 2 * t4);
+    bz[nt][1] = kh * __ldg(bias + 8 * nt + 2 * t4 + 1);
   }
   __syncthreads();
   __half* ob = out + (int64_t)b * out_bstride;
@@ -331,9 +359,11 @@ first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, i
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
           __half2 hh = __floats2half2_rn(acc[nt][2 * hr], acc[nt][2 * hr + 1]);
-          uint32_t th, in = *reinterpret_cast<uint32_t*>(&hh);
-          asm("tanh.approx.f16x2 %0, %1;" : "=r"(th) : "r"(in));
-          hh = __hfma2(hh, *reinterpret_cast<__half2*>(&th), hh);
+          if (ACT) {
+            uint32_t th, in = *reinterpret_cast<uint32_t*>(&hh);
+            asm("tanh.approx.f16x2 %0, %1;" : "=r"(th) : "r"(in));
+            hh = __hfma2(hh, *reinterpret_cast<__half2*>(&th), hh);
+          }
           *reinterpret_cast<__half2*>(o + ((int64_t)nt * plane_rows << 3)) = hh;
         }
       }
@@ -525,9 +555,11 @@ struct Workspace {
   void* act[4];                                // activation ring, each chunk*L*32 elements
   float* tdnn_out;                             // [chunk][128][L4-14] fp32
   size_t total;
+  const int* inC;                              // channels of each InstanceNorm slot
 };
 
-const int kInC[6] = {64, 64, 128, 128, 64, 32};
+const int kInC[6] = {64, 64, 128, 128, 64, 32};        // ConvAutoencoder: channels of the six InstanceNorms
+const int kInC_recon[6] = {32, 64, 64, 32, 8, 8};      // ConvReconstruction: encoder.{1,4,7,10} (two unused slots)
 
 int default_chunk(int64_t L, size_t esize) {
   // Utterances per pass over the layer list.  Measured on B200 (bench.py --chunk, 60 x 10 s): 6 utterances (planes of
@@ -539,7 +571,9 @@ int default_chunk(int64_t L, size_t esize) {
   return std::max(1, std::min(c, 64));
 }
 
-void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t esize) {
+void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t esize, const int* inC = kInC,
+           bool with_tdnn = true) {
+  ws.inC = inC;
   size_t off = 0;
   auto take = [&](size_t bytes) { void* p = base ? base + off : nullptr; off += align_up(bytes, 256); return p; };
   for (int i = 0; i < N_LAYERS; ++i) {
@@ -549,15 +583,15 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
   for (int i = 0; i < 4; ++i) { ws.bn_scale[i] = (float*)take(128 * 4); ws.bn_shift[i] = (float*)take(128 * 4); }
   ws.ones = (float*)take(128 * 4);
   // stats are contiguous so one memset clears them
-  for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * kInC[i] * 2 * sizeof(double));
+  for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * inC[i] * 2 * sizeof(double));
   ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
   ws.counter = (unsigned*)take(256);
   for (int i = 0; i < 6; ++i) {
-    ws.in_scale[i] = (float*)take((size_t)chunk * kInC[i] * 4);
-    ws.in_shift[i] = (float*)take((size_t)chunk * kInC[i] * 4);
+    ws.in_scale[i] = (float*)take((size_t)chunk * inC[i] * 4);
+    ws.in_shift[i] = (float*)take((size_t)chunk * inC[i] * 4);
   }
   for (int i = 0; i < 4; ++i) ws.act[i] = take((size_t)chunk * L * 32 * esize + 1024);
-  ws.tdnn_out = (float*)take((size_t)chunk * 128 * (size_t)std::max<int64_t>(L / 4 - 14, 1) * 4);
+  ws.tdnn_out = (float*)take(with_tdnn ? (size_t)chunk * 128 * (size_t)std::max<int64_t>(L / 4 - 14, 1) * 4 : 256);
   ws.total = off;
 }
 
@@ -666,7 +700,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
 
 int finalize_in(const Ctx& c, int producer, int idx, const float* gamma, const float* beta, int nb, double count) {
   if (layer_on_tc(c, producer)) return SPANON_OK;  // done by the producing tcgen05 kernel
-  const int C = kInC[idx];
+  const int C = c.ws.inC[idx];
   instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * C, 128), 128, 0, c.st>>>(
       c.ws.stats[idx], gamma, beta, nb, C, count, c.ws.in_scale[idx], c.ws.in_shift[idx]);
   return check_launch("instnorm_finalize_kernel");
@@ -768,7 +802,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
       const int32_t* um = utt_max ? utt_max + b0 : nullptr;
       if (c.tc)
-        first_layer_mma_kernel<<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um,
+        first_layer_mma_kernel<true><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um,
                                                          top_db, w->enc_w[0], w->enc_b[0], (__half*)X[0], L * 32);
       else
         first_layer_kernel<float, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
@@ -828,6 +862,103 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
                                      OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
     SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
+  }
+  return SPANON_OK;
+}
+
+// ====================================================================================================================
+// ConvReconstruction ("endtoend" anonymizer, models/EndToEnd.py:36-87): the same tap-GEMM kernels over a shorter layer
+// list with an InstanceNorm behind EVERY convolution but the last:
+//   encoder.0 Conv1d(1->32,k15,p7) -> IN(32) -> GLU -> encoder.3 Conv1d(32->64,k5,s2,p2) -> IN(64) -> GLU
+//   -> encoder.6 Conv1d(64->64,k5,p2) -> IN(64) -> GLU -> encoder.9 ConvTranspose1d(64->32,k5,s2,p2,op1) -> IN(32) -> GLU
+//   -> encoder.12 Conv1d(32->1,k15,p7)
+// (the external x-vector sex classifier the reference then runs on the output is scope row 8(f)-2, a separate call).
+extern "C" size_t spanon_convrecon_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts) {
+  if (B <= 0 || T <= 0 || F <= 0) return 0;
+  bool tc; int chunk;
+  if (resolve_opts(opts, T * F, &tc, &chunk) != SPANON_OK) return 0;
+  chunk = (int)std::min<int64_t>(chunk, B);
+  Workspace ws;
+  carve(ws, nullptr, chunk, T * F, tc, tc ? 2 : 4, kInC_recon, false);
+  return ws.total + 256;
+}
+
+extern "C" int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWeights* w, const float* norm_mean,
+                                    const float* norm_std, const int32_t* utt_max, float top_db, int64_t T_valid,
+                                    float* recon, void* workspace, size_t workspace_bytes, int64_t B, int64_t T,
+                                    int64_t F, const SpanonConvAEOpts* opts, void* stream) {
+  if (!w) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || T <= 0 || F <= 0) return SPANON_ERR_BAD_SHAPE;
+  const int64_t L = T * F;
+  // one stride-2 stage: the reference's final reshape fails for odd L (EndToEnd.py:78)
+  if (L % 2 != 0 || L > (int64_t)1 << 30) return SPANON_ERR_BAD_SHAPE;
+  if (B == 0) return SPANON_OK;
+  if (!feats || !recon || !workspace) return SPANON_ERR_NULL_POINTER;
+  if ((norm_mean == nullptr) != (norm_std == nullptr)) return SPANON_ERR_NULL_POINTER;
+  const bool fused_norm = norm_mean != nullptr;
+  if (!fused_norm) T_valid = T;
+  if (T_valid < 0 || T_valid > T) return SPANON_ERR_BAD_SHAPE;
+  Ctx c{};
+  int chunk;
+  SPANON_TRY(resolve_opts(opts, L, &c.tc, &chunk));
+  chunk = (int)std::min<int64_t>(chunk, B);
+  if (workspace_bytes < spanon_convrecon_workspace_bytes(B, T, F, opts)) return SPANON_ERR_WORKSPACE;
+  char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
+  const size_t esize = c.tc ? 2 : 4;
+  carve(c.ws, base, chunk, L, c.tc, esize, kInC_recon, false);
+  c.w = nullptr; c.L = L; c.st = as_stream(stream);
+  {
+    int dev = 0;
+    SPANON_CUDA_TRY(cudaGetDevice(&dev));
+    SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
+  }
+  if (!(opts && opts->weights_prepared)) {
+    SPANON_TRY(pack_layer(c, L_ENC2, w->conv_w[1]));
+    SPANON_TRY(pack_layer(c, L_ENC5, w->conv_w[2]));
+    SPANON_TRY(pack_layer(c, L_DEC5, w->conv_w[3]));
+    SPANON_TRY(pack_layer(c, L_DEC8, w->conv_w[4]));
+  }
+  const int64_t L2 = L / 2;
+  const size_t stats_bytes = reinterpret_cast<char*>(c.ws.pool) - reinterpret_cast<char*>(c.ws.stats[0]);
+  for (int64_t b0 = 0; b0 < B; b0 += chunk) {
+    const int nb = (int)std::min<int64_t>(chunk, B - b0);
+    SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.stats[0], 0, stats_bytes, c.st));
+    void** X = c.ws.act;
+    {   // encoder.0, raw (the InstanceNorm + GLU behind it run in encoder.3's operand load)
+      const int64_t fstride = fused_norm ? T_valid * F : L;
+      const float* src = feats + b0 * fstride;
+      dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
+      const int32_t* um = utt_max ? utt_max + b0 : nullptr;
+      if (c.tc) {
+        first_layer_mma_kernel<false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std,
+                                                                um, top_db, w->conv_w[0], w->conv_b[0], (__half*)X[0], L * 32);
+        SPANON_TRY(check_launch("first_layer_kernel"));
+        dim3 sg((unsigned)ceil_div(L2, ST_NT * ST_ROWS), 8u, (unsigned)nb);    // pair-folded: 8 planes of L/2 rows
+        instnorm_stats_kernel<<<sg, ST_NT, 0, c.st>>>((const __half*)X[0], 8, (int)L2, 32, c.ws.stats[0]);
+        SPANON_TRY(check_launch("instnorm_stats_kernel"));
+      } else {
+        first_layer_kernel<float, false, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
+                                                                          norm_mean, norm_std, um, top_db, w->conv_w[0],
+                                                                          w->conv_b[0], (float*)X[0], L * 32);
+        SPANON_TRY(check_launch("first_layer_kernel"));
+        dim3 sg((unsigned)std::min<int64_t>(ceil_div(L, 2048), 1024), (unsigned)nb);
+        instnorm_stats_f32c32_kernel<<<sg, 256, 0, c.st>>>((const float*)X[0], (int)L, c.ws.stats[0]);
+        SPANON_TRY(check_launch("instnorm_stats_kernel"));
+      }
+      instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * 32, 128), 128, 0, c.st>>>(
+          c.ws.stats[0], w->in_w[0], w->in_b[0], nb, 32, (double)L, c.ws.in_scale[0], c.ws.in_shift[0]);
+      SPANON_TRY(check_launch("instnorm_finalize_kernel"));
+    }
+    const bool tcp = c.tc;
+    auto nb_ = [&](const float* bias) { return tcp ? nullptr : bias; };   // a bias in front of an InstanceNorm is a no-op
+    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], 0, -1, nb_(w->conv_b[1]), 0, -1, 1, OUT_CHANNELS_LAST, w->in_w[1], w->in_b[1], (double)L2}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC2, 1, w->in_w[1], w->in_b[1], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 1, -1, nb_(w->conv_b[2]), 0, -1, 2, OUT_CHANNELS_LAST, w->in_w[2], w->in_b[2], (double)L2}, nb));
+    SPANON_TRY(finalize_in(c, L_ENC5, 2, w->in_w[2], w->in_b[2], nb, (double)L2));
+    SPANON_TRY(run_layer(c, L_DEC5, {X[2], X[3], 2, -1, nb_(w->conv_b[3]), 0, -1, 3, OUT_CHANNELS_LAST, w->in_w[3], w->in_b[3], (double)L,
+                                     OUT_PHASE_UNFOLD}, nb));
+    SPANON_TRY(finalize_in(c, L_DEC5, 3, w->in_w[3], w->in_b[3], nb, (double)L));
+    SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 3, -1, w->conv_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
   }
   return SPANON_OK;
 }

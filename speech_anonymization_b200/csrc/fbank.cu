@@ -43,6 +43,18 @@ struct FbankSmem {
   float red[NT / 32];
 };
 
+// PCM sample formats: fp32 (the reference's wire format after read_audio) or int16 (the FLAC/WAV payload itself);
+// int16 -> fp32 is x / 32768, exactly what torchaudio's normalised load produces (speechbrain_convae_train.py:483-485).
+__device__ __forceinline__ float load1(const float* x, int64_t i) { return __ldg(x + i); }
+__device__ __forceinline__ float load1(const int16_t* x, int64_t i) { return (float)__ldg(x + i) * (1.f / 32768.f); }
+__device__ __forceinline__ float4 load4(const float* x, int64_t i) { return __ldg(reinterpret_cast<const float4*>(x + i)); }
+__device__ __forceinline__ float4 load4(const int16_t* x, int64_t i) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(x + i));
+  const float k = 1.f / 32768.f;
+  return make_float4((float)(int16_t)(u.x & 0xffffu) * k, (float)(int16_t)(u.x >> 16) * k,
+                     (float)(int16_t)(u.y & 0xffffu) * k, (float)(int16_t)(u.y >> 16) * k);
+}
+
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
   return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
@@ -105,15 +117,16 @@ __device__ __forceinline__ void stockham_stage(const float2* __restrict__ in, fl
   }
 }
 
+template <typename TS>
 __global__ void __launch_bounds__(NT)
-fbank400_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
+fbank400_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
                 float* __restrict__ out, int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FbankSmem& S = *reinterpret_cast<FbankSmem*>(smem_raw);
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
   const int t0 = blockIdx.x * FRAMES_PER_CTA;
-  const float* x = pcm + (int64_t)b * pcm_stride;
+  const TS* x = pcm + (int64_t)b * pcm_stride;
 
   // twiddles (fp64 evaluation, once per CTA: 400 sincos) and the window
   for (int i = tid; i < N_FFT; i += NT) {
@@ -124,17 +137,17 @@ fbank400_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_st
   }
   // PCM segment: padded sample p = t*HOP + n - N_FFT/2  (center=True, zero padding)
   const int64_t base = (int64_t)t0 * HOP - N_FFT / 2;
-  const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && ((base & 3) == 0);
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & (4 * sizeof(TS) - 1)) == 0) && ((base & 3) == 0);
   for (int i4 = tid; i4 < SEG / 4; i4 += NT) {
     const int64_t s = base + 4 * (int64_t)i4;
     float4 v;
     if (vec_ok && s >= 0 && s + 3 < n_samples) {
-      v = __ldg(reinterpret_cast<const float4*>(x + s));
+      v = load4(x, s);
     } else {
-      v.x = (s + 0 >= 0 && s + 0 < n_samples) ? __ldg(x + s + 0) : 0.f;
-      v.y = (s + 1 >= 0 && s + 1 < n_samples) ? __ldg(x + s + 1) : 0.f;
-      v.z = (s + 2 >= 0 && s + 2 < n_samples) ? __ldg(x + s + 2) : 0.f;
-      v.w = (s + 3 >= 0 && s + 3 < n_samples) ? __ldg(x + s + 3) : 0.f;
+      v.x = (s + 0 >= 0 && s + 0 < n_samples) ? load1(x, s + 0) : 0.f;
+      v.y = (s + 1 >= 0 && s + 1 < n_samples) ? load1(x, s + 1) : 0.f;
+      v.z = (s + 2 >= 0 && s + 2 < n_samples) ? load1(x, s + 2) : 0.f;
+      v.w = (s + 3 >= 0 && s + 3 < n_samples) ? load1(x, s + 3) : 0.f;
     }
     *reinterpret_cast<float4*>(&S.seg[4 * i4]) = v;
   }
@@ -215,8 +228,9 @@ fbank400_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_st
 
 // Generic (any n_fft <= 4096, win_length <= n_fft) direct-DFT path: one CTA per frame.
 // O(n_fft^2) per frame -- correctness path for non-reference configurations only.
+template <typename TS>
 __global__ void __launch_bounds__(256)
-fbank_generic_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
+fbank_generic_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T,
                      float* __restrict__ out, int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_fft = cfg.n_fft;
@@ -227,7 +241,7 @@ fbank_generic_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t p
   __shared__ float red[8];
   const int tid = threadIdx.x;
   const int t = blockIdx.x, b = blockIdx.y;
-  const float* x = pcm + (int64_t)b * pcm_stride;
+  const TS* x = pcm + (int64_t)b * pcm_stride;
   const int wl = cfg.win_length;
   const int woff = (n_fft - wl) / 2;  // torch.stft centres a short window inside n_fft
   for (int i = tid; i < n_fft; i += blockDim.x) {
@@ -235,7 +249,7 @@ fbank_generic_kernel(const float* __restrict__ pcm, int64_t n_samples, int64_t p
     sincospi(-2.0 * (double)i / (double)n_fft, &s, &c);
     tw[i] = make_float2((float)c, (float)s);
     const int64_t p = (int64_t)t * cfg.hop_length + i - n_fft / 2;
-    const float v = (p >= 0 && p < n_samples) ? __ldg(x + p) : 0.f;
+    const float v = (p >= 0 && p < n_samples) ? load1(x, p) : 0.f;
     const float w = (i >= woff && i < woff + wl) ? cfg.window[i - woff] : 0.f;
     fr[i] = v * w;
   }
@@ -304,8 +318,10 @@ extern "C" int64_t spanon_num_frames(int64_t n_samples, int32_t hop_length) {
   return 1 + n_samples / hop_length;
 }
 
-extern "C" int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
-                                float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream) {
+namespace {
+template <typename TS>
+int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride, float* out, int32_t* utt_max,
+                 const SpanonFbankCfg* cfg, void* stream) {
   if (!cfg) return SPANON_ERR_NULL_POINTER;
   if (B < 0 || n_samples < 0 || pcm_stride < n_samples) return SPANON_ERR_BAD_SHAPE;
   if (cfg->n_fft <= 0 || cfg->hop_length <= 0 || cfg->win_length <= 0 || cfg->win_length > cfg->n_fft ||
@@ -322,19 +338,30 @@ extern "C" int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, 
   if (cfg->n_fft == N_FFT && cfg->win_length == N_FFT && cfg->hop_length == HOP) {
     static bool attr_done = false;
     if (!attr_done) {
-      SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(FbankSmem)));
       attr_done = true;
     }
     dim3 grid((unsigned)ceil_div(T, FRAMES_PER_CTA), (unsigned)B);
-    fbank400_kernel<<<grid, NT, sizeof(FbankSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+    fbank400_kernel<TS><<<grid, NT, sizeof(FbankSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
     return check_launch("fbank400_kernel");
   }
   if (cfg->n_fft > 4096) return SPANON_ERR_UNSUPPORTED;
   const size_t smem = (size_t)cfg->n_fft * (sizeof(float2) + sizeof(float)) + (cfg->n_fft / 2 + 1) * sizeof(float);
   dim3 grid((unsigned)T, (unsigned)B);
-  fbank_generic_kernel<<<grid, 256, smem, st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+  fbank_generic_kernel<TS><<<grid, 256, smem, st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
   return check_launch("fbank_generic_kernel");
+}
+}  // namespace
+
+extern "C" int spanon_fbank_f32(const float* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
+                                float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream) {
+  return fbank_launch<float>(pcm, B, n_samples, pcm_stride, out, utt_max, cfg, stream);
+}
+
+extern "C" int spanon_fbank_i16(const int16_t* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride,
+                                float* out, int32_t* utt_max, const SpanonFbankCfg* cfg, void* stream) {
+  return fbank_launch<int16_t>(pcm, B, n_samples, pcm_stride, out, utt_max, cfg, stream);
 }
 
 extern "C" int spanon_fbank_clamp(float* feats, const int32_t* utt_max, int64_t B, int64_t T, int64_t n_mels,

@@ -42,16 +42,21 @@ namespace {
 struct Lanes { cudaStream_t h2d, compute, d2h; cudaEvent_t ev_h2d, ev_compute; };   // ev_* NULL when all three are one stream
 
 // Enqueues one batch: H2D on lanes.h2d, kernels on lanes.compute, D2H on lanes.d2h (ordered by the two events).
-int enqueue_batch(int kind, const float* pcm_host, int64_t B, int64_t n_samples, const SpanonFbankCfg* fb,
+// fmt: bytes per PCM sample on the wire, 4 = fp32, 2 = int16 (half the H2D bytes; converted on load by the Fbank kernel)
+int enqueue_batch(int kind, const void* pcm_host, int fmt, int64_t B, int64_t n_samples, const SpanonFbankCfg* fb,
                   const float* norm_mean, const float* norm_std, const void* weights, const float* pool_noise,
                   const SpanonConvAEOpts* opts, float* recon_host, float* logp_host, const Carve& c, const Lanes& ln) {
   const int64_t T = 1 + n_samples / fb->hop_length, Tp = padded_T(kind, T), F = fb->n_mels;
-  SPANON_CUDA_TRY(cudaMemcpyAsync(c.pcm, pcm_host, (size_t)B * n_samples * 4, cudaMemcpyHostToDevice, ln.h2d));
+  SPANON_CUDA_TRY(cudaMemcpyAsync(c.pcm, pcm_host, (size_t)B * n_samples * fmt, cudaMemcpyHostToDevice, ln.h2d));
   if (ln.ev_h2d) {
     SPANON_CUDA_TRY(cudaEventRecord(ln.ev_h2d, ln.h2d));
     SPANON_CUDA_TRY(cudaStreamWaitEvent(ln.compute, ln.ev_h2d, 0));
   }
-  SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, ln.compute));
+  if (fmt == 2)
+    SPANON_TRY(spanon_fbank_i16(reinterpret_cast<const int16_t*>(c.pcm), B, n_samples, n_samples, c.fb, c.utt_max, fb,
+                                ln.compute));
+  else
+    SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, ln.compute));
   float* logp_dev = logp_host ? c.logp : nullptr;
   if (kind == 0) {
     SPANON_TRY(spanon_convae_fwd(c.fb, (const SpanonConvAEWeights*)weights, pool_noise, norm_mean, norm_std,
@@ -71,11 +76,11 @@ int enqueue_batch(int kind, const float* pcm_host, int64_t B, int64_t n_samples,
 }
 }  // namespace
 
-extern "C" int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B, int64_t n_samples,
-                                     const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
-                                     const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
-                                     float* recon_host, float* logp_host, void* dev_workspace,
-                                     size_t dev_workspace_bytes, void* stream) {
+static int anonymize_host(int kind, const void* pcm_host, int fmt, int64_t B, int64_t n_samples,
+                          const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                          const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                          float* recon_host, float* logp_host, void* dev_workspace,
+                          size_t dev_workspace_bytes, void* stream) {
   if (kind != 0 && kind != 1) return SPANON_ERR_UNSUPPORTED;
   if (!fb || !weights || !pcm_host || !recon_host || !dev_workspace || !norm_mean || !norm_std)
     return SPANON_ERR_NULL_POINTER;
@@ -86,10 +91,28 @@ extern "C" int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B,
   Carve c = carve(base, kind, B, n_samples, fb->hop_length, fb->n_mels, opts);
   cudaStream_t st = as_stream(stream);
   const Lanes ln{st, st, st, nullptr, nullptr};
-  SPANON_TRY(enqueue_batch(kind, pcm_host, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
+  SPANON_TRY(enqueue_batch(kind, pcm_host, fmt, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
                            logp_host, c, ln));
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
   return SPANON_OK;
+}
+
+extern "C" int spanon_anonymize_host(int kind, const float* pcm_host, int64_t B, int64_t n_samples,
+                                     const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                                     const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                                     float* recon_host, float* logp_host, void* dev_workspace,
+                                     size_t dev_workspace_bytes, void* stream) {
+  return anonymize_host(kind, pcm_host, 4, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
+                        logp_host, dev_workspace, dev_workspace_bytes, stream);
+}
+
+extern "C" int spanon_anonymize_host_i16(int kind, const int16_t* pcm_host, int64_t B, int64_t n_samples,
+                                         const SpanonFbankCfg* fb, const float* norm_mean, const float* norm_std,
+                                         const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                                         float* recon_host, float* logp_host, void* dev_workspace,
+                                         size_t dev_workspace_bytes, void* stream) {
+  return anonymize_host(kind, pcm_host, 2, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
+                        logp_host, dev_workspace, dev_workspace_bytes, stream);
 }
 
 // ------------------------------------------------------------------ streaming pipe
@@ -178,8 +201,8 @@ extern "C" int spanon_pipe_drain(SpanonPipe* p) {
   return SPANON_OK;
 }
 
-extern "C" int spanon_pipe_submit(SpanonPipe* p, const float* pcm_host, int64_t B, const float* pool_noise,
-                                  float* recon_host, float* logp_host) {
+static int pipe_submit(SpanonPipe* p, const void* pcm_host, int fmt, int64_t B, const float* pool_noise,
+                       float* recon_host, float* logp_host) {
   if (!p || !pcm_host || !recon_host) return SPANON_ERR_NULL_POINTER;
   if (B <= 0 || B > p->max_B) return SPANON_ERR_BAD_SHAPE;
   if (p->submitted - p->retired >= p->depth) SPANON_TRY(spanon_pipe_wait(p));   // the slot we are about to reuse
@@ -190,13 +213,23 @@ extern "C" int spanon_pipe_submit(SpanonPipe* p, const float* pcm_host, int64_t 
   Carve c = carve(base, p->kind, B, p->n_samples, p->fb.hop_length, p->fb.n_mels, &o);
   const Lanes ln{p->h2d, p->compute, p->d2h, s.ev_h2d, s.ev_compute};
   const void* w = p->kind == 0 ? (const void*)&p->w.conv : (const void*)&p->w.fc;
-  SPANON_TRY(enqueue_batch(p->kind, pcm_host, B, p->n_samples, &p->fb, p->norm_mean, p->norm_std, w, pool_noise, &o,
+  SPANON_TRY(enqueue_batch(p->kind, pcm_host, fmt, B, p->n_samples, &p->fb, p->norm_mean, p->norm_std, w, pool_noise, &o,
                            recon_host, logp_host, c, ln));
   SPANON_CUDA_TRY(cudaEventRecord(s.ev_done, p->d2h));
   s.busy = true;
   s.prepared_B = B;
   ++p->submitted;
   return SPANON_OK;
+}
+
+extern "C" int spanon_pipe_submit(SpanonPipe* p, const float* pcm_host, int64_t B, const float* pool_noise,
+                                  float* recon_host, float* logp_host) {
+  return pipe_submit(p, pcm_host, 4, B, pool_noise, recon_host, logp_host);
+}
+
+extern "C" int spanon_pipe_submit_i16(SpanonPipe* p, const int16_t* pcm_host, int64_t B, const float* pool_noise,
+                                      float* recon_host, float* logp_host) {
+  return pipe_submit(p, pcm_host, 2, B, pool_noise, recon_host, logp_host);
 }
 
 extern "C" int spanon_pipe_weights_changed(SpanonPipe* p, const void* weights) {

@@ -36,7 +36,8 @@ def _to_hz(mel):
 class Fbank(torch.nn.Module):
     """Drop-in for speechbrain.lobes.features.Fbank (lobes/features.py:78-143).
 
-    wav [B, n_samples] (or [B, n_samples, channels]) on a CUDA device -> [B, T, n_mels] log-mel
+    wav [B, n_samples] (or [B, n_samples, channels]) fp32 -- or int16 PCM, converted as x / 32768 on load like the
+    reference's read_audio does on the host -- on a CUDA device -> [B, T, n_mels] log-mel
     features in dB with the per-utterance top_db (80 dB) clamp; T = 1 + n_samples // hop.
     """
 
@@ -153,7 +154,8 @@ class Fbank(torch.nn.Module):
 
     def forward_raw(self, wav):
         """Unclamped dB features plus the per-utterance max keys (input of the fused consumers)."""
-        _lib.require_cuda(wav, "wav")
+        i16 = isinstance(wav, torch.Tensor) and wav.dtype == torch.int16   # raw PCM: sample = x / 32768 (read_audio)
+        _lib.require_cuda(wav, "wav", torch.int16 if i16 else torch.float32)
         if wav.dim() != 2:
             raise ValueError("forward_raw expects [batch, samples]")
         wav = wav.contiguous()
@@ -166,9 +168,9 @@ class Fbank(torch.nn.Module):
         out = torch.empty((B, T, self.n_mels), dtype=torch.float32, device=wav.device)
         utt_max = torch.empty((max(B, 1),), dtype=torch.int32, device=wav.device)
         with torch.cuda.device(wav.device):
-            _lib.check(_lib.lib().spanon_fbank_f32(_lib.ptr(wav), B, n, wav.stride(0) if B > 1 else n, _lib.ptr(out),
-                                                   _lib.ptr(utt_max), C.byref(st["cfg"]),
-                                                   _lib.stream_ptr(wav.device)), "fbank_f32")
+            fn = _lib.lib().spanon_fbank_i16 if i16 else _lib.lib().spanon_fbank_f32
+            _lib.check(fn(_lib.ptr(wav), B, n, wav.stride(0) if B > 1 else n, _lib.ptr(out), _lib.ptr(utt_max),
+                          C.byref(st["cfg"]), _lib.stream_ptr(wav.device)), "fbank")
         return out, utt_max
 
     def forward(self, wav):

@@ -1,6 +1,7 @@
 """Host-side mirror of the reference's anonymizer modules, backed by libspanon's CUDA kernels.
 
   ConvAutoencoder / TDNNSexClassifier / GLU / GradReverse   models/ConvAutoEncoder.py:12-69,113-200
+  ConvReconstruction ("endtoend")                           models/EndToEnd.py:36-87
   FullyConnectedAutoencoder / FullyConnSexClassifier        models/FullyConnected.py:65-159
   StatisticsPooling                                         speechbrain/speechbrain/nnet/pooling.py:229-326
 
@@ -233,6 +234,86 @@ class ConvAutoencoder(nn.Module):
                                            _lib.ptr(logp), _lib.ptr(ws), ws_bytes, B, T, F, C.byref(opts),
                                            _lib.stream_ptr(dev)), "convae_fwd")
         return recon, logp
+
+
+class ConvReconstruction(nn.Module):
+    """Drop-in for models.EndToEnd.ConvReconstruction (models/EndToEnd.py:36-87), the "endtoend" anonymizer.
+
+    `encoder` has the reference's layer objects at the reference's indices ({0,3,6,9,12} convolutions, {1,4,7,10}
+    InstanceNorms), so checkpoints load unchanged.  The reference builds its `sex_classifier` from a pretrained
+    x-vector EncoderClassifier on disk (`EncoderClassifier.from_hparams`, :57-61); here it is any callable
+    `feats [B,T,F] -> (log-probs, score, index)` handed to the constructor (None: forward returns None for the logits).
+
+    forward(input [B,T,F]) -> (reconstruction [B,T,F], sex_classifier_logits).
+    """
+
+    def __init__(self, sex_classifier=None):
+        super().__init__()
+        self.encoder = nn.Sequential(
+            nn.Conv1d(in_channels=1, out_channels=32, kernel_size=15, stride=1, padding=7),
+            nn.InstanceNorm1d(num_features=32, affine=True), GLU(),
+            nn.Conv1d(in_channels=32, out_channels=64, kernel_size=5, stride=2, padding=2),
+            nn.InstanceNorm1d(num_features=64, affine=True), GLU(),
+            nn.Conv1d(in_channels=64, out_channels=64, kernel_size=5, stride=1, padding=2),
+            nn.InstanceNorm1d(num_features=64, affine=True), GLU(),
+            nn.ConvTranspose1d(in_channels=64, out_channels=32, kernel_size=5, stride=2, padding=2, output_padding=1),
+            nn.InstanceNorm1d(num_features=32, affine=True), GLU(),
+            nn.Conv1d(in_channels=32, out_channels=1, kernel_size=15, stride=1, padding=7),
+        )
+        self.sex_classifier = sex_classifier
+        self.precision = _precision_from_env()
+        self.chunk_utts = 0
+
+    def weight_struct(self):
+        e = self.encoder
+        w = _lib.ConvReconWeights()
+        for i, k in enumerate((0, 3, 6, 9, 12)):
+            w.conv_w[i], w.conv_b[i] = _p(e[k].weight), _p(e[k].bias)
+        for i, k in enumerate((1, 4, 7, 10)):
+            w.in_w[i], w.in_b[i] = _p(e[k].weight), _p(e[k].bias)
+        return w
+
+    def opts(self):
+        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16, int(self.chunk_utts), 1, 0)
+
+    def forward(self, input, fused_norm=None):
+        """`fused_norm` = (mean [F], std [F], utt_max [B], top_db, T_pad) as in ConvAutoencoder.forward."""
+        _lib.require_cuda(input, "input")
+        if torch.is_grad_enabled() and (input.requires_grad or any(p.requires_grad for p in self.encoder.parameters())):
+            raise NotImplementedError("ConvReconstruction: only the forward pass runs on the CUDA kernels; call under "
+                                      "torch.no_grad() (the backward pass is scope row 8(f)-1)")
+        if input.dim() != 3:
+            raise ValueError("ConvReconstruction expects [batch, time, features]")
+        x = input.contiguous()
+        B, T_in, F = x.shape
+        T = T_in if fused_norm is None else int(fused_norm[4])
+        if (T * F) % 2 != 0:   # the reference's reshape at EndToEnd.py:78 fails: the stride-2 pair returns T*F + 1 values
+            raise RuntimeError("shape '[%d, %d, %d]' is invalid for input of size %d: time*features must be even"
+                               % (B, T, F, B * (T * F + 1)))
+        dev = x.device
+        recon = torch.empty((B, T, F), dtype=torch.float32, device=dev)
+        if B > 0:
+            w = self.weight_struct()
+            opts = self.opts()
+            L = _lib.lib()
+            ws_bytes = L.spanon_convrecon_workspace_bytes(B, T, F, C.byref(opts))
+            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+            if fused_norm is None:
+                mean = std = umax = None
+                top_db, t_valid = 0.0, T
+            else:
+                mean, std, umax, top_db = fused_norm[0], fused_norm[1], fused_norm[2], float(fused_norm[3])
+                mean = mean.to(device=dev, dtype=torch.float32).contiguous()
+                std = std.to(device=dev, dtype=torch.float32).contiguous()
+                t_valid = T_in
+            with torch.cuda.device(dev):
+                _lib.check(L.spanon_convrecon_fwd(_lib.ptr(x), C.byref(w), _lib.ptr(mean), _lib.ptr(std), _lib.ptr(umax),
+                                                  top_db, t_valid, _lib.ptr(recon), _lib.ptr(ws), ws_bytes, B, T, F,
+                                                  C.byref(opts), _lib.stream_ptr(dev)), "convrecon_fwd")
+        logits = None
+        if self.sex_classifier is not None:   # EndToEnd.py:81
+            logits, _score, _index = self.sex_classifier(recon)
+        return recon, logits
 
 
 class FullyConnSexClassifier(nn.Module):

@@ -71,7 +71,7 @@ class AnonymizerPipeline(torch.nn.Module):
 
     @torch.no_grad()
     def anonymize_host(self, pcm_host, recon_host, logp_host, workspace, pool_noise=None):
-        """pcm_host [B, n] (pinned) host fp32 -> recon_host [B, T', F], logp_host [B, 2] host tensors.
+        """pcm_host [B, n] (pinned) host fp32 or int16 PCM -> recon_host [B, T', F], logp_host [B, 2] host tensors.
         H2D copy, all kernels, D2H copy and the stream sync happen inside spanon_anonymize_host."""
         if not self._frozen_stats():
             raise _lib.SpanonError("anonymize_host needs eval-mode InputNormalization with loaded global statistics")
@@ -83,8 +83,9 @@ class AnonymizerPipeline(torch.nn.Module):
         w = self.model.weight_struct()
         opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
         B, ns = pcm_host.shape
+        fn = _lib.lib().spanon_anonymize_host_i16 if pcm_host.dtype == torch.int16 else _lib.lib().spanon_anonymize_host
         with torch.cuda.device(dev):
-            _lib.check(_lib.lib().spanon_anonymize_host(
+            _lib.check(fn(
                 0 if self.is_conv else 1, _lib.ptr(pcm_host), B, ns, C.byref(st["cfg"]), _lib.ptr(mean),
                 _lib.ptr(std), C.cast(C.byref(w), C.c_void_p), _lib.ptr(pool_noise), C.byref(opts),
                 _lib.ptr(recon_host), _lib.ptr(logp_host), _lib.ptr(workspace), workspace.numel(),
@@ -122,10 +123,11 @@ class StreamPipe:
         self.depth = depth
 
     def submit(self, pcm_host, recon_host, logp_host, pool_noise=None):
+        # int16 PCM (the audio file's own sample format) halves the host-to-device bytes; the Fbank kernel converts
+        fn = _lib.lib().spanon_pipe_submit_i16 if pcm_host.dtype == torch.int16 else _lib.lib().spanon_pipe_submit
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().spanon_pipe_submit(self._h, _lib.ptr(pcm_host), pcm_host.shape[0],
-                                                     _lib.ptr(pool_noise), _lib.ptr(recon_host), _lib.ptr(logp_host)),
-                       "pipe_submit")
+            _lib.check(fn(self._h, _lib.ptr(pcm_host), pcm_host.shape[0], _lib.ptr(pool_noise), _lib.ptr(recon_host),
+                          _lib.ptr(logp_host)), "pipe_submit")
         self._keep.append((pcm_host, recon_host, logp_host, pool_noise))
         del self._keep[:-self.depth]
 

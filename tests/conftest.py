@@ -37,6 +37,12 @@ def golden():
     return dict(np.load(os.path.join(GOLDEN_DIR, "golden_v1.npz")))
 
 
+@pytest.fixture(scope="session")
+def golden2():
+    """Scope rows 8(f) (tests/golden/make_golden_v2.py)."""
+    return dict(np.load(os.path.join(GOLDEN_DIR, "golden_v2.npz")))
+
+
 def rel_db_err(a, ref):
     """BASELINE.json parity metric for Fbank: |a-ref| / max(|ref|, 1), max over elements."""
     a = np.asarray(a, dtype=np.float64)

@@ -38,6 +38,18 @@ for _bn, _c in (("tdnn.2", 128), ("tdnn.5", 128), ("tdnn.8", 128), ("norm", 128)
         CONVAE_SHAPES["sex_classifier.%s.%s" % (_bn, _s)] = (_c,)
     CONVAE_SHAPES["sex_classifier.%s.num_batches_tracked" % _bn] = ()
 
+CONVRECON_SHAPES = {   # models/EndToEnd.py:40-54
+    "encoder.0.weight": (32, 1, 15), "encoder.0.bias": (32,),
+    "encoder.1.weight": (32,), "encoder.1.bias": (32,),
+    "encoder.3.weight": (64, 32, 5), "encoder.3.bias": (64,),
+    "encoder.4.weight": (64,), "encoder.4.bias": (64,),
+    "encoder.6.weight": (64, 64, 5), "encoder.6.bias": (64,),
+    "encoder.7.weight": (64,), "encoder.7.bias": (64,),
+    "encoder.9.weight": (64, 32, 5), "encoder.9.bias": (32,),
+    "encoder.10.weight": (32,), "encoder.10.bias": (32,),
+    "encoder.12.weight": (1, 32, 15), "encoder.12.bias": (1,),
+}
+
 FCAE_SHAPES = {
     "encoder.0.weight": (60, 80), "encoder.0.bias": (60,),
     "encoder.2.weight": (40, 60), "encoder.2.bias": (40,),

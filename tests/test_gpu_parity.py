@@ -109,6 +109,22 @@ def test_fbank_full_size_properties():
     assert rel_db_err(f[5:6].cpu().numpy(), sub) < FBANK_TOL
 
 
+def test_fbank_int16_wire_format():
+    """int16 PCM: sample = x / 32768 like read_audio -> bit-identical to the fp32 path on the converted
+    samples; rows of 16001 samples start off the 8-byte vector alignment (scalar-load path) except row 0; both the
+    400-point FFT kernel and the generic DFT kernel."""
+    rng = np.random.default_rng(5)
+    pcm = rng.integers(-32768, 32768, size=(3, 16001), dtype=np.int16)
+    pcm[1, 4000:] = 0
+    as_f32 = pcm.astype(np.float32) / 32768.0
+    for fb in (sab.Fbank(n_mels=80), sab.Fbank(n_mels=40, n_fft=512)):
+        raw_i, um_i = fb.forward_raw(torch.from_numpy(pcm).to(DEV))
+        raw_f, um_f = fb.forward_raw(cu(as_f32))
+        assert torch.equal(raw_i, raw_f) and torch.equal(um_i, um_f)
+    ref = fbank_np.fbank(as_f32[:1].astype(np.float64), n_mels=80)
+    assert rel_db_err(sab.Fbank(n_mels=80)(torch.from_numpy(pcm[:1]).to(DEV)).cpu().numpy(), ref) < FBANK_TOL
+
+
 # ------------------------------------------------------------------ InputNormalization
 def test_input_normalization_known_answer():
     # test_features.py:107-119
@@ -188,6 +204,33 @@ def test_convae_vs_oracle_10s(precision, tol):
         r_ref, l_ref = anonymizer_ref.convae_forward(x, w, noise)
     assert rel_max(rec.cpu().numpy(), r_ref.numpy()) < tol
     assert np.max(np.abs(logp.cpu().numpy() - l_ref.numpy())) < (1e-4 if precision == "fp32" else 2e-2)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("fp16", 1e-2)])
+def test_convrecon_vs_golden_and_oracle(golden2, precision, tol):
+    """ConvReconstruction ("endtoend", models/EndToEnd.py:36-87; scope row 8(f)-3)."""
+    m, w = load_model((sab.ConvReconstruction, ()), recipe.CONVRECON_SHAPES, precision=precision)
+    for name, (seed, B, T) in {"convrecon_a": (15, 2, 36), "convrecon_b": (16, 1, 101)}.items():
+        with torch.no_grad():
+            rec, logits = m(cu(recipe.make_feats(seed, B, T)))
+        assert rec.shape == (B, T, 80) and logits is None
+        assert rel_max(rec.cpu().numpy(), golden2[name + "_recon"]) < tol
+    # BASELINE unit of work (10 s: T = 1001 frames, L = 80080, no x36 padding needed), ragged chunking
+    m.chunk_utts = 2
+    x = recipe.make_feats(42, 3, 1001)
+    with torch.no_grad():
+        rec, _ = m(cu(x))
+    torch.set_num_threads(8)
+    with torch.no_grad():
+        r_ref = anonymizer_ref.convrecon_forward(x, w)
+    assert rel_max(rec.cpu().numpy(), r_ref.numpy()) < tol
+    # the external classifier hook (EndToEnd.py:81) and the reference's reshape failure for odd T*F
+    m.sex_classifier = lambda feats: (feats.mean(dim=(1, 2)), None, None)
+    with torch.no_grad():
+        rec2, logits = m(cu(x[:1]))
+    assert torch.equal(logits, rec2.mean(dim=(1, 2)))
+    with pytest.raises(RuntimeError):
+        m(cu(np.zeros((1, 3, 5), np.float32)))
 
 
 def test_convae_error_behaviour():
@@ -284,6 +327,22 @@ def test_pipeline_fused_equals_modular_equals_oracle(golden, kind):
         assert rel_max(r.numpy(), rec_h.numpy()[:nb]) < 1e-6      # (fp64 atomics: summation order may differ)
         assert float(np.abs(l.numpy() - logp_h.numpy()[:nb]).max()) < 1e-6
     sp.close()
+    # int16 PCM on the wire (half the H2D bytes) == fp32 path on x / 32768, one-shot and streaming
+    pcm16 = torch.from_numpy(np.clip(np.round(wav * 32768.0), -32768, 32767).astype(np.int16)).pin_memory()
+    pcm32 = (pcm16.to(torch.float32) / 32768.0).pin_memory()
+    r32 = torch.empty(rec_f.shape, dtype=torch.float32).pin_memory()
+    r16 = torch.empty(rec_f.shape, dtype=torch.float32).pin_memory()
+    l32 = torch.empty((4, 2), dtype=torch.float32).pin_memory()
+    l16 = torch.empty((4, 2), dtype=torch.float32).pin_memory()
+    pipe.anonymize_host(pcm32, r32, l32, ws, pool_noise=cu(noise))
+    pipe.anonymize_host(pcm16, r16, l16, ws, pool_noise=cu(noise))
+    assert rel_max(r16.numpy(), r32.numpy()) < 1e-6 and float((l16 - l32).abs().max()) < 1e-6
+    sp = pipe.stream_pipe(4, 16000, torch.device(DEV), depth=2)
+    r16s = torch.full(rec_f.shape, float("nan"), dtype=torch.float32).pin_memory()
+    sp.submit(pcm16, r16s, l16, pool_noise=cu(noise))
+    sp.drain()
+    sp.close()
+    assert rel_max(r16s.numpy(), r32.numpy()) < 1e-6
 
 
 def test_convae_sees_weight_updates():

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(handle, n), n
     assert sorted(_lib.SIGNATURES) == names          # the ctypes binding covers the whole header
-    assert _lib.lib().spanon_abi_version() == 1
+    assert _lib.lib().spanon_abi_version() == 2
     assert _lib.lib().spanon_strerror(-4).decode().startswith("workspace")
 
 
@@ -42,6 +42,10 @@ def test_c_abi_argument_validation_without_device():
     assert L.spanon_fbank_f32(None, 1, 10, 5, None, None, C.byref(cfg), None) == -1  # stride < n
     assert L.spanon_fbank_f32(None, 0, 10, 10, None, None, C.byref(cfg), None) == 0  # empty batch
     assert L.spanon_fbank_f32(None, 1, 10, 10, None, None, C.byref(cfg), None) == -2
+    assert L.spanon_fbank_i16(None, 1, 10, 5, None, None, C.byref(cfg), None) == -1  # int16 wire format: same checks
+    assert L.spanon_fbank_i16(None, 0, 10, 10, None, None, C.byref(cfg), None) == 0
+    assert L.spanon_fbank_i16(None, 1, 10, 10, None, None, C.byref(cfg), None) == -2
+    assert L.spanon_pipe_submit_i16(None, None, 1, None, None, None) == -2
     assert L.spanon_norm_apply(None, None, None, None, 3, None, 80.0, 1, 4, 4, 80, None) == -1
     opts = _lib.ConvAEOpts(_lib.PREC_FP16, 0, 0, 0)
     assert L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts)) > 8 * 80640 * 32 * 2
@@ -51,6 +55,14 @@ def test_c_abi_argument_validation_without_device():
     w = _lib.ConvAEWeights()
     assert L.spanon_convae_fwd(None, C.byref(w), None, None, None, None, 0.0, 0, None, None, None, 0, 1, 37, 81,
                                C.byref(opts), None) == -1                            # L % 4 != 0
+    rw = _lib.ConvReconWeights()
+    assert L.spanon_convrecon_fwd(None, C.byref(rw), None, None, None, 0.0, 0, None, None, 0, 1, 37, 81,
+                                  C.byref(opts), None) == -1                         # L odd (EndToEnd.py:78 reshape)
+    assert L.spanon_convrecon_fwd(None, C.byref(rw), None, None, None, 0.0, 0, None, None, 0, 0, 36, 80,
+                                  C.byref(opts), None) == 0                          # empty batch
+    assert L.spanon_convrecon_fwd(None, C.byref(rw), None, None, None, 0.0, 0, None, None, 0, 1, 36, 80,
+                                  C.byref(opts), None) == -2
+    assert 0 < L.spanon_convrecon_workspace_bytes(8, 1008, 80, C.byref(opts)) < L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts))
     assert L.spanon_knn_mi_stats(None, None, None, 1, 2, 4, 2, 3, None, None, None, None) == -5   # k+1 > N
     assert L.spanon_anonymize_workspace_bytes(0, 64, 160000, 160, 80, C.byref(opts)) > 64 * 160000 * 4
 
@@ -66,6 +78,11 @@ def test_state_dict_keys_match_reference():
     sd = fc.state_dict()
     assert set(sd) == set(recipe.FCAE_SHAPES)
     for k, shp in recipe.FCAE_SHAPES.items():
+        assert tuple(sd[k].shape) == tuple(shp), k
+    cr = sab.ConvReconstruction()
+    sd = cr.state_dict()
+    assert set(sd) == set(recipe.CONVRECON_SHAPES)                   # models/EndToEnd.py:40-54
+    for k, shp in recipe.CONVRECON_SHAPES.items():
         assert tuple(sd[k].shape) == tuple(shp), k
     assert sum(p.numel() for p in m.parameters()) == 533123
     m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in recipe.make_weights(recipe.CONVAE_SHAPES, 1).items()})

@@ -95,6 +95,13 @@ def test_convae_oracle_vs_golden(golden):
         assert np.max(np.abs(logp.numpy() - golden[name + "_logp"])) < 1e-5
 
 
+def test_convrecon_oracle_vs_golden(golden2):
+    w = recipe.make_weights(recipe.CONVRECON_SHAPES, 8886)
+    for name, (seed, B, T) in {"convrecon_a": (15, 2, 36), "convrecon_b": (16, 1, 101)}.items():
+        rec = anonymizer_ref.convrecon_forward(recipe.make_feats(seed, B, T), w)
+        assert rel_max(rec.numpy(), golden2[name + "_recon"]) < 1e-5
+
+
 def test_fcae_oracle_vs_golden(golden):
     w = recipe.make_weights(recipe.FCAE_SHAPES, 8886)
     x = recipe.make_feats(7, 3, 101)

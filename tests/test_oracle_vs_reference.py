@@ -60,6 +60,18 @@ def test_convae_live(R):
     assert np.abs(l2.numpy() - logp.numpy()).max() < 1e-5
 
 
+def test_convrecon_live(R):
+    """models/EndToEnd.py:66-78 executed from the reference tree vs the oracle restatement."""
+    w = recipe.make_weights(recipe.CONVRECON_SHAPES, 779)
+    m = R["ConvReconstruction"]().eval()
+    m.load_state_dict({k: t(v) for k, v in w.items()}, strict=False)
+    x = recipe.make_feats(106, 2, 37)
+    with torch.no_grad():
+        y = t(x).reshape(2, 37 * 80).unsqueeze(1)
+        y = m.encoder(y).squeeze(1).reshape(2, 37, 80)
+    assert rel_max(anonymizer_ref.convrecon_forward(x, w).numpy(), y.numpy()) < 1e-5
+
+
 def test_fcae_live(R):
     w = recipe.make_weights(recipe.FCAE_SHAPES, 778)
     m = R["FullyConnectedAutoencoder"](80, 2).eval()
