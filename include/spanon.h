@@ -224,6 +224,38 @@ SPANON_API int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWei
                          int64_t F, const SpanonConvAEOpts* opts, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * External x-vector gender classifier on (anonymized) features -- the evaluation half of
+ * gender_classifier_recon.yaml / evaluator_inference.yaml
+ * replaces  EncoderClassifier.classify_batch_feats  speechbrain/speechbrain/pretrained/interfaces.py:825-829 (:762-776)
+ *           Xvector.forward       speechbrain/speechbrain/lobes/models/Xvector.py:95-108  (layers :60-93)
+ *           Classifier            speechbrain/speechbrain/lobes/models/Xvector.py:111-172
+ *           Conv1d "same"/reflect speechbrain/speechbrain/nnet/CNN.py:349-352,400-403
+ *           StatisticsPooling     speechbrain/speechbrain/nnet/pooling.py:263-312
+ * Architecture fixed to evaluator_inference.yaml:34-48: TDNN 80->512->512->512->512->1500 (k 5,3,3,1,1; dilation
+ * 1,2,3,1,1), LeakyReLU, eval-mode BatchNorm, embedding 128, one DNN block, 2 classes.  fp16 operands on the tcgen05
+ * tensor cores with fp32 accumulation.
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonXvectorWeights {
+  const float* tdnn_w[5]; const float* tdnn_b[5];   /* embedding_model blocks.{0,3,6,9,12}.conv  [Cout,Cin,k] / [Cout] */
+  SpanonBatchNorm tdnn_bn[5];                        /* blocks.{2,5,8,11,14}.norm                                      */
+  const float* emb_w; const float* emb_b;            /* blocks.16.w  [128,3000] / [128]                                */
+  SpanonBatchNorm clf_norm;                          /* classifier norm.norm (128)                                     */
+  const float* dnn_w; const float* dnn_b;            /* classifier DNN.block_0.linear.w  [128,128] / [128]             */
+  SpanonBatchNorm dnn_bn;                            /* classifier DNN.block_0.norm.norm                               */
+  const float* out_w; const float* out_b;            /* classifier out.w  [2,128] / [2]                                */
+} SpanonXvectorWeights;
+
+SPANON_API size_t spanon_xvector_workspace_bytes(int64_t B, int64_t T);
+/* feats [B,T,80] fp32 (already normalised, like classify_batch_feats expects), rel_len [B] relative lengths (NULL = 1.0):
+ * pooling runs over round(rel_len * T) frames.  pool_noise [B,1500] is the tensor StatisticsPooling adds to the mean
+ * (NULL = none).  emb_out [B,128] (NULL to skip) = the x-vector; logp [B,2] = log posteriors.  weights_prepared = 1: the
+ * workspace still holds the packed weights of an earlier call with the same weights. */
+SPANON_API int spanon_xvector_classify(const float* feats, const float* rel_len, const SpanonXvectorWeights* w,
+                            const float* pool_noise, float* emb_out, float* logp, void* workspace,
+                            size_t workspace_bytes, int64_t B, int64_t T, int64_t F, int32_t weights_prepared,
+                            void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Loss statistics
  * replaces  CosineSimilarityLoss.forward   utils/cosine_similarity_loss.py:53-56
  *           _pairwise_dists / ClusterMI._mutual_information  utils/ClusterMI.py:12-63,88-121

@@ -84,7 +84,15 @@ def load():
     gmi = importlib.import_module("spanon_ref_utils.GroupSamplingMI")
     mil = importlib.import_module("spanon_ref_utils.mi_loss")
 
+    # Xvector.py reaches its layers through attribute access on the package (sb.nnet.containers.Sequential, ...):
+    # wire the leaf modules onto the namespace stubs
+    for sub in ("containers", "linear", "normalization", "activations", "CNN", "pooling"):
+        setattr(sb.nnet, sub, importlib.import_module("speechbrain.nnet." + sub))
+    xvec = importlib.import_module("speechbrain.lobes.models.Xvector")
+
     _loaded.update(
+        Xvector=xvec.Xvector,
+        XvectorClassifier=xvec.Classifier,
         Fbank=feats_lobe.Fbank,
         STFT=feats_proc.STFT,
         spectral_magnitude=feats_proc.spectral_magnitude,

@@ -9,8 +9,8 @@ from .features import Fbank, InputNormalization, pad_time  # noqa: F401
 from .losses import (ClusterMI, CosineSimilarityLoss, GroupSampler, GroupSamplingMI, MILoss,  # noqa: F401
                      SimilarityMetricsStats, cosine_distance_2d, knn_mi)
 from .models import (GLU, ConvAutoencoder, ConvReconstruction, FullyConnectedAutoencoder, FullyConnSexClassifier,  # noqa: F401
-                     GradReverse, StatisticsPooling, TDNNSexClassifier)
+                     GradReverse, StatisticsPooling, TDNNSexClassifier, Xvector, XvectorClassifier, XvectorHead)
 from .pipeline import AnonymizerPipeline, StreamPipe, shard_range  # noqa: F401
 
-__all__ = ["Fbank", "InputNormalization", "ConvAutoencoder", "ConvReconstruction", "FullyConnectedAutoencoder", "CosineSimilarityLoss",
+__all__ = ["Fbank", "InputNormalization", "ConvAutoencoder", "ConvReconstruction", "XvectorClassifier", "FullyConnectedAutoencoder", "CosineSimilarityLoss",
            "MILoss", "ClusterMI", "GroupSamplingMI", "AnonymizerPipeline", "StreamPipe", "shard_range", "pad_time", "lib"]

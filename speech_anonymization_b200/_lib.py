@@ -59,6 +59,13 @@ class ConvReconWeights(C.Structure):
                 ("in_w", C.c_void_p * 4), ("in_b", C.c_void_p * 4)]
 
 
+class XvectorWeights(C.Structure):
+    _fields_ = [("tdnn_w", C.c_void_p * 5), ("tdnn_b", C.c_void_p * 5), ("tdnn_bn", BatchNorm * 5),
+                ("emb_w", C.c_void_p), ("emb_b", C.c_void_p), ("clf_norm", BatchNorm),
+                ("dnn_w", C.c_void_p), ("dnn_b", C.c_void_p), ("dnn_bn", BatchNorm),
+                ("out_w", C.c_void_p), ("out_b", C.c_void_p)]
+
+
 class ConvAEOpts(C.Structure):
     _fields_ = [("precision", C.c_int32), ("chunk_utts", C.c_int32), ("skip_classifier", C.c_int32),
                 ("weights_prepared", C.c_int32)]
@@ -103,6 +110,10 @@ SIGNATURES = {
     "spanon_convrecon_fwd": (C.c_int, [C.c_void_p, C.POINTER(ConvReconWeights), C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_float, C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64, C.c_int64,
                                        C.c_int64, C.POINTER(ConvAEOpts), C.c_void_p]),
+    "spanon_xvector_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "spanon_xvector_classify": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(XvectorWeights), C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int32,
+                                          C.c_void_p]),
     "spanon_cosine_loss": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_float,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "spanon_cosine_loss_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,

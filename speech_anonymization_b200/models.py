@@ -2,6 +2,8 @@
 
   ConvAutoencoder / TDNNSexClassifier / GLU / GradReverse   models/ConvAutoEncoder.py:12-69,113-200
   ConvReconstruction ("endtoend")                           models/EndToEnd.py:36-87
+  Xvector / Classifier / EncoderClassifier (feature path)   speechbrain/speechbrain/lobes/models/Xvector.py:19-172,
+                                                            speechbrain/speechbrain/pretrained/interfaces.py:762-829
   FullyConnectedAutoencoder / FullyConnSexClassifier        models/FullyConnected.py:65-159
   StatisticsPooling                                         speechbrain/speechbrain/nnet/pooling.py:229-326
 
@@ -314,6 +316,168 @@ class ConvReconstruction(nn.Module):
         if self.sex_classifier is not None:   # EndToEnd.py:81
             logits, _score, _index = self.sex_classifier(recon)
         return recon, logits
+
+
+class _SbConv1d(nn.Module):
+    """Parameter container with the key layout of speechbrain.nnet.CNN.Conv1d (`conv.weight`, `conv.bias`)."""
+
+    def __init__(self, cin, cout, k, dilation):
+        super().__init__()
+        self.conv = nn.Conv1d(cin, cout, k, dilation=dilation, padding=0)
+
+
+class _SbBatchNorm1d(nn.Module):
+    """speechbrain.nnet.normalization.BatchNorm1d (`norm.*`)."""
+
+    def __init__(self, n):
+        super().__init__()
+        self.norm = nn.BatchNorm1d(n)
+
+
+class _SbLinear(nn.Module):
+    """speechbrain.nnet.linear.Linear (`w.*`)."""
+
+    def __init__(self, n_in, n_out):
+        super().__init__()
+        self.w = nn.Linear(n_in, n_out)
+
+
+class Xvector(nn.Module):
+    """Parameter container for speechbrain.lobes.models.Xvector.Xvector (Xvector.py:45-93) in the configuration of
+    evaluator_inference.yaml:34-41; `state_dict()` keys = the reference's embedding_model.ckpt (`blocks.{0,3,6,9,12}.conv.*`,
+    `blocks.{2,5,8,11,14}.norm.*`, `blocks.16.w.*`).  Computed inside XvectorClassifier."""
+
+    def __init__(self, device="cpu", activation=nn.LeakyReLU, tdnn_blocks=5, tdnn_channels=[512, 512, 512, 512, 1500],
+                 tdnn_kernel_sizes=[5, 3, 3, 1, 1], tdnn_dilations=[1, 2, 3, 1, 1], lin_neurons=128, in_channels=80):
+        super().__init__()
+        if (activation is not nn.LeakyReLU or tdnn_blocks != 5 or list(tdnn_channels) != [512, 512, 512, 512, 1500]
+                or list(tdnn_kernel_sizes) != [5, 3, 3, 1, 1] or list(tdnn_dilations) != [1, 2, 3, 1, 1]
+                or lin_neurons != 128 or in_channels != 80):
+            raise NotImplementedError("the CUDA x-vector path is built for evaluator_inference.yaml's architecture "
+                                      "(80 -> 512,512,512,512,1500; k 5,3,3,1,1; dilation 1,2,3,1,1; LeakyReLU; 128-d)")
+        self.blocks = nn.ModuleList()
+        cin = in_channels
+        for c, k, d in zip(tdnn_channels, tdnn_kernel_sizes, tdnn_dilations):
+            self.blocks.extend([_SbConv1d(cin, c, k, d), activation(), _SbBatchNorm1d(c)])
+            cin = c
+        self.blocks.append(StatisticsPooling())
+        self.blocks.append(_SbLinear(2 * cin, lin_neurons))
+
+    def forward(self, x, lens=None):
+        raise NotImplementedError("Xvector runs fused inside XvectorClassifier.classify_batch_feats")
+
+
+class _SbDNNBlock(nn.Module):
+    def __init__(self, n_in, n_out, activation):
+        super().__init__()
+        self.linear = _SbLinear(n_in, n_out)
+        self.act = activation()
+        self.norm = _SbBatchNorm1d(n_out)
+
+
+class _SbDNN(nn.Module):
+    def __init__(self, n_in, n_out, activation):
+        super().__init__()
+        self.block_0 = _SbDNNBlock(n_in, n_out, activation)
+
+
+class XvectorHead(nn.Module):
+    """Parameter container for speechbrain.lobes.models.Xvector.Classifier (Xvector.py:111-172) as configured by
+    evaluator_inference.yaml:43-48; keys = classifier.ckpt (`norm.norm.*`, `DNN.block_0.linear.w.*`,
+    `DNN.block_0.norm.norm.*`, `out.w.*`)."""
+
+    def __init__(self, input_shape=(None, None, 128), activation=nn.LeakyReLU, lin_blocks=1, lin_neurons=128,
+                 out_neurons=2):
+        super().__init__()
+        if activation is not nn.LeakyReLU or lin_blocks != 1 or lin_neurons != 128 or out_neurons != 2 or input_shape[-1] != 128:
+            raise NotImplementedError("the CUDA classifier head is built for evaluator_inference.yaml (128 -> 128 -> 2)")
+        self.act = activation()
+        self.norm = _SbBatchNorm1d(128)
+        self.DNN = _SbDNN(128, 128, activation)
+        self.out = _SbLinear(128, out_neurons)
+
+
+class XvectorClassifier(nn.Module):
+    """The external gender classifier of the evaluation configs: drop-in for the parts of
+    speechbrain.pretrained.EncoderClassifier the reference uses on FEATURES (interfaces.py:762-776, 825-829) with
+    `mods.embedding_model` = Xvector and `mods.classifier` = Classifier of evaluator_inference.yaml.
+
+    classify_batch_feats(feats [B,T,80], wav_lens) -> (log-probs [B,2], score [B], index [B]);
+    encode_batch_feat(feats, wav_lens) -> embeddings [B,1,128].  `pool_noise` [B,1500] fixes StatisticsPooling's noise.
+    Usable as ConvReconstruction(sex_classifier=XvectorClassifier(...).classify_batch_feats)."""
+
+    def __init__(self, embedding_model=None, classifier=None):
+        super().__init__()
+        self.embedding_model = embedding_model if embedding_model is not None else Xvector()
+        self.classifier = classifier if classifier is not None else XvectorHead()
+
+    def weight_struct(self):
+        e, c = self.embedding_model, self.classifier
+        w = _lib.XvectorWeights()
+        for i in range(5):
+            w.tdnn_w[i], w.tdnn_b[i] = _p(e.blocks[3 * i].conv.weight), _p(e.blocks[3 * i].conv.bias)
+            w.tdnn_bn[i] = _bn(e.blocks[3 * i + 2].norm)
+        w.emb_w, w.emb_b = _p(e.blocks[16].w.weight), _p(e.blocks[16].w.bias)
+        w.clf_norm = _bn(c.norm.norm)
+        w.dnn_w, w.dnn_b = _p(c.DNN.block_0.linear.w.weight), _p(c.DNN.block_0.linear.w.bias)
+        w.dnn_bn = _bn(c.DNN.block_0.norm.norm)
+        w.out_w, w.out_b = _p(c.out.w.weight), _p(c.out.w.bias)
+        return w
+
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d.pop("_ws_cache", None)
+        return d
+
+    def _run(self, feats, wav_lens, pool_noise):
+        _lib.require_cuda(feats, "feats")
+        _forward_only_guard(self, feats)
+        if feats.dim() != 3 or feats.shape[2] != 80:
+            raise ValueError("XvectorClassifier expects [batch, time, 80] features")
+        x = feats.contiguous()
+        B, T, F = x.shape
+        dev = x.device
+        emb = torch.empty((B, 1, 128), dtype=torch.float32, device=dev)
+        logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
+        if B == 0:
+            return emb, logp
+        if wav_lens is not None:
+            wav_lens = wav_lens.to(device=dev, dtype=torch.float32).contiguous()
+        if pool_noise is None:
+            pool_noise = self.embedding_model.blocks[15]._get_gauss_noise((B, 1500), device=dev)
+        pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
+        w = self.weight_struct()
+        L = _lib.lib()
+        ws_bytes = L.spanon_xvector_workspace_bytes(B, T)
+        key = (B, T, str(dev), tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers())))
+        cache = self.__dict__.get("_ws_cache")
+        if cache is None or cache[0].numel() != ws_bytes or cache[0].device != dev:
+            cache = [torch.empty((ws_bytes,), dtype=torch.uint8, device=dev), None]
+            self.__dict__["_ws_cache"] = cache
+        prepared = 1 if cache[1] == key else 0
+        cache[1] = key
+        with torch.cuda.device(dev):
+            _lib.check(L.spanon_xvector_classify(_lib.ptr(x), _lib.ptr(wav_lens), C.byref(w), _lib.ptr(pool_noise),
+                                                 _lib.ptr(emb), _lib.ptr(logp), _lib.ptr(cache[0]), ws_bytes, B, T, F,
+                                                 prepared, _lib.stream_ptr(dev)), "xvector_classify")
+        return emb, logp
+
+    @torch.no_grad()
+    def encode_batch_feat(self, feats, wav_lens=None, normalize=False, pool_noise=None):
+        """interfaces.py:762-776 (normalize=True needs hparams.mean_var_norm_emb, which evaluator_inference.yaml lacks)."""
+        if normalize:
+            raise NotImplementedError("mean_var_norm_emb is not part of evaluator_inference.yaml")
+        return self._run(feats, wav_lens, pool_noise)[0]
+
+    @torch.no_grad()
+    def classify_batch_feats(self, feat, wav_lens=None, pool_noise=None):
+        """interfaces.py:825-829."""
+        _, out_prob = self._run(feat, wav_lens, pool_noise)
+        score, index = torch.max(out_prob, dim=-1)
+        return out_prob, score, index
+
+    def forward(self, feats, wav_lens=None):
+        return self.classify_batch_feats(feats, wav_lens)
 
 
 class FullyConnSexClassifier(nn.Module):

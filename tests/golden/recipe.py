@@ -50,6 +50,21 @@ CONVRECON_SHAPES = {   # models/EndToEnd.py:40-54
     "encoder.12.weight": (1, 32, 15), "encoder.12.bias": (1,),
 }
 
+# evaluator_inference.yaml:34-48 (speechbrain/lobes/models/Xvector.py): embedding_model.ckpt / classifier.ckpt keys
+XVECTOR_EMB_SHAPES = {"blocks.16.w.weight": (128, 3000), "blocks.16.w.bias": (128,)}
+for _i, (_cin, _cout, _k) in enumerate(((80, 512, 5), (512, 512, 3), (512, 512, 3), (512, 512, 1), (512, 1500, 1))):
+    XVECTOR_EMB_SHAPES["blocks.%d.conv.weight" % (3 * _i)] = (_cout, _cin, _k)
+    XVECTOR_EMB_SHAPES["blocks.%d.conv.bias" % (3 * _i)] = (_cout,)
+    for _s in ("weight", "bias", "running_mean", "running_var"):
+        XVECTOR_EMB_SHAPES["blocks.%d.norm.%s" % (3 * _i + 2, _s)] = (_cout,)
+    XVECTOR_EMB_SHAPES["blocks.%d.norm.num_batches_tracked" % (3 * _i + 2)] = ()
+XVECTOR_CLF_SHAPES = {"DNN.block_0.linear.w.weight": (128, 128), "DNN.block_0.linear.w.bias": (128,),
+                      "out.w.weight": (2, 128), "out.w.bias": (2,)}
+for _p in ("norm.norm", "DNN.block_0.norm.norm"):
+    for _s in ("weight", "bias", "running_mean", "running_var"):
+        XVECTOR_CLF_SHAPES["%s.%s" % (_p, _s)] = (128,)
+    XVECTOR_CLF_SHAPES["%s.num_batches_tracked" % _p] = ()
+
 FCAE_SHAPES = {
     "encoder.0.weight": (60, 80), "encoder.0.bias": (60,),
     "encoder.2.weight": (40, 60), "encoder.2.bias": (40,),

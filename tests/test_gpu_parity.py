@@ -233,6 +233,56 @@ def test_convrecon_vs_golden_and_oracle(golden2, precision, tol):
         m(cu(np.zeros((1, 3, 5), np.float32)))
 
 
+def _load_xvector(seed=1230):
+    from oracle import xvector_ref  # noqa: F401
+    m = sab.XvectorClassifier()
+    we = recipe.make_weights(recipe.XVECTOR_EMB_SHAPES, seed)
+    wc = recipe.make_weights(recipe.XVECTOR_CLF_SHAPES, seed)
+    m.embedding_model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in we.items()})
+    m.classifier.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in wc.items()})
+    return m.to(DEV).eval(), we, wc
+
+
+def test_xvector_classifier_vs_golden_and_oracle(golden2):
+    """External x-vector gender classifier on features (scope row 8(f)-2): fp16 tensor-core TDNN, <= 1e-2 rel. on the
+    x-vector, <= 1e-2 abs. on the log posteriors; valid-frame counts of the pooling bit-exact (ragged lengths)."""
+    from oracle import xvector_ref
+    m, we, wc = _load_xvector()
+    for name, (seed, B, T, ragged) in {"xvec_a": (21, 3, 101, True), "xvec_b": (22, 2, 300, False)}.items():
+        lens = cu(np.linspace(0.6, 1.0, B).astype(np.float32)) if ragged else None
+        noise = cu(recipe.make_noise(seed, B, 1500))
+        x = cu(recipe.make_feats(seed, B, T))
+        emb = m.encode_batch_feat(x, lens, pool_noise=noise)
+        out_prob, score, index = m.classify_batch_feats(x, lens, pool_noise=noise)
+        assert emb.shape == (B, 1, 128) and out_prob.shape == (B, 2) and score.shape == (B,) and index.shape == (B,)
+        assert rel_max(emb.cpu().numpy(), golden2[name + "_emb"]) < 1e-2
+        assert np.max(np.abs(out_prob.cpu().numpy() - golden2[name + "_logp"])) < 1e-2
+        assert torch.equal(index.cpu(), torch.from_numpy(golden2[name + "_logp"]).argmax(dim=-1))
+    # BASELINE unit of work (10 s = 1001 frames, last 128-frame tile partly empty), ragged lengths, weights reused
+    B, T = 4, 1001
+    x = recipe.make_feats(43, B, T)
+    lens = np.array([1.0, 0.5, 0.7513, 0.9], np.float32)
+    noise = recipe.make_noise(43, B, 1500)
+    emb = m.encode_batch_feat(cu(x), cu(lens), pool_noise=cu(noise))
+    out_prob, _, _ = m.classify_batch_feats(cu(x), cu(lens), pool_noise=cu(noise))
+    torch.set_num_threads(8)
+    with torch.no_grad():
+        e_ref, l_ref = xvector_ref.classify_batch_feats(x, lens, we, wc, noise)
+    assert rel_max(emb.cpu().numpy(), e_ref.numpy()) < 1e-2
+    assert np.max(np.abs(out_prob.cpu().numpy() - l_ref.numpy())) < 1e-2
+    # an in-place weight update must be seen (packed weights are re-made)
+    with torch.no_grad():
+        m.classifier.out.w.bias.add_(torch.tensor([0.5, -0.5], device=DEV))
+    out2, _, _ = m.classify_batch_feats(cu(x), cu(lens), pool_noise=cu(noise))
+    assert float((out2 - out_prob).abs().max()) > 0.1
+    # the composed evaluation path of gender_classifier_recon.yaml: anonymizer output -> external classifier
+    cr, _ = load_model((sab.ConvReconstruction, ()), recipe.CONVRECON_SHAPES, precision="fp16")
+    cr.sex_classifier = m.classify_batch_feats
+    with torch.no_grad():
+        rec, logits = cr(cu(x[:2]))
+    assert logits.shape == (2, 2) and bool(torch.isfinite(logits).all())
+
+
 def test_convae_error_behaviour():
     m, _ = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES)
     with pytest.raises(RuntimeError):           # the reference's reshape fails when T*F % 4 != 0

@@ -63,6 +63,12 @@ def test_c_abi_argument_validation_without_device():
     assert L.spanon_convrecon_fwd(None, C.byref(rw), None, None, None, 0.0, 0, None, None, 0, 1, 36, 80,
                                   C.byref(opts), None) == -2
     assert 0 < L.spanon_convrecon_workspace_bytes(8, 1008, 80, C.byref(opts)) < L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts))
+    xw = _lib.XvectorWeights()
+    assert L.spanon_xvector_classify(None, None, C.byref(xw), None, None, None, None, 0, 1, 101, 40, 0, None) == -1  # F != 80
+    assert L.spanon_xvector_classify(None, None, C.byref(xw), None, None, None, None, 0, 1, 3, 80, 0, None) == -1    # T <= reflect pad
+    assert L.spanon_xvector_classify(None, None, C.byref(xw), None, None, None, None, 0, 0, 101, 80, 0, None) == 0
+    assert L.spanon_xvector_classify(None, None, C.byref(xw), None, None, None, None, 0, 1, 101, 80, 0, None) == -2
+    assert L.spanon_xvector_workspace_bytes(64, 1001) > 64 * 1001 * 1536 * 2
     assert L.spanon_knn_mi_stats(None, None, None, 1, 2, 4, 2, 3, None, None, None, None) == -5   # k+1 > N
     assert L.spanon_anonymize_workspace_bytes(0, 64, 160000, 160, 80, C.byref(opts)) > 64 * 160000 * 4
 
@@ -84,6 +90,11 @@ def test_state_dict_keys_match_reference():
     assert set(sd) == set(recipe.CONVRECON_SHAPES)                   # models/EndToEnd.py:40-54
     for k, shp in recipe.CONVRECON_SHAPES.items():
         assert tuple(sd[k].shape) == tuple(shp), k
+    xv = sab.XvectorClassifier()                                     # evaluator_inference.yaml checkpoints
+    assert set(xv.embedding_model.state_dict()) == set(recipe.XVECTOR_EMB_SHAPES)
+    assert set(xv.classifier.state_dict()) == set(recipe.XVECTOR_CLF_SHAPES)
+    for k, shp in recipe.XVECTOR_EMB_SHAPES.items():
+        assert tuple(xv.embedding_model.state_dict()[k].shape) == tuple(shp), k
     assert sum(p.numel() for p in m.parameters()) == 533123
     m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in recipe.make_weights(recipe.CONVAE_SHAPES, 1).items()})
 

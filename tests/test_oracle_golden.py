@@ -102,6 +102,19 @@ def test_convrecon_oracle_vs_golden(golden2):
         assert rel_max(rec.numpy(), golden2[name + "_recon"]) < 1e-5
 
 
+def test_xvector_oracle_vs_golden(golden2):
+    from oracle import xvector_ref
+    we = recipe.make_weights(recipe.XVECTOR_EMB_SHAPES, 1230)
+    wc = recipe.make_weights(recipe.XVECTOR_CLF_SHAPES, 1230)
+    for name, (seed, B, T, ragged) in {"xvec_a": (21, 3, 101, True), "xvec_b": (22, 2, 300, False)}.items():
+        lens = np.linspace(0.6, 1.0, B).astype(np.float32) if ragged else None
+        emb, logp = xvector_ref.classify_batch_feats(recipe.make_feats(seed, B, T), lens, we, wc,
+                                                     recipe.make_noise(seed, B, 1500))
+        assert emb.shape == (B, 1, 128) and logp.shape == (B, 2)
+        assert rel_max(emb.numpy(), golden2[name + "_emb"]) < 1e-5
+        assert np.max(np.abs(logp.numpy() - golden2[name + "_logp"])) < 1e-5
+
+
 def test_fcae_oracle_vs_golden(golden):
     w = recipe.make_weights(recipe.FCAE_SHAPES, 8886)
     x = recipe.make_feats(7, 3, 101)

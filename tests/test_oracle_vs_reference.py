@@ -72,6 +72,29 @@ def test_convrecon_live(R):
     assert rel_max(anonymizer_ref.convrecon_forward(x, w).numpy(), y.numpy()) < 1e-5
 
 
+def test_xvector_live(R):
+    """The reference's Xvector + Classifier (evaluator_inference.yaml) executed from the reference tree vs the oracle."""
+    from oracle import xvector_ref
+    we = recipe.make_weights(recipe.XVECTOR_EMB_SHAPES, 780)
+    wc = recipe.make_weights(recipe.XVECTOR_CLF_SHAPES, 780)
+    em = R["Xvector"](in_channels=80, activation=torch.nn.LeakyReLU, tdnn_blocks=5, tdnn_channels=[512, 512, 512, 512, 1500],
+                      tdnn_kernel_sizes=[5, 3, 3, 1, 1], tdnn_dilations=[1, 2, 3, 1, 1], lin_neurons=128).eval()
+    cl = R["XvectorClassifier"](input_shape=[None, None, 128], activation=torch.nn.LeakyReLU, lin_blocks=1,
+                                lin_neurons=128, out_neurons=2).eval()
+    em.load_state_dict({k: t(v) for k, v in we.items()})
+    cl.load_state_dict({k: t(v) for k, v in wc.items()})
+    x = recipe.make_feats(107, 2, 57)
+    lens = np.array([0.75, 1.0], np.float32)
+    noise = recipe.make_noise(107, 2, 1500)
+    R["StatisticsPooling"]._get_gauss_noise = lambda self, shape, device="cpu": t(noise)
+    with torch.no_grad():
+        emb = em(t(x), t(lens))
+        logp = cl(emb).squeeze(1)
+    e2, l2 = xvector_ref.classify_batch_feats(x, lens, we, wc, noise)
+    assert rel_max(e2.numpy(), emb.numpy()) < 1e-5
+    assert np.abs(l2.numpy() - logp.numpy()).max() < 1e-5
+
+
 def test_fcae_live(R):
     w = recipe.make_weights(recipe.FCAE_SHAPES, 778)
     m = R["FullyConnectedAutoencoder"](80, 2).eval()
