@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=4, help="utterances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the timed scope-row-8(f) extras (ConvReconstruction, x-vector)")
     ap.add_argument("--chunk", type=int, default=0, help="utterances per L2-resident chunk of the conv stack (0 = library default)")
     return ap.parse_args()
 
@@ -111,7 +112,35 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
 
+    def _nvml_handle(self):
+        """NVML in-process (no fork: spawning nvidia-smi from a process with a CUDA context can stall every thread for
+        milliseconds, which starves the launch loop being timed).  Returns None if pynvml is unusable."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            return pynvml, h
+        except Exception:
+            return None
+
     def run(self):
+        nv = self._nvml_handle()
+        while nv is not None and not self.stop_flag:
+            try:
+                pynvml, h = nv
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+                r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                act = lambda bit: "Active" if r & bit else "Not Active"   # noqa: E731
+                self.rows.append([str(sm), str(mx), act(0x8), act(0x40), act(0x20), act(0x4)])
+            except Exception:
+                nv = None
+                break
+            time.sleep(0.02)
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -335,6 +364,12 @@ def run_ours(a):
         gbs = BYTES_FBANK_UTT * B / (fb["ms_per_step"] * 1e-3) / 1e9
         stages["fbank"] = {"ms_per_step": fb["ms_per_step"], "GB/s": gbs, "frac_hbm": gbs / pk["hbm"]}
 
+    # ---- scope rows 8(f) built so far, timed next to the headline path (not part of `value`): the "endtoend"
+    #      anonymizer and the external x-vector gender classifier that evaluates anonymized features (config 3)
+    extras = None
+    if rank == 0 and world == 1 and a.workload == "convae" and not a.no_extras:
+        extras = time_extras(sab, _lib, recipe, dev, B, T)
+
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         v, dt, cores = time_cpu(a.workload, a.cpu_sample, 2, 1)
@@ -348,11 +383,52 @@ def run_ours(a):
                 "dtype": a.precision if a.workload == "convae" else "fp32", "data": "synthetic",
                 "config": workload_config(a, world),
                 "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roof,
-                "cpu_baseline": cpu, "stages": stages, "kernels": kern}
+                "cpu_baseline": cpu, "stages": stages, "kernels": kern, "extras": extras}
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+
+
+def time_extras(sab, _lib, recipe, dev, B, T, iters=6):
+    """ConvReconstruction forward and x-vector classification of B x T x 80 feature batches (device-resident)."""
+    def load(m, shapes, seed):
+        w = recipe.make_weights(shapes, seed)
+        m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in w.items()})
+        return m.to(dev).eval()
+
+    feats = [torch.from_numpy(recipe.make_feats(50 + i, B, T)).to(dev) for i in range(3)]   # 3 x 19 MB inputs
+    cr = load(sab.ConvReconstruction(), recipe.CONVRECON_SHAPES, 8886)
+    xv = sab.XvectorClassifier()
+    load(xv.embedding_model, recipe.XVECTOR_EMB_SHAPES, 1230)
+    load(xv.classifier, recipe.XVECTOR_CLF_SHAPES, 1230)
+    xv = xv.to(dev).eval()
+    noise = torch.from_numpy(recipe.make_noise(9, B, 1500)).to(dev)
+    out = {}
+    for name, fn in (("convrecon_fwd", lambda x: cr(x)), ("xvector_classify", lambda x: xv.classify_batch_feats(x, pool_noise=noise))):
+        with torch.no_grad():
+            for i in range(3):
+                fn(feats[i % 3])
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(iters):
+                fn(feats[i % 3])
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            _lib.profile_begin(dev)
+            fn(feats[0])
+            prof = _lib.profile_end()
+        out[name] = {"ms_per_batch": ms, "batch": B, "frames": T, "audio_s_per_s": B * UTT_SECONDS / (ms * 1e-3),
+                     "kernels_ms": {k: v[1] for k, v in prof.items()}}
+    # x-vector TDNN: 2 * T * sum(k * cin * cout) flops per utterance (Xvector.py:60-79 with evaluator_inference.yaml)
+    macs = T * (5 * 80 * 512 + 3 * 512 * 512 * 2 + 512 * 512 + 512 * 1500)
+    g = out["xvector_classify"]
+    gemm_ms = sum(v for k, v in g["kernels_ms"].items() if k.startswith("xv_gemm"))
+    g["tdnn_gflop_per_utt"] = 2 * macs / 1e9
+    g["tdnn_tflops"] = 2 * macs * B / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    return out
 
 
 def workload_config(a, world):

@@ -3,6 +3,7 @@
   launches:  python tools/ncu_summarize.py launches gpurun_out/launches_r01.csv  > profiles/r01_launches.md
   full:      python tools/ncu_summarize.py full /tmp/raw.csv                     > profiles/r01_ncu_full.md
              (raw.csv = `ncu -i gpurun_out/prof_r01.ncu-rep --page raw --csv`)
+  traffic:   python tools/ncu_summarize.py traffic /tmp/raw.csv                  > profiles/r01_traffic.json
 """
 import csv, re, sys
 from collections import OrderedDict
@@ -69,5 +70,29 @@ def full(path):
         print("| %s | " % short(r[kn]) + " | ".join(r[ix[l]] for l in labels) + " |")
 
 
+def traffic(path):
+    """Per-launch DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) by kernel -> JSON for bench.py's
+    roofline.traffic (profiles/rNN_traffic.json)."""
+    import json
+    rows = list(csv.reader(open(path)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    col = lambda key: [i for i, n in enumerate(hdr) if n == key or n.endswith("." + key)][0]   # noqa: E731
+    kn, rd, wr, tm = hdr.index("Kernel Name"), col("dram__bytes_read.sum"), col("dram__bytes_write.sum"), col("gpu__time_duration.sum")
+    scale = {"Mbyte": 1.0, "Gbyte": 1e3, "Kbyte": 1e-3, "byte": 1e-6}
+    agg = OrderedDict()
+    for r in data:
+        k = agg.setdefault(short(r[kn]), [0.0, 0.0, 0])
+        k[0] += float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]]
+        k[1] += float(r[tm]) * (1e-3 if units[tm] in ("ns", "nsecond") else 1.0)
+        k[2] += 1
+    out = {"source": "ncu --set full --clock-control none (tools/ncu_round.sh), batch 60 x 10 s",
+           "unit": "MB per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
+           "kernels": {k: {"traffic_mb": v[0] / v[2], "time_us": v[1] / v[2], "n": v[2]} for k, v in agg.items()}}
+    conv = [(k, v) for k, v in agg.items() if k.startswith("tapgemm_tc_kernel") or k.startswith("first_layer")]
+    n = sum(v[2] for _, v in conv)
+    out["conv_stack"] = {"traffic_mb_per_launch": sum(v[0] for _, v in conv) / n, "launches_captured": n}
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](sys.argv[2])
