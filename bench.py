@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=4, help="utterances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graphs", action="store_true", help="launch every kernel of a step from the host instead of replaying a CUDA graph")
     ap.add_argument("--no-extras", action="store_true", help="skip the timed scope-row-8(f) extras (ConvReconstruction, x-vector)")
     ap.add_argument("--chunk", type=int, default=0, help="utterances per L2-resident chunk of the conv stack (0 = library default)")
     return ap.parse_args()
@@ -111,6 +112,9 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        # NVML is initialised HERE, on the caller's thread and before any timed region: nvmlInit takes driver locks that
+        # kernel launches also need (an init inside the timed loop showed up as a one-off 15-75 ms stall of the launch loop)
+        self.nv = self._nvml_handle()
 
     def _nvml_handle(self):
         """NVML in-process (no fork: spawning nvidia-smi from a process with a CUDA context can stall every thread for
@@ -128,7 +132,7 @@ class ClockSampler(threading.Thread):
             return None
 
     def run(self):
-        nv = self._nvml_handle()
+        nv = self.nv
         while nv is not None and not self.stop_flag:
             try:
                 pynvml, h = nv
@@ -140,7 +144,7 @@ class ClockSampler(threading.Thread):
             except Exception:
                 nv = None
                 break
-            time.sleep(0.02)
+            time.sleep(0.025)
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -159,7 +163,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "sm_mhz_min": sm[0]}
 
 
 # --------------------------------------------------------------------------- helpers
@@ -249,12 +253,22 @@ def run_ours(a):
     T = 1 + N_SAMPLES // 160
     Tp = pipe.padded_frames(T)
 
+    # One CUDA graph per pool slice (AnonymizerPipeline.capture): a step is then ONE host call replaying the library's
+    # whole launch sequence, so host-side hiccups (a descheduled launch thread showed up as single 20-90 ms steps on a
+    # fresh box) cannot starve the GPU between kernels.  --no-graphs launches the ~29 kernels per step directly.
+    graphs = None
+    if not a.no_graphs:
+        graphs = [pipe.capture(dev_pool[k * B:(k + 1) * B], pool_noise=noise) for k in range(n_batches)]
+
     def step_device(i):
         k = i % n_batches
+        if graphs is not None:
+            return graphs[k].replay()
         return pipe(dev_pool[k * B:(k + 1) * B], pool_noise=noise)
 
     # clock ramp: a fresh box idles at low clocks and the first tens of milliseconds of work run slow; run untimed
     # steps for a fixed wall-clock budget before the W warm-up steps so that neither arm is timed during the ramp
+    sampler = ClockSampler(local)        # (initialises NVML now, outside every timed region)
     t_ramp = time.perf_counter()
     i = 0
     while time.perf_counter() - t_ramp < a.ramp_seconds:
@@ -262,24 +276,34 @@ def run_ours(a):
             step_device(i)
             i += 1
         torch.cuda.synchronize()
+    sampler.start()                      # (thread start-up and its first NVML calls happen during the warm-up)
     launches0 = _lib.lib().spanon_launch_count()
     for i in range(a.warmup):
         step_device(i)
     torch.cuda.synchronize()
     launches_w = _lib.lib().spanon_launch_count()
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier(world)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    import gc
+    gc.collect()
+    gc.disable()    # a generation-2 collection inside the launch loop is a 20 ms host stall = one starved step
+    step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]   # diagnostics only: per-step spread
     e0.record()
+    t_host = time.perf_counter()
     for i in range(a.steps):
         out = step_device(a.warmup + i)
+        step_ev[i].record()
+    host_enqueue_ms = (time.perf_counter() - t_host) * 1e3 / a.steps     # host time to enqueue one step (no sync)
     e1.record()
     torch.cuda.synchronize()
     ms_total = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    per_step = sorted(a_.elapsed_time(b_) for a_, b_ in zip([e0] + step_ev[:-1], step_ev))
+    step_spread = {"min": per_step[0], "median": per_step[len(per_step) // 2], "max": per_step[-1]}
     barrier(world)
     gpu_launches = int(_lib.lib().spanon_launch_count() - launches_w)
+    if graphs is not None:     # replays do not pass through the library's launch counter: kernels per captured step x K
+        gpu_launches = sum(graphs[(a.warmup + i) % n_batches].launches for i in range(a.steps))
     ms_step = ms_total / a.steps
     value = world * B * UTT_SECONDS / (ms_step * 1e-3)
 
@@ -315,6 +339,7 @@ def run_ours(a):
     ms_sync = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev) / n_sync
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    gc.enable()
     e2e = {"value": world * B * UTT_SECONDS / (ms_e2e * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": B * N_SAMPLES * 4, "d2h_bytes_per_step": B * Tp * 80 * 4 + B * 8,
            "api": "spanon_pipe_submit/wait (pinned host buffers in/out, %d batches in flight over H2D|kernel|D2H streams)" % depth,
@@ -323,10 +348,14 @@ def run_ours(a):
                                   "value": world * B * UTT_SECONDS / (ms_sync * 1e-3)}}
 
     # ---- per-kernel event timing (consecutive CUDA events on the launch stream, 2 extra steps)
+    for i in range(8):          # put the host ahead of the GPU first, so that no interval contains host latency
+        k = (a.warmup + a.steps + i) % n_batches
+        pipe(dev_pool[k * B:(k + 1) * B], pool_noise=noise)
     _lib.profile_begin(dev)
     n_prof = 2
-    for i in range(n_prof):
-        step_device(a.warmup + a.steps + i)
+    for i in range(n_prof):     # direct launches: the library records its profile events at launch time
+        k = (a.warmup + a.steps + i) % n_batches
+        pipe(dev_pool[k * B:(k + 1) * B], pool_noise=noise)
     prof = _lib.profile_end()
     kern = {k: {"launches_per_step": n / n_prof, "ms_per_step": ms / n_prof} for k, (n, ms) in prof.items()}
     prof_ms = sum(v["ms_per_step"] for v in kern.values())
@@ -379,7 +408,8 @@ def run_ours(a):
     if rank == 0:
         line = {"metric": "audio-sec/sec anonymized (Fbank+%s fwd)" % ("ConvAE" if a.workload == "convae" else "FC-AE"),
                 "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms_step, "host_enqueue_ms_per_step": host_enqueue_ms, "step_ms_spread": step_spread,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": a.precision if a.workload == "convae" else "fp32", "data": "synthetic",
                 "config": workload_config(a, world),
                 "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roof,
@@ -439,7 +469,8 @@ def workload_config(a, world):
                         "%d utterances (1 h) per GPU" % (a.workload, B, n_batches * B),
             "batch_per_gpu": B, "pool_per_gpu": n_batches * B, "parallelism": "utterance-sharded x%d" % world,
             "l2": "inputs cycle through a %.0f MB pool (> 126 MB L2)" % (n_batches * B * N_SAMPLES * 4 / 1e6),
-            "weights": "random-init seed 8886", "norm": "global stats from the reference's normalizer.ckpt"}
+            "weights": "random-init seed 8886", "norm": "global stats from the reference's normalizer.ckpt",
+            "launch": "direct kernel launches" if getattr(a, "no_graphs", False) else "one CUDA graph replay per step (device arm)"}
 
 
 # --------------------------------------------------------------------------- reference arm

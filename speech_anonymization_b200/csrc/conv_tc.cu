@@ -44,7 +44,7 @@ constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32;
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
 constexpr int TC_MAX_STAGES = 16;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
-enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4 };
+enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8 };
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
 constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
@@ -117,6 +117,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
       for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), TC_EPI_WARPS); }
       mbar_init(BAR(B_W), 1);
+      const_cast<uint32_t*>(tmem_ptr_smem)[1] = 0u;          // tiles stored by the epilogue warps (XF_STATS)
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       // resident weights: one bulk async copy per tap slice
       mbar_expect_tx(BAR(B_W), L.w_bytes);
@@ -188,7 +189,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // padding of the already activated tensor) exist only in an utterance's first / last tile and are zeroed there.
     const int xw = warp - TC_EPI_WARPS;
     constexpr bool do_silu = (XF & 3) == XF_SILU, do_relu = (XF & 3) == XF_RELU, has_t2 = (XF & XF_T2) != 0;
-    constexpr bool ident = XF == XF_IDENT;
+    constexpr bool ident = (XF & 7) == XF_IDENT;
+    constexpr bool do_stats = (XF & XF_STATS) != 0;
     const bool has_t1 = p.t1_scale != nullptr;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
     const int s_fix = xw % n_stage_tile;                       // stage-in-tile of this warp (n_stage_tile is 2, 4 or 8)
@@ -208,6 +210,99 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
     }
     int b_const = -1;                                          // utterance whose t1 constants are in registers
+    // ---- fused InstanceNorm statistics of THIS layer's output (XF_STATS): the epilogue warps bump a shared-memory
+    // counter after storing a tile; TC_STATS_LAG tiles later the transform warps read the tile back (it is still in L1/L2), lanes = rows, and keep per-lane partial sums of their planes in registers until the utterance
+    // changes.  Warp w owns destination plane(s) w, w + 8 (or plane w % n_pl and every (8 / n_pl)-th row group).
+    constexpr int NCH_O = COUT_V / 8;
+    const int st_npl = p.out_fold == OUT_PAIR_FOLD ? 2 * NCH_O : p.out_fold == OUT_PHASE_UNFOLD ? NCH_O / 2 : NCH_O;
+    const int st_rpp = p.out_fold == OUT_PAIR_FOLD ? TC_M / 2 : p.out_fold == OUT_PHASE_UNFOLD ? 2 * TC_M : TC_M;
+    const int st_ppw = st_npl > TC_XF_WARPS ? st_npl / TC_XF_WARPS : 1;       // planes per warp (1 or 2)
+    const int st_wpp = st_npl < TC_XF_WARPS ? TC_XF_WARPS / st_npl : 1;       // warps per plane (1 or 2)
+    float st_s[2][8], st_q[2][8];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { st_s[i][j] = 0.f; st_q[i][j] = 0.f; }
+    int st_b = -1;                                             // utterance the partial sums belong to
+    volatile uint32_t* st_counter = reinterpret_cast<volatile uint32_t*>(bars + B_TPTR) + 1;
+    const bool st_two = st_ppw == 2;
+    const int st_gpp = st_rpp / 32 / st_wpp;                   // row groups (32 rows) per plane and warp: 2, 4 or 8
+    auto st_flush = [&]() {
+      if (st_b < 0) return;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        // slots 4..7 (st_*[1]) belong to the warp's second plane, or to the same plane when it has only one
+        if (i == 1 && !st_two) break;
+        const int pl = (xw % st_npl) + i * TC_XF_WARPS;
+        const int c0 = p.out_fold == OUT_PAIR_FOLD ? (pl % NCH_O) * 8 : pl * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float a = warp_sum(st_two ? st_s[i][j] : st_s[0][j] + st_s[1][j]);
+          const float q = warp_sum(st_two ? st_q[i][j] : st_q[0][j] + st_q[1][j]);
+          if (lane == j) {
+            double* dst = p.stats + ((int64_t)st_b * p.cout_mod + c0 + j) * 2;
+            atomicAdd(dst, (double)a);
+            atomicAdd(dst + 1, (double)q);
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { st_s[i][j] = 0.f; st_q[i][j] = 0.f; }
+    };
+    // Software-pipelined over tiles: st_issue() starts the (up to eight) 16-byte loads of a stored tile, st_consume() adds
+    // the previous tile's values -- the L2 round trip of one tile hides behind the operand work of the next.
+    uint4 st_v[8];
+    int st_pending_b = -1;                                     // utterance of the tile whose loads are in flight
+    auto st_consume = [&]() {
+      if (st_pending_b < 0) return;
+      if (st_pending_b != st_b) { st_flush(); st_b = st_pending_b; }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const __half2* hv = reinterpret_cast<const __half2*>(&st_v[u]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = __half22float2(hv[j]);
+          st_s[u >> 2][2 * j] += f.x; st_s[u >> 2][2 * j + 1] += f.y;
+          st_q[u >> 2][2 * j] = fmaf(f.x, f.x, st_q[u >> 2][2 * j]);
+          st_q[u >> 2][2 * j + 1] = fmaf(f.y, f.y, st_q[u >> 2][2 * j + 1]);
+        }
+      }
+      st_pending_b = -1;
+    };
+    auto st_issue = [&](int j_tile) {
+      const int t = t_begin + j_tile;
+      const int tb = t / tiles_per_utt, ttin = t - tb * tiles_per_utt;
+      __threadfence_block();                                   // (the caller saw the epilogue's counter reach this tile)
+      const int m0 = ttin * tile_step;
+      const int r0 = p.out_fold == OUT_PAIR_FOLD ? m0 >> 1 : p.out_fold == OUT_PHASE_UNFOLD ? 2 * m0 : m0;
+      const __half* ob = reinterpret_cast<const __half*>(p.out) + (int64_t)tb * p.out_bstride;
+      const int g_first = (xw / st_npl) % st_wpp;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = st_two ? (u >> 2) : 0, gi = st_two ? (u & 3) : u;
+        const int r = r0 + (g_first + gi * st_wpp) * 32 + lane;
+        st_v[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (gi < st_gpp && r < p.out_plane_rows) {
+          const int pl = (xw % st_npl) + i * TC_XF_WARPS;
+          const uint4* src = reinterpret_cast<const uint4*>(ob + (((int64_t)pl * p.out_plane_rows + r) << 3));
+          asm volatile("ld.relaxed.cta.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(st_v[u].x), "=r"(st_v[u].y), "=r"(st_v[u].z), "=r"(st_v[u].w) : "l"(src) : "memory");
+        }
+      }
+      st_pending_b = tb;
+    };
+    // opportunistic: reduce the next stored tile if the epilogue has published it, never wait for it (waiting would tie
+    // the operand pipeline's run-ahead to the epilogue); the remainder is drained after the last stage
+    int st_next = 0;
+    auto st_poll = [&]() {
+      if (st_next < n_my_tiles && *st_counter >= (uint32_t)(st_next + 1) * TC_EPI_WARPS) {
+        st_consume();
+        st_issue(st_next);
+        ++st_next;
+      }
+    };
     for (; k < n_my_tiles; k += kstep) {
       const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
@@ -223,7 +318,11 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
         b_const = b;
       }
-      mbar_wait(BAR(B_RAW + stage), ph);
+      if (do_stats) {
+        while (!mbar_try(BAR(B_RAW + stage), ph)) st_poll();
+      } else {
+        mbar_wait(BAR(B_RAW + stage), ph);
+      }
       const int it = k * n_stage_tile + s_fix;
       if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
       unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)lane * 16u;
@@ -269,6 +368,19 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
       tin += kstep;
       while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+      if (do_stats) {
+        for (int n = 0; n < kstep; ++n) st_poll();             // keep pace: one stored tile per tile of operand work
+      }
+    }
+    if (do_stats) {
+      while (st_next < n_my_tiles) {
+        while (*st_counter < (uint32_t)(st_next + 1) * TC_EPI_WARPS) __nanosleep(64);
+        st_consume();
+        st_issue(st_next);
+        ++st_next;
+      }
+      st_consume();
+      st_flush();
     }
   } else if (warp == TC_MMA_WARP) {
     // =========================== MMA ISSUER ===========================
@@ -408,6 +520,11 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           }
         }
       }
+      if constexpr ((XF & XF_STATS) != 0) {              // publish the stored tile to the transform warps' statistics pass
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) atomicAdd(const_cast<uint32_t*>(tmem_ptr_smem) + 1, 1u);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
@@ -492,7 +609,7 @@ bool tapgemm_tc_supported(const TapGemmParams& p) {
   }
   if (p.tap_step < 1 || p.tap_kmax[p.ntaps - 1] % TC_STAGE_CH != 0 || p.tap_nmax[0] % 8 != 0) return false;
   if (p.out_fold == OUT_PAIR_FOLD && (p.rows_out & 1)) return false;
-  if (p.stats || p.fin_counter) return false;               // statistics are a separate pass (instnorm_stats_kernel)
+  if (p.fin_counter) return false;                           // finalize is a separate launch (instnorm_finalize_kernel)
   if (p.out_mode != OUT_CHANNELS_LAST) return false;        // fp16 chunk-planar output only
   return true;
 }
@@ -501,13 +618,17 @@ int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (!tapgemm_tc_supported(p) || p.B < 1) return SPANON_ERR_UNSUPPORTED;
   // one instantiation per (columns, operand transform) the layer lists use
   const int act = p.silu == 1 ? XF_SILU : p.silu == 2 ? XF_RELU : XF_IDENT;
-  const int xf = act | (p.t2_scale ? XF_T2 : 0);
+  const int xf = act | (p.t2_scale ? XF_T2 : 0) | (p.stats ? XF_STATS : 0);
   if (act == XF_IDENT && (p.t1_scale || p.t2_scale)) return SPANON_ERR_UNSUPPORTED;
   if (p.cout_v == 16 && xf == XF_SILU) return launch_tc<16, XF_SILU>(p, n_sm, st);
   if (p.cout_v == 64 && xf == XF_IDENT) return launch_tc<64, XF_IDENT>(p, n_sm, st);
   if (p.cout_v == 64 && xf == XF_SILU) return launch_tc<64, XF_SILU>(p, n_sm, st);
   if (p.cout_v == 128 && xf == XF_IDENT) return launch_tc<128, XF_IDENT>(p, n_sm, st);
   if (p.cout_v == 128 && xf == XF_SILU) return launch_tc<128, XF_SILU>(p, n_sm, st);
+  if (p.cout_v == 64 && xf == (XF_IDENT | XF_STATS)) return launch_tc<64, XF_IDENT | XF_STATS>(p, n_sm, st);
+  if (p.cout_v == 64 && xf == (XF_SILU | XF_STATS)) return launch_tc<64, XF_SILU | XF_STATS>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == (XF_IDENT | XF_STATS)) return launch_tc<128, XF_IDENT | XF_STATS>(p, n_sm, st);
+  if (p.cout_v == 128 && xf == (XF_SILU | XF_STATS)) return launch_tc<128, XF_SILU | XF_STATS>(p, n_sm, st);
   if (p.cout_v == 128 && xf == (XF_SILU | XF_T2)) return launch_tc<128, XF_SILU | XF_T2>(p, n_sm, st);
   if (p.cout_v == 128 && xf == (XF_RELU | XF_T2)) return launch_tc<128, XF_RELU | XF_T2>(p, n_sm, st);
   return SPANON_ERR_UNSUPPORTED;

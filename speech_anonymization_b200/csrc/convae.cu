@@ -676,7 +676,15 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.in_planar = c.tc ? 1 : 0;
   p.B = nb;
   p.tag = kLayerTag[id];
-  const bool split_stats = on_tc && io.out_stats >= 0;
+  // InstanceNorm statistics of a tcgen05 layer's output: fused into the producing kernel (its transform warps reduce the
+  // stored tiles while they are still in cache) or a separate bandwidth-bound pass over the plane (instnorm_stats_kernel).
+  // $SPANON_FUSED_STATS: 0 = always separate (default), 1 = fused where the transform warps are idle (no activation on
+  // load), 2 = fused everywhere.  Measured on B200 (tools/ab_env.sh, 60 x 10 s): reading the stored tiles back costs
+  // +40..+100 us per producing launch (the launch is already moving ~570 MB through L2 for HBM; the read-back competes
+  // for the same L2 slices) against 66 us for the separate HBM-rate pass, so the fused form is kept as an option only.
+  static const int fused_mode = getenv("SPANON_FUSED_STATS") ? atoi(getenv("SPANON_FUSED_STATS")) : 0;
+  const bool fuse = on_tc && io.out_stats >= 0 && (fused_mode >= 2 || (fused_mode == 1 && p.silu == 0));
+  const bool split_stats = on_tc && io.out_stats >= 0 && !fuse;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
@@ -687,6 +695,12 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
                                                       c.ws.stats[io.out_stats]);
       SPANON_TRY(check_launch("instnorm_stats_kernel"));
       // (a separate tiny launch instead of a last-block-done counter: blocks then end without waiting on an atomic)
+      instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * s.cout, 128), 128, 0, c.st>>>(
+          c.ws.stats[io.out_stats], io.fin_gamma, io.fin_beta, nb, s.cout, io.fin_count, c.ws.in_scale[io.out_stats],
+          c.ws.in_shift[io.out_stats]);
+      return check_launch("instnorm_finalize_kernel");
+    }
+    if (fuse) {
       instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * s.cout, 128), 128, 0, c.st>>>(
           c.ws.stats[io.out_stats], io.fin_gamma, io.fin_beta, nb, s.cout, io.fin_count, c.ws.in_scale[io.out_stats],
           c.ws.in_shift[io.out_stats]);

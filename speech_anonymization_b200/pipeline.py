@@ -61,6 +61,12 @@ class AnonymizerPipeline(torch.nn.Module):
             feats = pad_time(feats)
         return self.model(feats, pool_noise=pool_noise)
 
+    def capture(self, wavs, wav_lens=None, pool_noise=None):
+        """Captures one forward pass on `wavs` (a device tensor that stays alive and may be overwritten in place) into a
+        CUDA graph: GraphedStep.replay() re-runs the whole launch sequence (Fbank, the anonymizer's ~28 kernels and its
+        memsets) with ONE host call, so a busy or descheduled host thread cannot starve the GPU between kernels."""
+        return GraphedStep(self, wavs, wav_lens, pool_noise)
+
     # -- host-buffer path through the single C entry point (bench.py's e2e leg)
     def host_workspace(self, B, n_samples, device):
         opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
@@ -95,6 +101,31 @@ class AnonymizerPipeline(torch.nn.Module):
     def stream_pipe(self, max_batch, n_samples, device, depth=2):
         """A StreamPipe (spanon_pipe_*) bound to this pipeline's frozen features, statistics and weights."""
         return StreamPipe(self, max_batch, n_samples, device, depth)
+
+
+class GraphedStep:
+    """One captured forward pass of an AnonymizerPipeline (torch.cuda.CUDAGraph around the C-ABI launches; the library
+    only enqueues on the current stream and never synchronises, so its launch sequence is capturable as is).
+    `recon`, `logp` are the static output tensors every replay() overwrites."""
+
+    def __init__(self, pipeline, wavs, wav_lens=None, pool_noise=None, warmup=2):
+        self.wavs = wavs
+        side = torch.cuda.Stream(device=wavs.device)
+        side.wait_stream(torch.cuda.current_stream(wavs.device))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):      # first calls pack weights / set kernel attributes: keep them out of the graph
+                pipeline(wavs, wav_lens, pool_noise=pool_noise)
+        torch.cuda.current_stream(wavs.device).wait_stream(side)
+        torch.cuda.synchronize(wavs.device)
+        self.launches_before = _lib.lib().spanon_launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.recon, self.logp = pipeline(wavs, wav_lens, pool_noise=pool_noise)
+        self.launches = int(_lib.lib().spanon_launch_count() - self.launches_before)   # kernels per replay
+
+    def replay(self):
+        self.graph.replay()
+        return self.recon, self.logp
 
 
 class StreamPipe:

@@ -395,6 +395,28 @@ def test_pipeline_fused_equals_modular_equals_oracle(golden, kind):
     assert rel_max(r16s.numpy(), r32.numpy()) < 1e-6
 
 
+def test_graphed_step_equals_direct_launches(golden):
+    """AnonymizerPipeline.capture: replaying the captured launch sequence gives the direct call's result, also after the
+    input buffer has been overwritten in place (fp16 mode: the path bench.py times)."""
+    m, _ = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES, precision="fp16")
+    pipe = _pipeline(m, golden)
+    wav, _ = recipe.make_wav(61, 3, 16000)
+    wav2, _ = recipe.make_wav(62, 3, 16000)
+    noise = cu(recipe.make_noise(61, 3, 128))
+    buf = cu(wav).clone()
+    rec_d, logp_d = pipe(buf, pool_noise=noise)
+    rec_d2, logp_d2 = pipe(cu(wav2), pool_noise=noise)
+    g = pipe.capture(buf, pool_noise=noise)
+    assert g.launches >= 25
+    r, l = g.replay()
+    torch.cuda.synchronize()
+    assert rel_max(r.cpu().numpy(), rec_d.cpu().numpy()) < 1e-6 and float((l - logp_d).abs().max()) < 1e-6
+    buf.copy_(cu(wav2))
+    r, l = g.replay()
+    torch.cuda.synchronize()
+    assert rel_max(r.cpu().numpy(), rec_d2.cpu().numpy()) < 1e-6 and float((l - logp_d2).abs().max()) < 1e-6
+
+
 def test_convae_sees_weight_updates():
     """The module keeps its workspace (with the packed weights) between calls; an in-place parameter update must
     invalidate that cache (key = storage pointer + version counter of every parameter and buffer)."""
