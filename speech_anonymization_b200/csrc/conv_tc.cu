@@ -5,21 +5,28 @@
 // layout (8 rows x 16 B core matrices, SBO = 128 B), so a (128 + halo)-row slab of one chunk is ONE contiguous
 // cp.async.bulk copy into shared memory, and a conv tap is the same slab read at start_address + 16 * shift.
 //
-// One persistent CTA per SM walks (utterance, 128-row tile) pairs of one layer:
+// One persistent CTA per SM (480 threads) walks a CONTIGUOUS run of (utterance, 128-row tile) pairs of one layer; the
+// operand ring is cut into 16-channel stages (two 8-channel chunks x slab rows = one K=16 MMA step per tap):
 //
-//   warp 13      LOADER      one thread: per stage (32 input channels = 4 chunks) four bulk copies global -> smem,
-//                            completion on the stage's `raw` mbarrier (expect_tx).  Runs as far ahead as the ring allows.
-//   warps 4..11  TRANSFORM   in place in shared memory: InstanceNorm affine (fp32) -> SiLU (tanh.approx.f16x2) ->
-//                            folded BatchNorm of the PRODUCER layer, zero rows outside the utterance (= the conv's zero
-//                            padding of the already activated tensor); fence.proxy.async, then the `full` mbarrier.
-//   warp 12      MMA ISSUER  one thread: per stage and tap two tcgen05.mma (M=128, N=cout_v, K=16, kind::f16, fp32
-//                            accumulate in TMEM).  All of the layer's packed weights are resident in shared memory.
+//   warps 13,14  LOADERS     loader l owns the stages it == l (mod 2): per stage two bulk copies global -> smem issued by
+//                            one elected lane of the converged warp (operands stay in uniform registers), completion on the
+//                            stage's `raw` mbarrier (expect_tx).  They run as far ahead as the ring (8 or 16 stages) allows.
+//   warps 4..11  TRANSFORM   warp w owns the stages it == w (mod 8), in place in shared memory, all packed fp16:
+//                            InstanceNorm affine (HFMA2) -> SiLU (tanh.approx.f16x2) | ReLU -> folded BatchNorm of the
+//                            PRODUCER layer; rows outside the utterance (= the conv's zero padding of the already activated
+//                            tensor) are zeroed in an utterance's first / last tile; fence.proxy.async, `full` mbarrier.
+//                            The per-utterance constants are reloaded only when the utterance changes.  One kernel
+//                            instantiation per transform mode (XF_*): the roles share a small instruction cache.
+//   warp 12      MMA ISSUER  converged warp, elect.sync-predicated tcgen05.mma (M=128, N=cout_v, K=16, kind::f16, fp32
+//                            accumulate in TMEM), one per stage and tap.  All of the layer's packed weights are resident in
+//                            shared memory.  (An M=128 N=128 K=16 UMMA reads 8 KB of operands from shared memory = 64 cycles
+//                            at 128 B/clk, exactly its math time; N=64 takes 48: tools/ubench/umma_rate.cu.)
 //   warps 0..3   EPILOGUE    tcgen05.ld of the accumulator (double-buffered in TMEM) -> + bias, ReLU, folded BN -> fp16 ->
 //                            16-byte stores straight into the CONSUMER's chunk-planar view (direct, pair-folded for a
 //                            stride-2 consumer, phase-unfolded after a transposed conv): a warp's 32 rows of one chunk are
-//                            512 contiguous bytes.  InstanceNorm statistics (sum, sum of squares per channel) come from a
-//                            butterfly transpose-reduce over the warp's rows (31 shuffles per 32 columns); the last CTA to
-//                            finish turns them into the consumer's scale/shift.
+//                            512 contiguous bytes.
+// InstanceNorm statistics of the output are a separate HBM-rate pass (instnorm_stats_kernel) by default; XF_STATS fuses
+// them into this kernel (the transform warps read the stored tiles back), which measured slower (see convae.cu run_layer).
 //
 // 16-bit operands are fp16, not bf16: tools/precision_study.py shows bf16 operands + bf16 planes cannot hold the 1e-2
 // parity bar on this network (1.0-1.3e-2); fp16 gives 1.5e-3 at the same tensor-core rate.

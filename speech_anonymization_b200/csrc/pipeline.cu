@@ -5,6 +5,7 @@
 // folded into the anonymizer's first load so the features make one HBM round trip.
 #include "common.cuh"
 #include <algorithm>
+#include <stdlib.h>
 
 using namespace spanon;
 
@@ -39,7 +40,26 @@ extern "C" size_t spanon_anonymize_workspace_bytes(int kind, int64_t B, int64_t 
 }
 
 namespace {
-struct Lanes { cudaStream_t h2d, compute, d2h; cudaEvent_t ev_h2d, ev_compute; };   // ev_* NULL when all three are one stream
+struct Lanes {   // ev_* NULL when all three are one stream; graph != NULL: replay instead of launching the kernels
+  cudaStream_t h2d, compute, d2h; cudaEvent_t ev_h2d, ev_compute; cudaGraphExec_t graph = nullptr;
+};
+
+// The kernels of one batch (Fbank -> anonymizer) on `st`; everything it touches is device memory of the slot.
+int enqueue_compute(int kind, int fmt, int64_t B, int64_t n_samples, const SpanonFbankCfg* fb, const float* norm_mean,
+                    const float* norm_std, const void* weights, const float* pool_noise, const SpanonConvAEOpts* opts,
+                    bool want_logp, const Carve& c, cudaStream_t st) {
+  const int64_t T = 1 + n_samples / fb->hop_length, Tp = padded_T(kind, T), F = fb->n_mels;
+  if (fmt == 2)
+    SPANON_TRY(spanon_fbank_i16(reinterpret_cast<const int16_t*>(c.pcm), B, n_samples, n_samples, c.fb, c.utt_max, fb, st));
+  else
+    SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, st));
+  float* logp_dev = want_logp ? c.logp : nullptr;
+  if (kind == 0)
+    return spanon_convae_fwd(c.fb, (const SpanonConvAEWeights*)weights, pool_noise, norm_mean, norm_std, c.utt_max,
+                             fb->top_db, T, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, Tp, F, opts, st);
+  return spanon_fcae_fwd(c.fb, (const SpanonFcaeWeights*)weights, pool_noise, norm_mean, norm_std, c.utt_max, fb->top_db,
+                         c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, T, st);
+}
 
 // Enqueues one batch: H2D on lanes.h2d, kernels on lanes.compute, D2H on lanes.d2h (ordered by the two events).
 // fmt: bytes per PCM sample on the wire, 4 = fp32, 2 = int16 (half the H2D bytes; converted on load by the Fbank kernel)
@@ -52,19 +72,11 @@ int enqueue_batch(int kind, const void* pcm_host, int fmt, int64_t B, int64_t n_
     SPANON_CUDA_TRY(cudaEventRecord(ln.ev_h2d, ln.h2d));
     SPANON_CUDA_TRY(cudaStreamWaitEvent(ln.compute, ln.ev_h2d, 0));
   }
-  if (fmt == 2)
-    SPANON_TRY(spanon_fbank_i16(reinterpret_cast<const int16_t*>(c.pcm), B, n_samples, n_samples, c.fb, c.utt_max, fb,
-                                ln.compute));
-  else
-    SPANON_TRY(spanon_fbank_f32(c.pcm, B, n_samples, n_samples, c.fb, c.utt_max, fb, ln.compute));
-  float* logp_dev = logp_host ? c.logp : nullptr;
-  if (kind == 0) {
-    SPANON_TRY(spanon_convae_fwd(c.fb, (const SpanonConvAEWeights*)weights, pool_noise, norm_mean, norm_std,
-                                 c.utt_max, fb->top_db, T, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, Tp, F, opts,
-                                 ln.compute));
+  if (ln.graph) {          // the kernels of this batch were captured on an earlier use of the slot: one launch
+    SPANON_CUDA_TRY(cudaGraphLaunch(ln.graph, ln.compute));
   } else {
-    SPANON_TRY(spanon_fcae_fwd(c.fb, (const SpanonFcaeWeights*)weights, pool_noise, norm_mean, norm_std, c.utt_max,
-                               fb->top_db, c.recon, logp_dev, c.anon_ws, c.anon_bytes, B, T, ln.compute));
+    SPANON_TRY(enqueue_compute(kind, fmt, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, logp_host != nullptr,
+                               c, ln.compute));
   }
   if (ln.ev_compute) {
     SPANON_CUDA_TRY(cudaEventRecord(ln.ev_compute, ln.compute));
@@ -90,7 +102,7 @@ static int anonymize_host(int kind, const void* pcm_host, int fmt, int64_t B, in
   char* base = reinterpret_cast<char*>(up256(reinterpret_cast<uintptr_t>(dev_workspace)));
   Carve c = carve(base, kind, B, n_samples, fb->hop_length, fb->n_mels, opts);
   cudaStream_t st = as_stream(stream);
-  const Lanes ln{st, st, st, nullptr, nullptr};
+  const Lanes ln{st, st, st, nullptr, nullptr, nullptr};
   SPANON_TRY(enqueue_batch(kind, pcm_host, fmt, B, n_samples, fb, norm_mean, norm_std, weights, pool_noise, opts, recon_host,
                            logp_host, c, ln));
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
@@ -127,7 +139,9 @@ struct SpanonPipe {
   const float* norm_mean = nullptr; const float* norm_std = nullptr;
   cudaStream_t h2d = nullptr, compute = nullptr, d2h = nullptr;
   size_t ws_bytes = 0;
-  struct Slot { void* ws = nullptr; cudaEvent_t ev_h2d = nullptr, ev_compute = nullptr, ev_done = nullptr; bool busy = false; int64_t prepared_B = -1; };
+  struct Slot { void* ws = nullptr; cudaEvent_t ev_h2d = nullptr, ev_compute = nullptr, ev_done = nullptr; bool busy = false; int64_t prepared_B = -1;
+                // CUDA graph of the slot's kernel sequence, valid for exactly this (batch size, sample format, noise, logp)
+                cudaGraphExec_t graph = nullptr; int64_t g_B = -1; int g_fmt = 0; const float* g_noise = nullptr; bool g_logp = false; };
   Slot* slots = nullptr;
   int64_t submitted = 0, retired = 0;
 };
@@ -141,6 +155,7 @@ extern "C" void spanon_pipe_destroy(SpanonPipe* p) {
       if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
       if (s.ev_compute) cudaEventDestroy(s.ev_compute);
       if (s.ev_done) cudaEventDestroy(s.ev_done);
+      if (s.graph) cudaGraphExecDestroy(s.graph);
       if (s.ws) cudaFree(s.ws);
     }
     delete[] p->slots;
@@ -211,8 +226,32 @@ static int pipe_submit(SpanonPipe* p, const void* pcm_host, int fmt, int64_t B, 
   SpanonConvAEOpts o = p->opts;
   o.weights_prepared = (p->kind == 0 && s.prepared_B == B) ? 1 : 0;   // this slot already holds the packed weights
   Carve c = carve(base, p->kind, B, p->n_samples, p->fb.hop_length, p->fb.n_mels, &o);
-  const Lanes ln{p->h2d, p->compute, p->d2h, s.ev_h2d, s.ev_compute};
   const void* w = p->kind == 0 ? (const void*)&p->w.conv : (const void*)&p->w.fc;
+  // From the second use of a slot at a given batch size on (packed weights in place, every attribute set) the slot's
+  // ~29 launches + memsets are captured once into a CUDA graph and replayed with one call: no inter-kernel launch gaps and
+  // a submit costs the host three enqueues.  $SPANON_PIPE_GRAPHS=0 turns this off.
+  static const bool use_graphs = !(getenv("SPANON_PIPE_GRAPHS") && getenv("SPANON_PIPE_GRAPHS")[0] == '0') && !g_debug_sync;
+  const bool want_logp = logp_host != nullptr;
+  if (s.graph && !(s.g_B == B && s.g_fmt == fmt && s.g_noise == pool_noise && s.g_logp == want_logp && s.prepared_B == B)) {
+    cudaGraphExecDestroy(s.graph);
+    s.graph = nullptr;
+  }
+  if (!s.graph && use_graphs && s.prepared_B == B && !g_profile_on.load()) {
+    SpanonConvAEOpts og = p->opts;
+    og.weights_prepared = 1;
+    cudaGraph_t g = nullptr;
+    SPANON_CUDA_TRY(cudaStreamBeginCapture(p->compute, cudaStreamCaptureModeThreadLocal));
+    const int rc = enqueue_compute(p->kind, fmt, B, p->n_samples, &p->fb, p->norm_mean, p->norm_std, w, pool_noise, &og,
+                                   want_logp, c, p->compute);
+    const cudaError_t ce = cudaStreamEndCapture(p->compute, &g);
+    if (rc != SPANON_OK) { if (g) cudaGraphDestroy(g); return rc; }
+    SPANON_CUDA_TRY(ce);
+    const cudaError_t ci = cudaGraphInstantiate(&s.graph, g, 0);
+    cudaGraphDestroy(g);
+    SPANON_CUDA_TRY(ci);
+    s.g_B = B; s.g_fmt = fmt; s.g_noise = pool_noise; s.g_logp = want_logp;
+  }
+  const Lanes ln{p->h2d, p->compute, p->d2h, s.ev_h2d, s.ev_compute, s.graph};
   SPANON_TRY(enqueue_batch(p->kind, pcm_host, fmt, B, p->n_samples, &p->fb, p->norm_mean, p->norm_std, w, pool_noise, &o,
                            recon_host, logp_host, c, ln));
   SPANON_CUDA_TRY(cudaEventRecord(s.ev_done, p->d2h));
@@ -236,6 +275,9 @@ extern "C" int spanon_pipe_weights_changed(SpanonPipe* p, const void* weights) {
   if (!p) return SPANON_ERR_NULL_POINTER;
   SPANON_TRY(spanon_pipe_drain(p));
   if (weights) { if (p->kind == 0) p->w.conv = *(const SpanonConvAEWeights*)weights; else p->w.fc = *(const SpanonFcaeWeights*)weights; }
-  for (int i = 0; i < p->depth; ++i) p->slots[i].prepared_B = -1;
+  for (int i = 0; i < p->depth; ++i) {
+    p->slots[i].prepared_B = -1;
+    if (p->slots[i].graph) { cudaGraphExecDestroy(p->slots[i].graph); p->slots[i].graph = nullptr; }
+  }
   return SPANON_OK;
 }
