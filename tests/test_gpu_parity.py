@@ -283,6 +283,24 @@ def test_xvector_classifier_vs_golden_and_oracle(golden2):
     assert logits.shape == (2, 2) and bool(torch.isfinite(logits).all())
 
 
+def test_convae_config3_batch_is_utterance_independent(golden):
+    """BASELINE config 3 size (batch 256 x 10 s through Fbank -> ConvAE, fp16): utterances are independent on the
+    inference path, so every utterance's result must not depend on its batch, chunk (60/60/60/60/16) or position."""
+    m, _ = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES, precision="fp16")
+    pipe = _pipeline(m, golden)
+    B = 256
+    g = torch.Generator().manual_seed(7)
+    wav = (0.1 * torch.randn(B, 160000, generator=g)).to(DEV)
+    noise = cu(recipe.make_noise(7, B, 128))
+    rec, logp = pipe(wav, pool_noise=noise)
+    assert rec.shape == (B, 1008, 80) and logp.shape == (B, 2) and bool(torch.isfinite(rec).all())
+    for i in (0, 59, 60, 255):
+        r1, l1 = pipe(wav[i:i + 1].contiguous(), pool_noise=noise[i:i + 1].contiguous())
+        assert rel_max(rec[i:i + 1].cpu().numpy(), r1.cpu().numpy()) < 1e-5     # (fp64 atomics: summation order)
+        assert float((logp[i:i + 1] - l1).abs().max()) < 1e-4
+    assert float(rec[:, 1001:].abs().max()) < 50.0 and float((rec[0] - rec[1]).abs().max()) > 0.0
+
+
 def test_convae_error_behaviour():
     m, _ = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES)
     with pytest.raises(RuntimeError):           # the reference's reshape fails when T*F % 4 != 0
