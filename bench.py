@@ -176,6 +176,8 @@ def convae_layer_flops(L=80640):
            "tapgemm:tdnn6": (L // 4 - 14) * 128 * 3 * 128,
            "tapgemm:dec0": (L // 4) * 128 * 5 * 128, "tapgemm:dec1": (L // 4) * 128 * 5 * 64,
            "tapgemm:dec4": (L // 2) * 64 * 5 * 64, "tapgemm:dec5": (L // 2) * 64 * 5 * 32,
+           # decoder.4 o decoder.5 run as one composed layer: counted at the ALGORITHMIC flops of the two reference layers
+           "tapgemm:dec45": (L // 2) * 64 * 5 * 64 + (L // 2) * 64 * 5 * 32,
            "tapgemm:dec8": L * 32 * 15}
     return {k: 2.0 * v for k, v in mac.items()}
 

@@ -143,7 +143,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     float* ec = reinterpret_cast<float*>(smem + L.epi);
     for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_THREADS) {
       const int cm = c % p.cout_mod;
-      ec[c] = p.bias ? p.bias[cm] : 0.f;
+      ec[c] = p.bias ? p.bias[p.bias_v ? c : cm] : 0.f;
       ec[COUT_V + c] = p.e_scale ? p.e_scale[cm] : 1.f;
       ec[2 * COUT_V + c] = p.e_shift ? p.e_shift[cm] : 0.f;
     }

@@ -24,7 +24,7 @@ int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 namespace {
 
 // ------------------------------------------------------------------ weight packing
-enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2, PACK_TOEPLITZ = 3 };
+enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2, PACK_TOEPLITZ = 3, PACK_COMPOSED = 4 };
 
 // Source value of packed element (tap, civ, cov); cin/cout/k are the REAL layer sizes.
 __device__ __forceinline__ float packed_src(const float* __restrict__ w, int mode, int cin, int cout, int k,
@@ -70,6 +70,116 @@ __global__ void pack_umma_kernel(const float* __restrict__ w, __half* __restrict
     const int kc = (int)((i / (8 * (int64_t)cout_v)) % (cin_v / 8));
     const int tap = (int)(i / ((int64_t)cout_v * cin_v));
     dst[i] = __float2half_rn(packed_src(w, mode, cin, cout, k, tap, kc * 8 + e, cov));
+  }
+}
+
+// ------------------------------------------------------------------ decoder.4 o decoder.5 as ONE transposed convolution
+// models/ConvAutoEncoder.py:166-167: Conv1d(C0->C1,k5,p2) is followed directly (no norm, no activation) by
+// ConvTranspose1d(C1->C2,k5,s2,p2,op1), so their composition is linear:
+//   h[i]      = b4 + sum_{s=-2..2} x[i+s] W4[:, :, s+2]
+//   y[2m+ph]  = b5 + sum_d h[m+d] W5[:, :, 2 - 2d + ph]          (d = -1,0,1 even phase; d = 0,1 odd phase)
+//             = bc[ph] + sum_{u=-3..3} x[m+u] Wc[ph][u],   Wc[ph][u] = sum_{d, s=u-d} W4[s+2]^T W5[2-2d+ph]
+// i.e. a 7-tap phase-view tap GEMM (tap u = -3 feeds only the even phase): one launch and one HBM round trip instead of
+// two, 6.5 instead of 7.5 tap-slices of MMAs.  The composition assumes h exists at i = -1 and i = L2 (computed from the
+// zero-padded x); the reference has no such rows, so dec45_edge_kernel subtracts their contribution from the three
+// affected output rows of each utterance (y[0], y[2*L2-2], y[2*L2-1]).
+// Composed weights in the fp16 UMMA layout [7][C0/8][2*C2][8]; w4 = Conv1d weight [C1][C0][5], w5 = ConvT weight [C1][C2][5].
+__global__ void compose_dec45_kernel(const float* __restrict__ w4, const float* __restrict__ w5, __half* __restrict__ dst,
+                                     int C0, int C1, int C2) {
+  const int cout_v = 2 * C2;
+  const int64_t n = (int64_t)7 * C0 * cout_v;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i % 8);
+    const int cov = (int)((i / 8) % cout_v);
+    const int kc = (int)((i / (8 * (int64_t)cout_v)) % (C0 / 8));
+    const int u = (int)(i / ((int64_t)cout_v * C0)) - 3;
+    const int c0 = kc * 8 + e, ph = cov / C2, c2 = cov - ph * C2;
+    float acc = 0.f;
+    for (int d = -1; d <= 1; ++d) {
+      const int sft = u - d, t = 2 - 2 * d + ph;
+      if (sft < -2 || sft > 2 || t > 4) continue;
+      for (int c1 = 0; c1 < C1; ++c1)
+        acc = fmaf(__ldg(w4 + ((int64_t)c1 * C0 + c0) * 5 + sft + 2), __ldg(w5 + ((int64_t)c1 * C2 + c2) * 5 + t), acc);
+    }
+    dst[i] = __float2half_rn(acc);
+  }
+}
+
+// bc[ph*C2 + c2] = b5[c2] + sum_c1 b4[c1] * sum_{t = ph (mod 2)} W5[c1][c2][t]
+__global__ void compose_dec45_bias_kernel(const float* __restrict__ b4, const float* __restrict__ w5,
+                                          const float* __restrict__ b5, float* __restrict__ bc, int C1, int C2) {
+  const int cov = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cov >= 2 * C2) return;
+  const int ph = cov / C2, c2 = cov - ph * C2;
+  float acc = b5[c2];
+  for (int c1 = 0; c1 < C1; ++c1) {
+    float ws = 0.f;
+    for (int t = ph; t < 5; t += 2) ws += w5[((int64_t)c1 * C2 + c2) * 5 + t];
+    acc = fmaf(b4[c1], ws, acc);
+  }
+  bc[cov] = acc;
+}
+
+// The correction is linear in the four activated input rows x[0], x[1], x[L2-2], x[L2-1]; its matrices are composed
+// once with the weights: E[j][r][c0][c2] (j = y[0] | y[2*L2-2] | y[2*L2-1]; r = nearer | farther input row) followed by
+// the constants Ec[j][c2] = sum_c1 b4[c1] W5[c1][c2][tap_j].
+constexpr int EDGE45_FLOATS = 3 * 2 * 64 * 32 + 3 * 32;
+__global__ void compose_dec45_edge_kernel(const float* __restrict__ w4, const float* __restrict__ b4,
+                                          const float* __restrict__ w5, float* __restrict__ E, int C0, int C1, int C2) {
+  const int n_mat = 3 * 2 * C0 * C2;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_mat + 3 * C2) return;
+  const int tap5[3] = {4, 0, 1};
+  float acc = 0.f;
+  if (i < n_mat) {
+    const int c2 = i % C2, c0 = (i / C2) % C0, r = (i / (C2 * C0)) % 2, j = i / (2 * C2 * C0);
+    // h[-1] = b4 + x[0] W4[k=3] + x[1] W4[k=4];   h[L2] = b4 + x[L2-1] W4[k=1] + x[L2-2] W4[k=0]
+    const int k4 = j == 0 ? 3 + r : 1 - r;
+    for (int c1 = 0; c1 < C1; ++c1)
+      acc = fmaf(w4[((int64_t)c1 * C0 + c0) * 5 + k4], w5[((int64_t)c1 * C2 + c2) * 5 + tap5[j]], acc);
+  } else {
+    const int c2 = (i - n_mat) % C2, j = (i - n_mat) / C2;
+    for (int c1 = 0; c1 < C1; ++c1) acc = fmaf(b4[c1], w5[((int64_t)c1 * C2 + c2) * 5 + tap5[j]], acc);
+  }
+  E[i] = acc;
+}
+
+// One block per utterance, 384 threads = 3 output rows x 4 slices of c0 x 32 channels.  x: raw planes [utt][8][L2][8]
+// fp16 of the composed layer's input, scale/shift: its InstanceNorm affine [utt][64]; y: planes [utt][4][2*L2][8] fp16.
+__global__ void __launch_bounds__(384)
+dec45_edge_kernel(const __half* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
+                  const float* __restrict__ E, __half* __restrict__ y, int L2) {
+  constexpr int C0 = 64, C2 = 32;
+  __shared__ float xs[4][C0], part[3][4][C2];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  if (tid < 4 * C0) {   // rows 0, 1, L2-2, L2-1 of the activated input
+    const int r = tid / C0, c = tid % C0;
+    const int row = r < 2 ? r : L2 - 4 + r;
+    const float v = __half2float(x[(((int64_t)b * (C0 / 8) + c / 8) * L2 + row) * 8 + (c & 7)]);
+    xs[r][c] = silu_fast(fmaf(v, scale[(int64_t)b * C0 + c], shift[(int64_t)b * C0 + c]));
+  }
+  __syncthreads();
+  {
+    const int c2 = tid % C2, sl = (tid / C2) % 4, j = tid / (4 * C2);
+    const float* near = xs[j == 0 ? 0 : 3];
+    const float* far = xs[j == 0 ? 1 : 2];
+    const float* e0 = E + ((int64_t)(j * 2 + 0) * C0) * C2 + c2;
+    const float* e1 = E + ((int64_t)(j * 2 + 1) * C0) * C2 + c2;
+    float acc = sl == 0 ? E[3 * 2 * C0 * C2 + j * C2 + c2] : 0.f;
+#pragma unroll
+    for (int c0 = sl * 16; c0 < sl * 16 + 16; ++c0) {
+      acc = fmaf(near[c0], e0[c0 * C2], acc);
+      acc = fmaf(far[c0], e1[c0 * C2], acc);
+    }
+    part[j][sl][c2] = acc;
+  }
+  __syncthreads();
+  if (tid < 3 * C2) {
+    const int c2 = tid % C2, j = tid / C2;
+    const float corr = part[j][0][c2] + part[j][1][c2] + part[j][2][c2] + part[j][3][c2];
+    const int64_t row = j == 0 ? 0 : 2 * (int64_t)L2 - 3 + j;
+    __half* q = y + (((int64_t)b * (C2 / 8) + c2 / 8) * (2 * (int64_t)L2) + row) * 8 + (c2 & 7);
+    *q = __float2half_rn(__half2float(*q) - corr);
   }
 }
 
@@ -513,9 +623,10 @@ struct LayerSpec {
   int rows_shrink;          // rows_out = rows_in - rows_shrink (TDNN, no padding)
 };
 
-enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, N_LAYERS };
+enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, L_DEC45, N_LAYERS };
 const char* const kLayerTag[N_LAYERS] = {"tapgemm:enc2", "tapgemm:enc5", "tapgemm:enc8", "tapgemm:enc11", "tapgemm:tdnn0", "tapgemm:tdnn3",
-                                        "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8"};
+                                        "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8",
+                                        "tapgemm:dec45"};
 
 // tc = this layer runs on the tcgen05 kernel (fp16 UMMA-packed weights)
 LayerSpec make_spec(int id, bool tc) {
@@ -533,6 +644,7 @@ LayerSpec make_spec(int id, bool tc) {
     case L_DEC1:  s = {PACK_CONVT_S2, 128, 64, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
     case L_DEC4:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
     case L_DEC5:  s = {PACK_CONVT_S2, 64, 32, 5, 64, 64, 0, {}, 2, 0};   taps({-1, 0, 1}); break;
+    case L_DEC45: s = {PACK_COMPOSED, 64, 32, 7, 64, 64, 0, {}, 2, 0};   taps({-3, -2, -1, 0, 1, 2, 3}); break;
     case L_DEC8:
       if (tc) { s = {PACK_TOEPLITZ, 32, 1, 15, 32, 16, 0, {}, 1, 0}; taps({-7}); }   // Toeplitz GEMM, see conv_tc.cu
       else { s = {PACK_CONV_S1, 32, 1, 15, 32, 4, 0, {}, 1, 0}; taps({-7, -6, -5, -4, -3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7}); }
@@ -548,6 +660,8 @@ struct Workspace {
   void* packed[N_LAYERS];
   float* bn_scale[4]; float* bn_shift[4];      // clf norm, tdnn bn 0..2
   float* ones;                                 // [128] 1.0f (unit scale of a bias-only affine on load)
+  float* bias45;                               // [64] per-column bias of the composed decoder.4 o decoder.5 layer
+  float* edge45;                               // [EDGE45_FLOATS] its edge-correction matrices (dec45_edge_kernel)
   double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
   float* in_scale[6]; float* in_shift[6];      // [chunk][C]
   double* pool;                                // [chunk][128][2]
@@ -582,6 +696,8 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
   }
   for (int i = 0; i < 4; ++i) { ws.bn_scale[i] = (float*)take(128 * 4); ws.bn_shift[i] = (float*)take(128 * 4); }
   ws.ones = (float*)take(128 * 4);
+  ws.bias45 = (float*)take(64 * 4);
+  ws.edge45 = (float*)take(EDGE45_FLOATS * 4);
   // stats are contiguous so one memset clears them
   for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * inC[i] * 2 * sizeof(double));
   ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
@@ -605,6 +721,12 @@ struct Ctx {
 };
 
 bool layer_on_tc(const Ctx& c, int id) { return c.tc; (void)id; }
+
+// $SPANON_COMPOSE_DEC=0 runs decoder.4 and decoder.5 as two launches on the tcgen05 path too (A/B switch)
+bool compose_dec45(const Ctx& c) {
+  static const bool on = !(getenv("SPANON_COMPOSE_DEC") && getenv("SPANON_COMPOSE_DEC")[0] == '0');
+  return c.tc && on;
+}
 
 int pack_layer(const Ctx& c, int id, const float* w) {
   const bool on_tc = layer_on_tc(c, id);
@@ -659,7 +781,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   }
   p.tap_step = s.ntaps > 1 ? s.shift[1] - s.shift[0] : 0;
   if (s.mode == PACK_CONV_S2) p.tap_kmax[s.ntaps - 1] = s.cin;   // tap (2*tap+1) = 5 does not exist
-  if (s.mode == PACK_CONVT_S2) p.tap_nmax[0] = s.cout;            // shift -1 only feeds the even phase
+  if (s.mode == PACK_CONVT_S2 || s.mode == PACK_COMPOSED) p.tap_nmax[0] = s.cout;   // the first shift only feeds the even phase
   p.w = c.ws.packed[id];
   p.t1_bstride = s.cin;
   if (io.in_norm >= 0) { p.t1_scale = c.ws.in_scale[io.in_norm]; p.t1_shift = c.ws.in_shift[io.in_norm]; p.silu = 1; }
@@ -667,6 +789,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   if (io.act >= 0) p.silu = io.act;
   if (io.t2_bn >= 0) { p.t2_scale = c.ws.bn_scale[io.t2_bn]; p.t2_shift = c.ws.bn_shift[io.t2_bn]; }
   p.bias = io.bias;
+  p.bias_v = id == L_DEC45 ? 1 : 0;
   p.relu = io.relu;
   if (io.e_bn >= 0) { p.e_scale = c.ws.bn_scale[io.e_bn]; p.e_shift = c.ws.bn_shift[io.e_bn]; }
   p.stats = io.out_stats >= 0 ? c.ws.stats[io.out_stats] : nullptr;
@@ -683,11 +806,16 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   // +40..+100 us per producing launch (the launch is already moving ~570 MB through L2 for HBM; the read-back competes
   // for the same L2 slices) against 66 us for the separate HBM-rate pass, so the fused form is kept as an option only.
   static const int fused_mode = getenv("SPANON_FUSED_STATS") ? atoi(getenv("SPANON_FUSED_STATS")) : 0;
-  const bool fuse = on_tc && io.out_stats >= 0 && (fused_mode >= 2 || (fused_mode == 1 && p.silu == 0));
+  const bool fuse = on_tc && io.out_stats >= 0 && id != L_DEC45 && (fused_mode >= 2 || (fused_mode == 1 && p.silu == 0));
   const bool split_stats = on_tc && io.out_stats >= 0 && !fuse;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
+    if (id == L_DEC45) {   // take the two rows of decoder.4 the reference does not have back out (before the statistics)
+      dec45_edge_kernel<<<(unsigned)nb, 384, 0, c.st>>>((const __half*)io.in, p.t1_scale, p.t1_shift, c.ws.edge45,
+                                                        (__half*)io.out, p.rows_in);
+      SPANON_TRY(check_launch("dec45_edge_kernel"));
+    }
     if (split_stats) {   // one bandwidth-bound pass over the fp16 plane just written (cheaper than reducing in the epilogue)
       const int P = p.out_fold == OUT_PAIR_FOLD ? s.cout_v / 4 : p.out_fold == OUT_PHASE_UNFOLD ? s.cout_v / 16 : s.cout_v / 8;
       dim3 grid((unsigned)ceil_div(p.out_plane_rows, ST_NT * ST_ROWS), (unsigned)P, (unsigned)nb);
@@ -785,8 +913,18 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   SPANON_TRY(pack_layer(c, L_ENC11, w->enc_w[4]));
   SPANON_TRY(pack_layer(c, L_DEC0, w->dec_w[0]));
   SPANON_TRY(pack_layer(c, L_DEC1, w->dec_w[1]));
-  SPANON_TRY(pack_layer(c, L_DEC4, w->dec_w[2]));
-  SPANON_TRY(pack_layer(c, L_DEC5, w->dec_w[3]));
+  if (compose_dec45(c)) {
+    compose_dec45_kernel<<<112, 256, 0, c.st>>>(w->dec_w[2], w->dec_w[3], (__half*)c.ws.packed[L_DEC45], 64, 64, 32);
+    SPANON_TRY(check_launch("compose_dec45_kernel"));
+    compose_dec45_bias_kernel<<<1, 64, 0, c.st>>>(w->dec_b[2], w->dec_w[3], w->dec_b[3], c.ws.bias45, 64, 32);
+    SPANON_TRY(check_launch("compose_dec45_bias_kernel"));
+    compose_dec45_edge_kernel<<<(unsigned)ceil_div(EDGE45_FLOATS, 256), 256, 0, c.st>>>(w->dec_w[2], w->dec_b[2], w->dec_w[3],
+                                                                                        c.ws.edge45, 64, 64, 32);
+    SPANON_TRY(check_launch("compose_dec45_edge_kernel"));
+  } else {
+    SPANON_TRY(pack_layer(c, L_DEC4, w->dec_w[2]));
+    SPANON_TRY(pack_layer(c, L_DEC5, w->dec_w[3]));
+  }
   SPANON_TRY(pack_layer(c, L_DEC8, w->dec_w[4]));
   if (run_clf) {
     SPANON_TRY(pack_layer(c, L_TD0, w->tdnn_w[0]));
@@ -871,10 +1009,15 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, nb_(w->dec_b[1]), 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2,
                                      OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC1, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
-    SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
-    SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, nb_(w->dec_b[3]), 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
-                                     OUT_PHASE_UNFOLD}, nb));
-    SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
+    if (compose_dec45(c)) {   // decoder.4 o decoder.5 as one 7-tap phase-view layer (compose_dec45_kernel)
+      SPANON_TRY(run_layer(c, L_DEC45, {X[2], X[3], 4, -1, c.ws.bias45, 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
+                                        OUT_PHASE_UNFOLD}, nb));
+    } else {
+      SPANON_TRY(run_layer(c, L_DEC4, {X[2], X[1], 4, -1, w->dec_b[2], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
+      SPANON_TRY(run_layer(c, L_DEC5, {X[1], X[3], -1, -1, nb_(w->dec_b[3]), 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
+                                       OUT_PHASE_UNFOLD}, nb));
+      SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
+    }
     SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
   }
   return SPANON_OK;

@@ -53,7 +53,8 @@ struct TapGemmParams {
   int64_t t1_bstride;  // tcgen05 kernel: elements between utterances of t1_* (0 = per-channel constants shared by all)
   int silu;                // activation on load: 0 none, 1 SiLU, 2 ReLU (2: tcgen05 kernel only)
   const float* t2_scale; const float* t2_shift;  // [cin_mod] or null
-  const float* bias;   // [cout_mod]
+  const float* bias;   // [cout_mod]  (bias_v != 0: [cout_v], one value per output COLUMN, tcgen05 kernel only)
+  int bias_v;
   int relu;
   const float* e_scale; const float* e_shift;    // [cout_mod] or null
   double* stats;       // [B][cout_mod][2] or null

@@ -206,6 +206,23 @@ def test_convae_vs_oracle_10s(precision, tol):
     assert np.max(np.abs(logp.cpu().numpy() - l_ref.numpy())) < (1e-4 if precision == "fp32" else 2e-2)
 
 
+def test_convae_composed_decoder_edges():
+    # The 16-bit path runs decoder.4 o decoder.5 (ConvAutoEncoder.py:166-167) as ONE composed transposed convolution
+    # and takes the two rows of decoder.4 that the reference does not have back out of y[0], y[L-2], y[L-1]
+    # (convae.cu: dec45_edge_kernel).  Those rows reach the first and last 8 samples of the reconstruction through
+    # decoder.8 (k15): their error must be no worse than the interior's, for short and long utterances alike.
+    m, w = load_model((sab.ConvAutoencoder, ()), recipe.CONVAE_SHAPES, precision="fp16")
+    for seed, B, T in [(51, 3, 1), (52, 2, 2), (53, 2, 5), (54, 1, 127)]:
+        x = recipe.make_feats(seed, B, T)
+        with torch.no_grad():
+            rec, _ = m(cu(x), pool_noise=cu(recipe.make_noise(seed, B, 128)))
+            r_ref, _ = anonymizer_ref.convae_forward(x, w, recipe.make_noise(seed, B, 128))
+        err = np.abs(rec.cpu().numpy().reshape(B, -1) - r_ref.numpy().reshape(B, -1)) / np.max(np.abs(r_ref.numpy()))
+        assert err.max() < 1e-2
+        edge = max(err[:, :8].max(), err[:, -8:].max())
+        assert edge < max(2.0 * err[:, 8:-8].max(), 2e-3), (T, edge, err[:, 8:-8].max())
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("fp16", 1e-2)])
 def test_convrecon_vs_golden_and_oracle(golden2, precision, tol):
     """ConvReconstruction ("endtoend", models/EndToEnd.py:36-87; scope row 8(f)-3)."""
