@@ -25,8 +25,11 @@
 //                            16-byte stores straight into the CONSUMER's chunk-planar view (direct, pair-folded for a
 //                            stride-2 consumer, phase-unfolded after a transposed conv): a warp's 32 rows of one chunk are
 //                            512 contiguous bytes.
-// InstanceNorm statistics of the output are a separate HBM-rate pass (instnorm_stats_kernel) by default; XF_STATS fuses
-// them into this kernel (the transform warps read the stored tiles back), which measured slower (see convae.cu run_layer).
+// InstanceNorm statistics of the output (XF_STATS instantiations, eight epilogue warps): reduced in the epilogue from the
+// accumulator values as they are stored (a butterfly reduce-scatter over the warp's 32 rows per 32-column block), kept
+// in registers per lane = column until the utterance changes, then added to `stats` with fp64 atomics.  That costs
+// +25..+48 us per producing launch on B200 against 72 us for a separate pass over the stored plane
+// (instnorm_stats_kernel, still used by the SIMT path and selectable with $SPANON_FUSED_STATS=0).
 //
 // 16-bit operands are fp16, not bf16: tools/precision_study.py shows bf16 operands + bf16 planes cannot hold the 1e-2
 // parity bar on this network (1.0-1.3e-2); fp16 gives 1.5e-3 at the same tensor-core rate.
@@ -41,17 +44,26 @@ namespace spanon {
 namespace {
 
 using namespace tc;
-constexpr int TC_EPI_WARPS = 4;           // one warp per TMEM lane quarter (448 threads per CTA -> 144 registers per thread)
 constexpr int TC_XF_WARPS = 8;            // transform warps; warp w owns the stages it == w (mod 8), one stage in flight each
-constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_XF_WARPS;
-constexpr int TC_LOAD_WARP = TC_MMA_WARP + 1;
 constexpr int TC_LOAD_WARPS = 2;          // loader l issues the stages it == l (mod 2): a lone warp needs ~300 cycles per stage
-constexpr int TC_THREADS = (TC_LOAD_WARP + TC_LOAD_WARPS) * 32;
-constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32;
+// Warp roles, E = epilogue warps (4: one per TMEM lane quarter; 8 when the epilogue also reduces the InstanceNorm
+// statistics: two per quarter, each half of the columns).  A warp runs on SM sub-partition warp % 4.  The issuer's
+// instruction stream (one thread, every instruction dependent on the last) is the kernel's critical path, so it gets
+// sub-partition 3 almost to itself: only the two loaders (a few instructions per stage) and one epilogue warp (TMEM lane
+// quarter 3 has to live there) share its scheduler; the eight transform warps run on sub-partitions 0..2.
+//   warps [0, E)            epilogue
+//   warps E+3, E+7          loaders
+//   warp  E+11              MMA issuer
+//   warp  E+10              idle
+//   other warps of [E, E+10) transform (E+0,1,2,4,5,6,8,9)
+__host__ __device__ constexpr int tc_epi_warps(int xf);
+__host__ __device__ constexpr int tc_threads(int xf) { return (tc_epi_warps(xf) + 12) * 32; }
+constexpr int TC_EPI_THREADS = 128;       // Toeplitz epilogue (always four warps)
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
 constexpr int TC_MAX_STAGES = 16;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
 enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8 };
+__host__ __device__ constexpr int tc_epi_warps(int xf) { return (xf & XF_STATS) ? 8 : 4; }
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
 constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
@@ -99,11 +111,14 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
 enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54 };
 
 template <int COUT_V, int XF>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(tc_threads(XF), 1)
 tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
   extern __shared__ __align__(128) unsigned char smem[];
   const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int E = tc_epi_warps(XF), TC_MMA_WARP = E + 11;
+  const int wd = warp - E;                                   // role index among the non-epilogue warps
+  const bool is_loader = wd == 3 || wd == 7, is_xform = wd >= 0 && wd < 10 && !is_loader;
   const uint32_t s_base = smem_u32(smem);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
   const uint32_t bar0 = s_base + L.bars;
@@ -122,9 +137,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         mbar_init(BAR(B_FULL + i), 1);
         mbar_init(BAR(B_EMPTY + i), 1);
       }
-      for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), TC_EPI_WARPS); }
+      for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), E); }
       mbar_init(BAR(B_W), 1);
-      const_cast<uint32_t*>(tmem_ptr_smem)[1] = 0u;          // tiles stored by the epilogue warps (XF_STATS)
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       // resident weights: one bulk async copy per tap slice
       mbar_expect_tx(BAR(B_W), L.w_bytes);
@@ -139,9 +153,9 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp < TC_EPI_WARPS) {  // epilogue constants
+  if (warp < E) {  // epilogue constants
     float* ec = reinterpret_cast<float*>(smem + L.epi);
-    for (int c = threadIdx.x; c < COUT_V; c += TC_EPI_THREADS) {
+    for (int c = threadIdx.x; c < COUT_V; c += E * 32) {
       const int cm = c % p.cout_mod;
       ec[c] = p.bias ? p.bias[p.bias_v ? c : cm] : 0.f;
       ec[COUT_V + c] = p.e_scale ? p.e_scale[cm] : 1.f;
@@ -154,12 +168,12 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int planes_in = p.cin_v / 8;
 
-  if (warp >= TC_LOAD_WARP) {
+  if (is_loader) {
     // =========================== LOADER ===========================
     // two bulk copies per stage (one per 8-channel chunk), issued by one elected lane of the converged warp
     {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
-      const int lw = warp - TC_LOAD_WARP;
+      const int lw = wd >> 2;
       uint32_t stage = (uint32_t)lw, ph = 0;
       int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
       for (int k = 0; k < n_my_tiles; ++k) {
@@ -185,7 +199,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
     }
-  } else if (warp >= TC_EPI_WARPS && warp < TC_MMA_WARP) {
+  } else if (is_xform) {
     // =========================== TRANSFORM (in place) ===========================
     // Eight warps; warp w owns the stages it == w (mod 8) (16 channels = two 8-channel chunks x slab rows), so eight
     // stages are in flight and the per-stage chain (mbarrier wait -> LDS -> math -> STS -> proxy fence -> arrive) is
@@ -194,10 +208,9 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     //   -> y*s2 + h2 (folded eval-mode BatchNorm of the producer)
     // i.e. per 8 elements 4 HFMA2 + 4 MUFU + 4 HFMA2 (+ 4 HFMA2).  Rows outside the utterance (= the conv's zero
     // padding of the already activated tensor) exist only in an utterance's first / last tile and are zeroed there.
-    const int xw = warp - TC_EPI_WARPS;
+    const int xw = wd - (wd >> 2);
     constexpr bool do_silu = (XF & 3) == XF_SILU, do_relu = (XF & 3) == XF_RELU, has_t2 = (XF & XF_T2) != 0;
     constexpr bool ident = (XF & 7) == XF_IDENT;
-    constexpr bool do_stats = (XF & XF_STATS) != 0;
     const bool has_t1 = p.t1_scale != nullptr;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
     const int s_fix = xw % n_stage_tile;                       // stage-in-tile of this warp (n_stage_tile is 2, 4 or 8)
@@ -217,99 +230,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
     }
     int b_const = -1;                                          // utterance whose t1 constants are in registers
-    // ---- fused InstanceNorm statistics of THIS layer's output (XF_STATS): the epilogue warps bump a shared-memory
-    // counter after storing a tile; TC_STATS_LAG tiles later the transform warps read the tile back (it is still in L1/L2), lanes = rows, and keep per-lane partial sums of their planes in registers until the utterance
-    // changes.  Warp w owns destination plane(s) w, w + 8 (or plane w % n_pl and every (8 / n_pl)-th row group).
-    constexpr int NCH_O = COUT_V / 8;
-    const int st_npl = p.out_fold == OUT_PAIR_FOLD ? 2 * NCH_O : p.out_fold == OUT_PHASE_UNFOLD ? NCH_O / 2 : NCH_O;
-    const int st_rpp = p.out_fold == OUT_PAIR_FOLD ? TC_M / 2 : p.out_fold == OUT_PHASE_UNFOLD ? 2 * TC_M : TC_M;
-    const int st_ppw = st_npl > TC_XF_WARPS ? st_npl / TC_XF_WARPS : 1;       // planes per warp (1 or 2)
-    const int st_wpp = st_npl < TC_XF_WARPS ? TC_XF_WARPS / st_npl : 1;       // warps per plane (1 or 2)
-    float st_s[2][8], st_q[2][8];
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { st_s[i][j] = 0.f; st_q[i][j] = 0.f; }
-    int st_b = -1;                                             // utterance the partial sums belong to
-    volatile uint32_t* st_counter = reinterpret_cast<volatile uint32_t*>(bars + B_TPTR) + 1;
-    const bool st_two = st_ppw == 2;
-    const int st_gpp = st_rpp / 32 / st_wpp;                   // row groups (32 rows) per plane and warp: 2, 4 or 8
-    auto st_flush = [&]() {
-      if (st_b < 0) return;
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        // slots 4..7 (st_*[1]) belong to the warp's second plane, or to the same plane when it has only one
-        if (i == 1 && !st_two) break;
-        const int pl = (xw % st_npl) + i * TC_XF_WARPS;
-        const int c0 = p.out_fold == OUT_PAIR_FOLD ? (pl % NCH_O) * 8 : pl * 8;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float a = warp_sum(st_two ? st_s[i][j] : st_s[0][j] + st_s[1][j]);
-          const float q = warp_sum(st_two ? st_q[i][j] : st_q[0][j] + st_q[1][j]);
-          if (lane == j) {
-            double* dst = p.stats + ((int64_t)st_b * p.cout_mod + c0 + j) * 2;
-            atomicAdd(dst, (double)a);
-            atomicAdd(dst + 1, (double)q);
-          }
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 2; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { st_s[i][j] = 0.f; st_q[i][j] = 0.f; }
-    };
-    // Software-pipelined over tiles: st_issue() starts the (up to eight) 16-byte loads of a stored tile, st_consume() adds
-    // the previous tile's values -- the L2 round trip of one tile hides behind the operand work of the next.
-    uint4 st_v[8];
-    int st_pending_b = -1;                                     // utterance of the tile whose loads are in flight
-    auto st_consume = [&]() {
-      if (st_pending_b < 0) return;
-      if (st_pending_b != st_b) { st_flush(); st_b = st_pending_b; }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const __half2* hv = reinterpret_cast<const __half2*>(&st_v[u]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 f = __half22float2(hv[j]);
-          st_s[u >> 2][2 * j] += f.x; st_s[u >> 2][2 * j + 1] += f.y;
-          st_q[u >> 2][2 * j] = fmaf(f.x, f.x, st_q[u >> 2][2 * j]);
-          st_q[u >> 2][2 * j + 1] = fmaf(f.y, f.y, st_q[u >> 2][2 * j + 1]);
-        }
-      }
-      st_pending_b = -1;
-    };
-    auto st_issue = [&](int j_tile) {
-      const int t = t_begin + j_tile;
-      const int tb = t / tiles_per_utt, ttin = t - tb * tiles_per_utt;
-      __threadfence_block();                                   // (the caller saw the epilogue's counter reach this tile)
-      const int m0 = ttin * tile_step;
-      const int r0 = p.out_fold == OUT_PAIR_FOLD ? m0 >> 1 : p.out_fold == OUT_PHASE_UNFOLD ? 2 * m0 : m0;
-      const __half* ob = reinterpret_cast<const __half*>(p.out) + (int64_t)tb * p.out_bstride;
-      const int g_first = (xw / st_npl) % st_wpp;
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int i = st_two ? (u >> 2) : 0, gi = st_two ? (u & 3) : u;
-        const int r = r0 + (g_first + gi * st_wpp) * 32 + lane;
-        st_v[u] = make_uint4(0u, 0u, 0u, 0u);
-        if (gi < st_gpp && r < p.out_plane_rows) {
-          const int pl = (xw % st_npl) + i * TC_XF_WARPS;
-          const uint4* src = reinterpret_cast<const uint4*>(ob + (((int64_t)pl * p.out_plane_rows + r) << 3));
-          asm volatile("ld.relaxed.cta.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(st_v[u].x), "=r"(st_v[u].y), "=r"(st_v[u].z), "=r"(st_v[u].w) : "l"(src) : "memory");
-        }
-      }
-      st_pending_b = tb;
-    };
-    // opportunistic: reduce the next stored tile if the epilogue has published it, never wait for it (waiting would tie
-    // the operand pipeline's run-ahead to the epilogue); the remainder is drained after the last stage
-    int st_next = 0;
-    auto st_poll = [&]() {
-      if (st_next < n_my_tiles && *st_counter >= (uint32_t)(st_next + 1) * TC_EPI_WARPS) {
-        st_consume();
-        st_issue(st_next);
-        ++st_next;
-      }
-    };
     for (; k < n_my_tiles; k += kstep) {
       const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
@@ -325,11 +245,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
         b_const = b;
       }
-      if (do_stats) {
-        while (!mbar_try(BAR(B_RAW + stage), ph)) st_poll();
-      } else {
-        mbar_wait(BAR(B_RAW + stage), ph);
-      }
+      mbar_wait(BAR(B_RAW + stage), ph);
       const int it = k * n_stage_tile + s_fix;
       if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
       unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)lane * 16u;
@@ -375,19 +291,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
       tin += kstep;
       while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
-      if (do_stats) {
-        for (int n = 0; n < kstep; ++n) st_poll();             // keep pace: one stored tile per tile of operand work
-      }
-    }
-    if (do_stats) {
-      while (st_next < n_my_tiles) {
-        while (*st_counter < (uint32_t)(st_next + 1) * TC_EPI_WARPS) __nanosleep(64);
-        st_consume();
-        st_issue(st_next);
-        ++st_next;
-      }
-      st_consume();
-      st_flush();
     }
   } else if (warp == TC_MMA_WARP) {
     // =========================== MMA ISSUER ===========================
@@ -435,13 +338,13 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         tc_commit_elect(BAR(B_TFULL + buf));        // accumulator complete
       }
     }
-  } else {
+  } else if (warp < E) {
     // =========================== EPILOGUE ===========================
     // warp w: TMEM lanes (rows) 32*(w%4).., columns [(w/4)*COUT_V/2, +COUT_V/2)
     const float* ec = reinterpret_cast<const float*>(smem + L.epi);
     const int quarter = warp & 3, chalf = warp >> 2;
     const int mloc = quarter * 32 + lane;
-    constexpr int CPW = COUT_V / (TC_EPI_WARPS / 4);     // columns per warp
+    constexpr int CPW = COUT_V / (E / 4);     // columns per warp
     constexpr int NCH = COUT_V / 8;     // output chunks
     const bool cl = p.out_mode == OUT_CHANNELS_LAST;
     int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
@@ -473,7 +376,22 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
         if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
-    } else
+    } else {
+    // ---- InstanceNorm statistics of the output from the accumulator itself (XF_STATS): after a 32-column block is
+    // stored, a butterfly over the warp's 32 rows (reduce-scatter: 31 shuffles for 32 columns) leaves lane l with the
+    // sum (and the sum of squares) of column cb + l; they stay in registers until the utterance changes.
+    constexpr bool e_stats = (XF & XF_STATS) != 0;
+    float es[4] = {0.f, 0.f, 0.f, 0.f}, eq[4] = {0.f, 0.f, 0.f, 0.f};
+    auto e_flush = [&](int bb) {
+#pragma unroll
+      for (int i = 0; i < CPW / 32; ++i) {
+        const int ch = (chalf * CPW + 32 * i + lane) % p.cout_mod;
+        double* dst = p.stats + ((int64_t)bb * p.cout_mod + ch) * 2;
+        atomicAdd(dst, (double)es[i]);
+        atomicAdd(dst + 1, (double)eq[i]);
+        es[i] = 0.f; eq[i] = 0.f;
+      }
+    };
     for (int k = 0; k < n_my_tiles; ++k) {
       const int m0 = tin * tile_step;
       const int m = m0 + mloc;
@@ -526,17 +444,37 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
             }
           }
         }
-      }
-      if constexpr ((XF & XF_STATS) != 0) {              // publish the stored tile to the transform warps' statistics pass
-        __threadfence_block();
-        __syncwarp();
-        if (lane == 0) atomicAdd(const_cast<uint32_t*>(tmem_ptr_smem) + 1, 1u);
+        if constexpr (e_stats) {
+          float q[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float x = valid ? v[j] : 0.f; v[j] = x; q[j] = x * x; }
+#pragma unroll
+          for (int h = 16; h >= 1; h >>= 1) {
+            const bool up = (lane & h) != 0;      // this lane keeps the columns whose bit h is set
+#pragma unroll
+            for (int j = 0; j < h; ++j) {
+              const float sv = up ? v[j] : v[j + h], kv = up ? v[j + h] : v[j];
+              const float sq = up ? q[j] : q[j + h], kq = up ? q[j + h] : q[j];
+              v[j] = kv + __shfl_xor_sync(0xffffffffu, sv, h);
+              q[j] = kq + __shfl_xor_sync(0xffffffffu, sq, h);
+            }
+          }
+          const int cbi = (cb - chalf * CPW) >> 5;
+#pragma unroll
+          for (int i = 0; i < CPW / 32; ++i)
+            if (i == cbi) { es[i] += v[0]; eq[i] += q[0]; }
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
-      if (++tin == tiles_per_utt) { tin = 0; ++b; }
+      if (++tin == tiles_per_utt) {
+        if constexpr (e_stats) e_flush(b);
+        tin = 0; ++b;
+      }
+    }
+    if constexpr (e_stats) { if (tin != 0) e_flush(b); }
     }
   }
 
@@ -569,7 +507,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int grid = std::min(total, n_sm);
   static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
   if (!trace_on) {
-    kern<<<grid, TC_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step);
+    kern<<<grid, tc_threads(XF), L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step);
     return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   }
   // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch
@@ -579,7 +517,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
   TapGemmParams q = p;
   q.trace = dbuf;
-  kern<<<grid, TC_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total, tile_step);
+  kern<<<grid, tc_threads(XF), L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total, tile_step);
   int rc = check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
   std::vector<long long> h((size_t)6 * TRACE_N);

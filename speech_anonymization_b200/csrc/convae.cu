@@ -148,7 +148,7 @@ __global__ void compose_dec45_edge_kernel(const float* __restrict__ w4, const fl
 // fp16 of the composed layer's input, scale/shift: its InstanceNorm affine [utt][64]; y: planes [utt][4][2*L2][8] fp16.
 __global__ void __launch_bounds__(384)
 dec45_edge_kernel(const __half* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                  const float* __restrict__ E, __half* __restrict__ y, int L2) {
+                  const float* __restrict__ E, __half* __restrict__ y, int L2, double* __restrict__ stats) {
   constexpr int C0 = 64, C2 = 32;
   __shared__ float xs[4][C0], part[3][4][C2];
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -179,7 +179,14 @@ dec45_edge_kernel(const __half* __restrict__ x, const float* __restrict__ scale,
     const float corr = part[j][0][c2] + part[j][1][c2] + part[j][2][c2] + part[j][3][c2];
     const int64_t row = j == 0 ? 0 : 2 * (int64_t)L2 - 3 + j;
     __half* q = y + (((int64_t)b * (C2 / 8) + c2 / 8) * (2 * (int64_t)L2) + row) * 8 + (c2 & 7);
-    *q = __float2half_rn(__half2float(*q) - corr);
+    const float was = __half2float(*q);
+    const __half now = __float2half_rn(was - corr);
+    *q = now;
+    if (stats) {   // statistics already reduced by the producing kernel's epilogue: move them with the corrected sample
+      const float nw = __half2float(now);
+      atomicAdd(stats + ((int64_t)b * C2 + c2) * 2, (double)(nw - was));
+      atomicAdd(stats + ((int64_t)b * C2 + c2) * 2 + 1, (double)nw * nw - (double)was * was);
+    }
   }
 }
 
@@ -799,21 +806,20 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.in_planar = c.tc ? 1 : 0;
   p.B = nb;
   p.tag = kLayerTag[id];
-  // InstanceNorm statistics of a tcgen05 layer's output: fused into the producing kernel (its transform warps reduce the
-  // stored tiles while they are still in cache) or a separate bandwidth-bound pass over the plane (instnorm_stats_kernel).
-  // $SPANON_FUSED_STATS: 0 = always separate (default), 1 = fused where the transform warps are idle (no activation on
-  // load), 2 = fused everywhere.  Measured on B200 (tools/ab_env.sh, 60 x 10 s): reading the stored tiles back costs
-  // +40..+100 us per producing launch (the launch is already moving ~570 MB through L2 for HBM; the read-back competes
-  // for the same L2 slices) against 66 us for the separate HBM-rate pass, so the fused form is kept as an option only.
-  static const int fused_mode = getenv("SPANON_FUSED_STATS") ? atoi(getenv("SPANON_FUSED_STATS")) : 0;
-  const bool fuse = on_tc && io.out_stats >= 0 && id != L_DEC45 && (fused_mode >= 2 || (fused_mode == 1 && p.silu == 0));
+  // InstanceNorm statistics of a tcgen05 layer's output: reduced by the producing kernel's epilogue (default), or by a
+  // separate bandwidth-bound pass over the stored plane (instnorm_stats_kernel, $SPANON_FUSED_STATS=0).  Measured on
+  // B200 (tools/ab_env.sh SPANON_FUSED_STATS 0 1, 60 x 10 s): +25..+48 us per producing launch against 66 + 6 us for
+  // the separate pass and its 310 MB of re-read, 2.33 -> 2.20 ms per step.  (Two earlier forms, the transform warps
+  // reading the stored tiles back through L2, and the butterfly on four epilogue warps, were slower than the pass.)
+  static const bool fused_stats = !(getenv("SPANON_FUSED_STATS") && getenv("SPANON_FUSED_STATS")[0] == '0');
+  const bool fuse = on_tc && io.out_stats >= 0 && fused_stats;
   const bool split_stats = on_tc && io.out_stats >= 0 && !fuse;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
     if (id == L_DEC45) {   // take the two rows of decoder.4 the reference does not have back out (before the statistics)
       dec45_edge_kernel<<<(unsigned)nb, 384, 0, c.st>>>((const __half*)io.in, p.t1_scale, p.t1_shift, c.ws.edge45,
-                                                        (__half*)io.out, p.rows_in);
+                                                        (__half*)io.out, p.rows_in, fuse ? c.ws.stats[io.out_stats] : nullptr);
       SPANON_TRY(check_launch("dec45_edge_kernel"));
     }
     if (split_stats) {   // one bandwidth-bound pass over the fp16 plane just written (cheaper than reducing in the epilogue)

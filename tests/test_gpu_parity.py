@@ -442,7 +442,7 @@ def test_graphed_step_equals_direct_launches(golden):
     rec_d, logp_d = pipe(buf, pool_noise=noise)
     rec_d2, logp_d2 = pipe(cu(wav2), pool_noise=noise)
     g = pipe.capture(buf, pool_noise=noise)
-    assert g.launches >= 25
+    assert g.launches >= 19
     r, l = g.replay()
     torch.cuda.synchronize()
     assert rel_max(r.cpu().numpy(), rec_d.cpu().numpy()) < 1e-6 and float((l - logp_d).abs().max()) < 1e-6
