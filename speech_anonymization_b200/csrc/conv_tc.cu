@@ -85,7 +85,8 @@ struct TcLayout {        // byte offsets inside dynamic shared memory
   int n_stages, slab;
 };
 
-__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used) {
+constexpr int TC_ST_PITCH = 17;              // fp32 row pitch of the statistics transpose buffer ([32 rows][16 columns] per warp)
+__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, bool stats) {
   TcLayout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;              // == 1 (mod 8): chunks start 16 B apart modulo 128 B
   L.lbo_a = (uint32_t)L.slab * 16u;
@@ -93,8 +94,9 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.w_bytes = (uint32_t)ntaps * cin_v * cout_v * 2u;
   L.w = 0;
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
-  L.red = L.epi + 3u * cout_v * 4u;                   // Toeplitz epilogue only: 2 x [128][17] fp32 copies of the tile
-  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : 0u);
+  L.red = L.epi + 3u * cout_v * 4u;                   // Toeplitz epilogue: 2 x [128][17] fp32 copies of the tile;
+                                                      // statistics: one [32][17] fp32 transpose buffer per epilogue warp
+  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : stats ? 8u * 32u * TC_ST_PITCH * 4u : 0u);
   L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
@@ -114,7 +116,7 @@ template <int COUT_V, int XF>
 __global__ void __launch_bounds__(tc_threads(XF), 1)
 tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int E = tc_epi_warps(XF), TC_MMA_WARP = E + 11;
   const int wd = warp - E;                                   // role index among the non-epilogue warps
@@ -378,8 +380,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
     } else {
     // ---- InstanceNorm statistics of the output from the accumulator itself (XF_STATS): after a 32-column block is
-    // stored, a butterfly over the warp's 32 rows (reduce-scatter: 31 shuffles for 32 columns) leaves lane l with the
-    // sum (and the sum of squares) of column cb + l; they stay in registers until the utterance changes.
+    // stored, its column sums over the warp's 32 rows leave lane l with the sum (and the sum of squares) of column
+    // cb + l; they stay in registers until the utterance changes.
     constexpr bool e_stats = (XF & XF_STATS) != 0;
     float es[4] = {0.f, 0.f, 0.f, 0.f}, eq[4] = {0.f, 0.f, 0.f, 0.f};
     auto e_flush = [&](int bb) {
@@ -445,24 +447,28 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           }
         }
         if constexpr (e_stats) {
-          float q[32];
+          // column sums over the warp's 32 rows through a padded shared-memory transpose, 16 columns at a time:
+          // lane = row writes its values, lane = (column c, row half) reads 16 rows of column c (both conflict-free)
+          float* tb = reinterpret_cast<float*>(smem + L.red) + warp * (32 * TC_ST_PITCH);
+          float bs = 0.f, bq = 0.f;                 // this lane's column (cb + lane): sum, sum of squares
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { const float x = valid ? v[j] : 0.f; v[j] = x; q[j] = x * x; }
+          for (int hf = 0; hf < 2; ++hf) {
+            __syncwarp();
 #pragma unroll
-          for (int h = 16; h >= 1; h >>= 1) {
-            const bool up = (lane & h) != 0;      // this lane keeps the columns whose bit h is set
+            for (int j = 0; j < 16; ++j) tb[lane * TC_ST_PITCH + j] = valid ? v[16 * hf + j] : 0.f;
+            __syncwarp();
+            const float* col = tb + ((lane >> 4) * 16) * TC_ST_PITCH + (lane & 15);
+            float a0 = 0.f, q0 = 0.f;
 #pragma unroll
-            for (int j = 0; j < h; ++j) {
-              const float sv = up ? v[j] : v[j + h], kv = up ? v[j + h] : v[j];
-              const float sq = up ? q[j] : q[j + h], kq = up ? q[j + h] : q[j];
-              v[j] = kv + __shfl_xor_sync(0xffffffffu, sv, h);
-              q[j] = kq + __shfl_xor_sync(0xffffffffu, sq, h);
-            }
+            for (int r = 0; r < 16; ++r) { const float x = col[r * TC_ST_PITCH]; a0 += x; q0 = fmaf(x, x, q0); }
+            a0 += __shfl_xor_sync(0xffffffffu, a0, 16);
+            q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
+            if ((lane >> 4) == hf) { bs = a0; bq = q0; }
           }
           const int cbi = (cb - chalf * CPW) >> 5;
 #pragma unroll
           for (int i = 0; i < CPW / 32; ++i)
-            if (i == cbi) { es[i] += v[0]; eq[i] += q[0]; }
+            if (i == cbi) { es[i] += bs; eq[i] += bq; }
         }
       }
       tc_fence_before();
@@ -498,7 +504,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
   const int nst = p.cin_v / TC_STAGE_CH;
   if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0);
   if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc_kernel<COUT_V, XF>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
