@@ -381,13 +381,13 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     } else {
     // ---- InstanceNorm statistics of the output from the accumulator itself (XF_STATS): after a 32-column block is
     // stored, its column sums over the warp's 32 rows leave lane l with the sum (and the sum of squares) of column
-    // cb + l; they stay in registers until the utterance changes.
+    // cb + 2*(l & 15) + (l >> 4); they stay in registers until the utterance changes.
     constexpr bool e_stats = (XF & XF_STATS) != 0;
     float es[4] = {0.f, 0.f, 0.f, 0.f}, eq[4] = {0.f, 0.f, 0.f, 0.f};
     auto e_flush = [&](int bb) {
 #pragma unroll
       for (int i = 0; i < CPW / 32; ++i) {
-        const int ch = (chalf * CPW + 32 * i + lane) % p.cout_mod;
+        const int ch = (chalf * CPW + 32 * i + 2 * (lane & 15) + (lane >> 4)) % p.cout_mod;
         double* dst = p.stats + ((int64_t)bb * p.cout_mod + ch) * 2;
         atomicAdd(dst, (double)es[i]);
         atomicAdd(dst + 1, (double)eq[i]);
@@ -409,6 +409,11 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       for (int cb = chalf * CPW; cb < (chalf + 1) * CPW; cb += 32) {
         float v[32];
         tmem_ld32(taddr + (uint32_t)cb, v);
+        if (cb + 32 >= (chalf + 1) * CPW) {                  // last read of this accumulator buffer: hand it back now,
+          tc_fence_before();                                 // the stores (and statistics) below overlap the next MMAs
+          __syncwarp();
+          if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));
+        }
         if (p.bias) {   // (a bias in front of an InstanceNorm is a no-op and is dropped by the caller)
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
@@ -429,14 +434,17 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
             v[j + 2] = fmaf(v[j + 2], es.z, eh.z); v[j + 3] = fmaf(v[j + 3], es.w, eh.w);
           }
         }
+        uint32_t hw[16];                                      // the block as stored: 16 fp16 pairs
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const __half2 h2 = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
+          hw[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        }
         if (cl) {
           if (valid) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              uint4 o;
-              __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) oh[j] = __floats2half2_rn(v[8 * q + 2 * j], v[8 * q + 2 * j + 1]);
+              const uint4 o = make_uint4(hw[4 * q], hw[4 * q + 1], hw[4 * q + 2], hw[4 * q + 3]);
               const int c8 = (cb >> 3) + q;
               int pl, row;       // destination plane / row in the consumer's view
               if (p.out_fold == OUT_PAIR_FOLD) { pl = (m & 1) * NCH + c8; row = m >> 1; }
@@ -447,33 +455,31 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           }
         }
         if constexpr (e_stats) {
-          // column sums over the warp's 32 rows through a padded shared-memory transpose, 16 columns at a time:
-          // lane = row writes its values, lane = (column c, row half) reads 16 rows of column c (both conflict-free)
-          float* tb = reinterpret_cast<float*>(smem + L.red) + warp * (32 * TC_ST_PITCH);
-          float bs = 0.f, bq = 0.f;                 // this lane's column (cb + lane): sum, sum of squares
+          // column sums over the warp's 32 rows of the values AS STORED (fp16 pairs), through a padded shared-memory
+          // transpose: lane = row writes its 16 words, lane = (word w, row half) reads 16 rows of word w (both
+          // conflict-free); the halves meet in one shuffle and lane l keeps column cb + 2*(l & 15) + (l >> 4)
+          uint32_t* tb = reinterpret_cast<uint32_t*>(smem + L.red) + warp * (32 * TC_ST_PITCH);
+          __syncwarp();
 #pragma unroll
-          for (int hf = 0; hf < 2; ++hf) {
-            __syncwarp();
+          for (int j = 0; j < 16; ++j) tb[lane * TC_ST_PITCH + j] = valid ? hw[j] : 0u;
+          __syncwarp();
+          const uint32_t* col = tb + ((lane >> 4) * 16) * TC_ST_PITCH + (lane & 15);
+          float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) tb[lane * TC_ST_PITCH + j] = valid ? v[16 * hf + j] : 0.f;
-            __syncwarp();
-            const float* col = tb + ((lane >> 4) * 16) * TC_ST_PITCH + (lane & 15);
-            float a0 = 0.f, q0 = 0.f;
-#pragma unroll
-            for (int r = 0; r < 16; ++r) { const float x = col[r * TC_ST_PITCH]; a0 += x; q0 = fmaf(x, x, q0); }
-            a0 += __shfl_xor_sync(0xffffffffu, a0, 16);
-            q0 += __shfl_xor_sync(0xffffffffu, q0, 16);
-            if ((lane >> 4) == hf) { bs = a0; bq = q0; }
+          for (int r = 0; r < 16; ++r) {
+            const uint32_t w = col[r * TC_ST_PITCH];
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+            a0 += f.x; a1 += f.y; q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
           }
+          a0 += __shfl_xor_sync(0xffffffffu, a0, 16); a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+          q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+          const float bs = (lane >> 4) ? a1 : a0, bq = (lane >> 4) ? q1 : q0;
           const int cbi = (cb - chalf * CPW) >> 5;
 #pragma unroll
           for (int i = 0; i < CPW / 32; ++i)
             if (i == cbi) { es[i] += bs; eq[i] += bq; }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));   // accumulator buffer may be overwritten
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
       if (++tin == tiles_per_utt) {
         if constexpr (e_stats) e_flush(b);

@@ -996,7 +996,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         t6.t1s = c.ws.ones; t6.t1h = w->tdnn_b[1]; t6.act = 2;     // ReLU(x + b1) -> BatchNorm 2
         SPANON_TRY(run_layer(c, L_TD6, t6, nb));
         // (pooling in tdnn.6's epilogue instead -- a lane rotation per column hands each value to the lane owning its bin
-        // -- was measured at +140 us on that launch against 85 us for this pass: the kernel is issue-bound)
+        // -- was measured at +140 us on that launch against 85 us for this pass: ~20 dependent instructions per column on
+        // two warps per TMEM lane quarter run at ~3 cycles each)
         dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);   // ReLU(x + b2) -> BatchNorm 3 -> pooling
         pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, w->tdnn_b[2], c.ws.bn_scale[3],
                                                    c.ws.bn_shift[3], c.ws.pool);
