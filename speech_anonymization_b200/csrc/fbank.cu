@@ -128,11 +128,12 @@ fbank400_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_strid
   const int t0 = blockIdx.x * FRAMES_PER_CTA;
   const TS* x = pcm + (int64_t)b * pcm_stride;
 
-  // twiddles (fp64 evaluation, once per CTA: 400 sincos) and the window
+  // twiddles and the window, once per CTA.  fp32 sincospif (<= 1 ulp) of the correctly rounded -i/200: an fp64
+  // evaluation here was ~a quarter of the kernel's instruction issue (ncu: the conversion/MUFU pipe saturated).
   for (int i = tid; i < N_FFT; i += NT) {
-    double s, c;
-    sincospi(-2.0 * (double)i / (double)N_FFT, &s, &c);
-    S.tw[i] = make_float2((float)c, (float)s);
+    float s, c;
+    sincospif((float)(-i) / 200.f, &s, &c);
+    S.tw[i] = make_float2(c, s);
     S.win[i] = cfg.window[i];
   }
   // PCM segment: padded sample p = t*HOP + n - N_FFT/2  (center=True, zero padding)
@@ -199,6 +200,9 @@ fbank400_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_strid
   // mel projection + dB + running max
   const int n_mels = cfg.n_mels;
   float lmax = -INFINITY;
+  // amplitude -> dB in fp32 like the reference (processing/features.py:701-710); the floor value (silence: exactly
+  // -100 dB in the reference's test_features.py:66-77) is evaluated once in fp64
+  const float db_floor = (float)((double)cfg.multiplier * log10((double)cfg.amin)) - cfg.db_offset;
   for (int w = tid; w < FRAMES_PER_CTA * n_mels; w += NT) {
     const int fr = w / n_mels;
     const int m = w - fr * n_mels;
@@ -210,8 +214,7 @@ fbank400_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_strid
     const float* p = P + fr * P_STRIDE + st;
     float acc = 0.f;
     for (int i = 0; i < ln; ++i) acc = fmaf(p[i], __ldg(wv + i), acc);
-    // fp64 log10: exactly -100 dB for silence (reference test_features.py:66-77)
-    const float db = (float)((double)cfg.multiplier * log10((double)fmaxf(acc, cfg.amin))) - cfg.db_offset;
+    const float db = acc <= cfg.amin ? db_floor : cfg.multiplier * log10f(acc) - cfg.db_offset;
     out[((int64_t)b * T + t) * n_mels + m] = db;
     lmax = fmaxf(lmax, db);
   }
