@@ -385,7 +385,7 @@ def run_ours(a):
         if os.path.exists(tp):
             tj = json.load(open(tp))
             traffic = tj["conv_stack"]["traffic_mb_per_launch"] * 1e6 * B / 60.0
-            tsrc = "profiles/r01_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, avg over the 13 conv launches)"
+            tsrc = "profiles/r01_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, avg over the %d conv launches of a step)" % tj["conv_stack"].get("launches_captured", 0)
         ms_launch = conv_ms / max(conv_launches, 1)
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "traffic": traffic, "traffic_source": tsrc, "kernel": "conv stack (first_layer + tap-GEMM launches)",
