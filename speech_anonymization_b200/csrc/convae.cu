@@ -580,19 +580,29 @@ pool_planar_kernel(const __half* __restrict__ x, int P, int R, const float* __re
     s[j] = 0.f; q[j] = 0.f;
     cb[j] = __ldg(bias + 8 * p + j); cs[j] = __ldg(bn_scale + 8 * p + j); ch[j] = __ldg(bn_shift + 8 * p + j);
   }
-#pragma unroll 8
-  for (int i = 0; i < PL_ROWS; ++i) {
-    const int r = r0 + i * PL_NT + tid;
-    if (r < R) {
-      const uint4 v = __ldg(base + r);
-      const __half2* h = reinterpret_cast<const __half2*>(&v);
+  constexpr int PL_BATCH = 8;   // 16 B loads in flight per thread (issued back to back before any use, as in instnorm_stats_kernel)
+#pragma unroll 1
+  for (int i0 = 0; i0 < PL_ROWS; i0 += PL_BATCH) {
+    uint4 v[PL_BATCH];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float2 f = __half22float2(h[j]);
-        f.x = fmaf(fmaxf(f.x + cb[2 * j], 0.f), cs[2 * j], ch[2 * j]);
-        f.y = fmaf(fmaxf(f.y + cb[2 * j + 1], 0.f), cs[2 * j + 1], ch[2 * j + 1]);
-        s[2 * j] += f.x; s[2 * j + 1] += f.y;
-        q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
+    for (int u = 0; u < PL_BATCH; ++u) {
+      const int r = r0 + (i0 + u) * PL_NT + tid;
+      const uint4* src = base + (r < R ? r : 0);
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src));
+    }
+#pragma unroll
+    for (int u = 0; u < PL_BATCH; ++u) {
+      if (r0 + (i0 + u) * PL_NT + tid < R) {
+        const __half2* h = reinterpret_cast<const __half2*>(&v[u]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float2 f = __half22float2(h[j]);
+          f.x = fmaf(fmaxf(f.x + cb[2 * j], 0.f), cs[2 * j], ch[2 * j]);
+          f.y = fmaf(fmaxf(f.y + cb[2 * j + 1], 0.f), cs[2 * j + 1], ch[2 * j + 1]);
+          s[2 * j] += f.x; s[2 * j + 1] += f.y;
+          q[2 * j] = fmaf(f.x, f.x, q[2 * j]); q[2 * j + 1] = fmaf(f.y, f.y, q[2 * j + 1]);
+        }
       }
     }
   }
