@@ -412,6 +412,8 @@ def run_ours(a):
     extras = None
     if rank == 0 and world == 1 and a.workload == "convae" and not a.no_extras:
         extras = time_extras(sab, _lib, recipe, dev, B, T)
+        if a.workload == "convae":
+            extras["library_gpu_convae_fwd"] = time_library_gpu(recipe, dev, B, T)
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -472,6 +474,63 @@ def time_extras(sab, _lib, recipe, dev, B, T, iters=6):
     gemm_ms = sum(v for k, v in g["kernels_ms"].items() if k.startswith("xv_gemm"))
     g["tdnn_gflop_per_utt"] = 2 * macs / 1e9
     g["tdnn_tflops"] = 2 * macs * B / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    return out
+
+
+def time_library_gpu(recipe, dev, B, T, iters=4):
+    """the library-kernel baseline -- the same ConvAutoencoder + classifier forward written with plain
+    torch ops (cuDNN / ATen kernels, fp16 weights and activations) on the same device-resident feature batch.  None of
+    this repo's kernels run here; it is reported under `extras`, it is not a bench value."""
+    import torch.nn.functional as F
+    w = {k: torch.from_numpy(np.asarray(v)).to(dev).half() for k, v in recipe.make_weights(recipe.CONVAE_SHAPES, 8886).items()}
+    feats = torch.from_numpy(recipe.make_feats(50, B, T)).to(dev).half()
+    noise = torch.from_numpy(recipe.make_noise(9, B, 128)).to(dev).half()
+    act = lambda x: x * torch.sigmoid(x)
+    inorm = lambda x, p: F.instance_norm(x, weight=w[p + ".weight"], bias=w[p + ".bias"], eps=1e-5)
+    bnorm = lambda x, p: F.batch_norm(x, w[p + ".running_mean"], w[p + ".running_var"], w[p + ".weight"], w[p + ".bias"], False, 0.0, 1e-5)
+    conv = lambda x, p, **kw: F.conv1d(x, w[p + ".weight"], w[p + ".bias"], **kw)
+    convt = lambda x, p: F.conv_transpose1d(x, w[p + ".weight"], w[p + ".bias"], stride=2, padding=2, output_padding=1)
+
+    def fwd(f):
+        x = f.reshape(B, 1, -1)
+        x = act(conv(x, "encoder.0", padding=7))
+        x = act(inorm(conv(x, "encoder.2", stride=2, padding=2), "encoder.3"))
+        x = act(inorm(conv(x, "encoder.5", padding=2), "encoder.6"))
+        x = act(inorm(conv(x, "encoder.8", stride=2, padding=2), "encoder.9"))
+        enc = act(inorm(conv(x, "encoder.11", padding=2), "encoder.12"))
+        c = bnorm(enc, "sex_classifier.norm")
+        for i, dil in ((0, 1), (3, 2), (6, 3)):
+            c = bnorm(F.relu(conv(c, "sex_classifier.tdnn.%d" % i, dilation=dil)), "sex_classifier.tdnn.%d" % (i + 2))
+        c = c.reshape(B, c.shape[2], c.shape[1]).float()
+        st = torch.cat((c.mean(dim=1) + noise.float(), c.std(dim=1) + 1e-5), dim=1).half()
+        st = bnorm(F.relu(F.linear(st, w["sex_classifier.classify.0.weight"], w["sex_classifier.classify.0.bias"])), "sex_classifier.classify.2")
+        st = bnorm(F.relu(F.linear(st, w["sex_classifier.classify.3.weight"], w["sex_classifier.classify.3.bias"])), "sex_classifier.classify.5")
+        logp = F.log_softmax(F.linear(st, w["sex_classifier.classify.6.weight"], w["sex_classifier.classify.6.bias"]).float(), 1)
+        x = convt(conv(enc, "decoder.0", padding=2), "decoder.1")
+        x = act(inorm(x, "decoder.2"))
+        x = convt(conv(x, "decoder.4", padding=2), "decoder.5")
+        x = act(inorm(x, "decoder.6"))
+        return conv(x, "decoder.8", padding=7).reshape(B, T, -1), logp
+
+    try:
+        with torch.no_grad():
+            for _ in range(2):
+                fwd(feats)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fwd(feats)
+            e1.record()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        out = {"ms_per_batch": ms, "batch": B, "frames": T, "audio_s_per_s": B * UTT_SECONDS / (ms * 1e-3),
+               "what": "ConvAutoencoder + classifier forward on device-resident features with torch ops "
+                       "(cuDNN/ATen, fp16), no Fbank/normalisation; this repo's kernels are not involved"}
+    except Exception as e:   # (cuDNN may refuse the 80 640-sample 1-D problem or run out of workspace)
+        out = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
+    del w, feats
+    torch.cuda.empty_cache()
     return out
 
 
