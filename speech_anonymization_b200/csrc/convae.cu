@@ -329,6 +329,7 @@ instnorm_stats_f32c32_kernel(const float* __restrict__ x, int R, double* __restr
 
 // ------------------------------------------------------------------ encoder.0 (1 -> 32, k15, p7) + SiLU
 constexpr int FL_NT = 256;
+constexpr int FL_CHUNKS = 3;     // 256-row chunks per block of first_layer_mma_kernel
 // ACT = false stores the raw convolution (ConvReconstruction puts an InstanceNorm between encoder.0 and its "GLU")
 template <typename TAct, bool FAST_ACT, bool ACT = true>
 __global__ void __launch_bounds__(FL_NT)
@@ -418,25 +419,13 @@ first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, i
                        const float* __restrict__ norm_mean, const float* __restrict__ norm_std,
                        const int32_t* __restrict__ utt_max, float top_db, const float* __restrict__ w /*[32][1][15]*/,
                        const float* __restrict__ bias, __half* __restrict__ out, int64_t out_bstride) {
-  __shared__ __align__(16) __half sh[2][FL_NT + 32];    // sh[0][i] = x[l0 - 7 + i], sh[1][i] = x[l0 - 6 + i]
+  // A block walks FL_CHUNKS consecutive 256-row chunks: the weight fragments below (a third of the per-chunk
+  // instructions of this issue-bound kernel) are then built once per 768 rows.  Two copies of the signal buffer
+  // alternate, so one barrier per chunk is enough.
+  __shared__ __align__(16) __half shbuf[2][2][FL_NT + 32];    // [buffer]: sh[0][i] = x[l0 - 7 + i], sh[1][i] = x[l0 - 6 + i]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, b = blockIdx.y;
-  const int l0 = blockIdx.x * FL_NT;
   const float* x = feats + (int64_t)b * feats_bstride;
   const float floor_db = utt_max ? key_to_float(utt_max[b]) - top_db : -INFINITY;
-  for (int i = tid; i < FL_NT + 32; i += FL_NT) {
-    const int l = l0 - 7 + i;
-    float v = 0.f;
-    if (l >= 0 && l < L && (int64_t)l < n_valid) {
-      v = __ldg(x + l);
-      if (norm_mean) {
-        const int f = l % F;
-        v = (fmaxf(v, floor_db) - __ldg(norm_mean + f)) / __ldg(norm_std + f);
-      }
-    }
-    const __half hv = __float2half_rn(v);
-    sh[0][i] = hv;
-    if (i > 0) sh[1][i - 1] = hv;
-  }
   const int g = lane >> 2, t4 = lane & 3;
   uint32_t bw[4][2];       // B fragments: channel 8*nt + g, taps (2*t4, 2*t4+1) and (2*t4+8, 2*t4+9)
   float bz[4][2];          // bias/2 of channels 8*nt + 2*t4, +1 (accumulator columns)
@@ -452,9 +441,28 @@ first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, i
     bz[nt][0] = kh * __ldg(bias + 8 * nt + 2 * t4);
     bz[nt][1] = kh * __ldg(bias + 8 * nt + 2 * t4 + 1);
   }
-  __syncthreads();
   __half* ob = out + (int64_t)b * out_bstride;
   const int64_t plane_rows = L >> 1;
+#pragma unroll 1
+  for (int ck = 0; ck < FL_CHUNKS; ++ck) {
+  const int l0 = (blockIdx.x * FL_CHUNKS + ck) * FL_NT;
+  if (l0 >= L) break;
+  __half (*sh)[FL_NT + 32] = shbuf[ck & 1];
+  for (int i = tid; i < FL_NT + 32; i += FL_NT) {
+    const int l = l0 - 7 + i;
+    float v = 0.f;
+    if (l >= 0 && l < L && (int64_t)l < n_valid) {
+      v = __ldg(x + l);
+      if (norm_mean) {
+        const int f = l % F;
+        v = (fmaxf(v, floor_db) - __ldg(norm_mean + f)) / __ldg(norm_std + f);
+      }
+    }
+    const __half hv = __float2half_rn(v);
+    sh[0][i] = hv;
+    if (i > 0) sh[1][i - 1] = hv;
+  }
+  __syncthreads();
 #pragma unroll
   for (int mt = 0; mt < 2; ++mt) {
     const int base = warp * 32 + mt * 16;              // first row of this 16-row tile inside the block
@@ -486,6 +494,7 @@ first_layer_mma_kernel(const float* __restrict__ feats, int64_t feats_bstride, i
       }
     }
   }
+  }   // chunk
 }
 
 // ------------------------------------------------------------------ reshape + StatisticsPooling
@@ -970,7 +979,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
       const int32_t* um = utt_max ? utt_max + b0 : nullptr;
       if (c.tc)
-        first_layer_mma_kernel<true><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um,
+        first_layer_mma_kernel<true><<<dim3((unsigned)ceil_div(L, FL_NT * FL_CHUNKS), (unsigned)nb), FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std, um,
                                                          top_db, w->enc_w[0], w->enc_b[0], (__half*)X[0], L * 32);
       else
         first_layer_kernel<float, false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F,
@@ -1106,7 +1115,7 @@ extern "C" int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWei
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
       const int32_t* um = utt_max ? utt_max + b0 : nullptr;
       if (c.tc) {
-        first_layer_mma_kernel<false><<<grid, FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std,
+        first_layer_mma_kernel<false><<<dim3((unsigned)ceil_div(L, FL_NT * FL_CHUNKS), (unsigned)nb), FL_NT, 0, c.st>>>(src, fstride, T_valid * F, (int)L, (int)F, norm_mean, norm_std,
                                                                 um, top_db, w->conv_w[0], w->conv_b[0], (__half*)X[0], L * 32);
         SPANON_TRY(check_launch("first_layer_kernel"));
         dim3 sg((unsigned)ceil_div(L2, ST_NT * ST_ROWS), 8u, (unsigned)nb);    // pair-folded: 8 planes of L/2 rows
