@@ -8,13 +8,14 @@
 //   Filterbank.forward :548    spectrogram @ fbank_matrix
 //   _amplitude_to_DB :701-710  10*log10(clamp(x, amin)) - offset, max(., amax - top_db)
 //
-// Kernel design (fbank400_kernel): one CTA = 16 consecutive frames of one utterance.
-//   * the 2800 PCM samples the 16 frames cover are loaded once with 128-bit coalesced
+// Kernel design (fbank400_kernel): one CTA = 8 consecutive frames of one utterance (36 KB of shared memory, six
+// CTAs per SM; 16 frames per CTA = 67 KB left three CTAs per SM and the issue slots half empty: 117 -> 104 us).
+//   * the 1520 PCM samples the 8 frames cover are loaded once with 128-bit coalesced
 //     loads (each sample is used by 2.5 frames);
 //   * two real frames are packed into one complex 400-point FFT (frame t -> real part,
-//     frame t+1 -> imaginary part) and separated afterwards, so the CTA runs 8 complex
+//     frame t+1 -> imaginary part) and separated afterwards, so the CTA runs 4 complex
 //     FFTs; the FFT is a Stockham autosort radix 4,4,5,5 in shared memory with a
-//     twiddle table evaluated in fp64 on first use;
+//     twiddle table evaluated per CTA (fp32 sincospif);
 //   * power, mel (only the <= 13 non-zero taps of each filter) and log run from shared
 //     memory; the only HBM traffic is 4 B/sample in and 4 B/mel-bin out.
 #include "common.cuh"
@@ -27,9 +28,9 @@ namespace {
 
 constexpr int N_FFT = 400;
 constexpr int HOP = 160;
-constexpr int FRAMES_PER_CTA = 16;
+constexpr int FRAMES_PER_CTA = 8;
 constexpr int PAIRS = FRAMES_PER_CTA / 2;
-constexpr int SEG = (FRAMES_PER_CTA - 1) * HOP + N_FFT;  // 2800 samples
+constexpr int SEG = (FRAMES_PER_CTA - 1) * HOP + N_FFT;  // 1520 samples
 constexpr int NT = 256;
 constexpr int N_BINS = N_FFT / 2 + 1;  // 201
 constexpr int P_STRIDE = 204;          // padded row of the power buffer
