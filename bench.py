@@ -377,18 +377,31 @@ def run_ours(a):
         fl = convae_layer_flops(Tp * 80)
         conv_ms = sum(v["ms_per_step"] for k, v in kern.items() if k in fl)
         conv_launches = sum(v["launches_per_step"] for k, v in kern.items() if k in fl)
-        flops_step = sum(fl.values()) * B
+        # algorithmic flops of the launches that RAN (a fused launch is listed at the sum of the reference layers it
+        # replaces, so the layers it replaced must not be counted again)
+        flops_step = sum(fl[k] for k in kern if k in fl) * B
+        if Tp * 80 == 80640:     # 22.28 GFLOP per 10 s utterance
+            assert abs(flops_step / B - FLOP_CONVAE_UTT) < 2e7, flops_step / B
         achieved = flops_step / (conv_ms * 1e-3) / 1e12
         peak = pk["tf_sust"]
         traffic, tsrc = None, None       # DRAM bytes per launch from the committed ncu --set full capture (batch 60)
-        tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
-        if os.path.exists(tp):
+        tp = next((q for q in (os.path.join(ROOT, "profiles", n) for n in ("r02_traffic.json", "r01_traffic.json"))
+                   if os.path.exists(q)), None)
+        if tp:
             tj = json.load(open(tp))
             traffic = tj["conv_stack"]["traffic_mb_per_launch"] * 1e6 * B / 60.0
-            tsrc = "profiles/r01_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, avg over the %d conv launches of a step)" % tj["conv_stack"].get("launches_captured", 0)
+            tsrc = "profiles/" + os.path.basename(tp) + " (ncu dram__bytes_read.sum + dram__bytes_write.sum, avg over the %d conv launches of a step)" % tj["conv_stack"].get("launches_captured", 0)
         ms_launch = conv_ms / max(conv_launches, 1)
+        # whole driver-timed step against the same peak (Fbank, pooling, classifier head and launch gaps included)
+        step_tf = flops_step / (ms_step * 1e-3) / 1e12
+        # algorithmic minimum bytes of the fused path = PCM in + padded features out (+ log-probs)
+        alg_bytes_step = B * (N_SAMPLES * 4 + Tp * 80 * 4 + 8)
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "step_achieved": step_tf, "step_frac": step_tf / peak, "step_frac_of_burst": step_tf / pk["tf_burst"],
+                "algorithmic_flops_per_step": flops_step, "algorithmic_bytes_per_step": alg_bytes_step,
                 "traffic": traffic, "traffic_source": tsrc, "kernel": "conv stack (first_layer + tap-GEMM launches)",
+                "traffic_per_step": None if traffic is None else traffic * conv_launches,
+                "traffic_over_algorithmic_bytes": None if traffic is None else traffic * conv_launches / alg_bytes_step,
                 "flops_per_launch": flops_step / max(conv_launches, 1), "ms_per_launch": ms_launch,
                 "share_of_step": conv_ms / prof_ms, "peak_source": pk["src"] + " bf16 sustained",
                 # the fp16 planes of a 60-utterance chunk do not fit L2, so every launch also streams them through HBM
@@ -412,8 +425,8 @@ def run_ours(a):
     extras = None
     if rank == 0 and world == 1 and a.workload == "convae" and not a.no_extras:
         extras = time_extras(sab, _lib, recipe, dev, B, T)
-        if a.workload == "convae":
-            extras["library_gpu_convae_fwd"] = time_library_gpu(recipe, dev, B, T)
+        extras["library_gpu_convae_fwd"] = time_library_gpu(recipe, dev, B, T)
+        extras.update(time_config_lines(sab, _lib, recipe, dev, dev_pool, pk))
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -474,6 +487,76 @@ def time_extras(sab, _lib, recipe, dev, B, T, iters=6):
     gemm_ms = sum(v for k, v in g["kernels_ms"].items() if k.startswith("xv_gemm"))
     g["tdnn_gflop_per_utt"] = 2 * macs / 1e9
     g["tdnn_tflops"] = 2 * macs * B / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    return out
+
+
+def _time_fn(fn, iters, warm=2):
+    with torch.no_grad():
+        for i in range(warm):
+            fn(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            fn(warm + i)
+        e1.record()
+        torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def time_config_lines(sab, _lib, recipe, dev, dev_pool, pk):
+    """The other lines SURVEY 8(d) / BASELINE.json name, device-resident, under `extras` (not part of `value`):
+    the fp32 parity mode of the headline path, configs[1] (Fbank + FullyConnected, batch 64) and configs[2]
+    (Fbank + ConvAutoencoder on 256 x 10 s, anonymized features classified by the external x-vector model)."""
+    out = {}
+    n_pool = dev_pool.shape[0]
+    # -- fp32 parity mode (<= 1e-4): CUDA-core FMA convolutions, reported separately, never against the bf16 peak
+    B = 60
+    p32 = build_pipeline("convae", "fp32", dev)
+    ms = _time_fn(lambda i: p32(dev_pool[(i * B) % (n_pool - B + 1):(i * B) % (n_pool - B + 1) + B]), 3, warm=1)
+    out["convae_fp32_parity_mode"] = {"ms_per_step": ms, "batch": B, "audio_s_per_s": B * UTT_SECONDS / (ms * 1e-3),
+                                      "dtype": "fp32", "tflops_fp32": FLOP_CONVAE_UTT * B / (ms * 1e-3) / 1e12,
+                                      "what": "Fbank + ConvAutoencoder forward, fp32 activations and CUDA-core FMA "
+                                              "(the <= 1e-4 parity mode); device-resident PCM pool"}
+    del p32
+    # -- configs[1]: FullyConnected anonymizer over Fbank features, batch 64 x 10 s (HBM-bound: 960 320 B per utterance)
+    B = 64
+    pfc = build_pipeline("fcae", "fp32", dev)
+    nb = n_pool // B
+    _lib.lib()
+    ms = _time_fn(lambda i: pfc(dev_pool[(i % nb) * B:(i % nb + 1) * B]), 20, warm=3)
+    _lib.profile_begin(dev)
+    with torch.no_grad():
+        pfc(dev_pool[:B])
+    prof = _lib.profile_end()
+    gbs = BYTES_FBANK_UTT * B / (ms * 1e-3) / 1e9
+    out["config1_fbank_fcae_b64"] = {"ms_per_step": ms, "batch": B, "audio_s_per_s": B * UTT_SECONDS / (ms * 1e-3),
+                                     "dtype": "fp32", "algorithmic_GB/s": gbs, "frac_hbm": gbs / pk["hbm"],
+                                     "kernels_ms": {k: v[1] for k, v in prof.items()}}
+    del pfc
+    # -- configs[2]: ConvAutoencoder + external gender-classifier evaluation on 256 x 10 s utterances
+    B = 256
+    if n_pool >= B:
+        pca = build_pipeline("convae", "fp16", dev)
+        xv = sab.XvectorClassifier()
+        for m, shapes in ((xv.embedding_model, recipe.XVECTOR_EMB_SHAPES), (xv.classifier, recipe.XVECTOR_CLF_SHAPES)):
+            m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in recipe.make_weights(shapes, 1230).items()})
+        xv = xv.to(dev).eval()
+        T = 1 + N_SAMPLES // 160
+        noise = torch.from_numpy(recipe.make_noise(5, B, 128)).to(dev)
+        xnoise = torch.from_numpy(recipe.make_noise(6, B, 1500)).to(dev)
+
+        def cfg2(i):
+            o = (i * 52) % (n_pool - B + 1)
+            rec, logp = pca(dev_pool[o:o + B], pool_noise=noise)
+            return xv.classify_batch_feats(rec[:, :T], pool_noise=xnoise)
+        ms = _time_fn(cfg2, 4, warm=2)
+        out["config2_convae_xvector_b256"] = {"ms_per_step": ms, "batch": B, "audio_s_per_s": B * UTT_SECONDS / (ms * 1e-3),
+                                              "dtype": "fp16",
+                                              "what": "Fbank -> ConvAutoencoder (recon + sex log-probs) -> x-vector "
+                                                      "classify_batch_feats on the anonymized features, 256 x 10 s"}
+        del pca, xv
+    torch.cuda.empty_cache()
     return out
 
 

@@ -102,6 +102,26 @@ template <> __device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(f
 
 template <> __device__ __forceinline__ __half from_float<__half>(float v) { return __float2half_rn(v); }
 
+// Per-device one-time setup (cudaFuncSetAttribute is a per-device setting, and one process may drive several GPUs):
+// returns true the first time it is called with `mask` while device `dev` is current.  Thread-safe.
+inline bool first_use_on_device(std::atomic<unsigned long long>& mask, int dev) {
+  const unsigned long long bit = 1ull << (dev & 63);
+  return (mask.fetch_or(bit, std::memory_order_acq_rel) & bit) == 0;
+}
+// Multiprocessor count of the CURRENT device (cached per device).
+inline int current_device_sms(int* dev_out = nullptr) {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (dev_out) *dev_out = dev;
+  int n = cache[dev & 63].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    cache[dev & 63].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
+
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

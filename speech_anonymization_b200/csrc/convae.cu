@@ -951,7 +951,10 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_TRY(pack_layer(c, L_DEC5, w->dec_w[3]));
   }
   SPANON_TRY(pack_layer(c, L_DEC8, w->dec_w[4]));
-  if (run_clf) {
+  // The classifier's constants are packed whenever its parameters are given, whether or not THIS call runs it: a later
+  // call with weights_prepared = 1 may ask for the log-probabilities (a pipe slot first used with logp_host == NULL).
+  if (run_clf || (w->tdnn_w[0] && w->tdnn_w[1] && w->tdnn_w[2] && w->clf_norm.weight && w->tdnn_bn[0].weight &&
+                  w->tdnn_bn[1].weight && w->tdnn_bn[2].weight)) {
     SPANON_TRY(pack_layer(c, L_TD0, w->tdnn_w[0]));
     SPANON_TRY(pack_layer(c, L_TD3, w->tdnn_w[1]));
     SPANON_TRY(pack_layer(c, L_TD6, w->tdnn_w[2]));

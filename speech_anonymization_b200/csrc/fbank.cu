@@ -340,12 +340,12 @@ int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride
   const int64_t T = 1 + n_samples / cfg->hop_length;
   SPANON_TRY(fill_i32(utt_max, B, INT32_MIN, st));
   if (cfg->n_fft == N_FFT && cfg->win_length == N_FFT && cfg->hop_length == HOP) {
-    static bool attr_done = false;
-    if (!attr_done) {
+    static std::atomic<unsigned long long> attr_done{0};   // per device: the attribute belongs to the device's context
+    int dev = 0;
+    SPANON_CUDA_TRY(cudaGetDevice(&dev));
+    if (first_use_on_device(attr_done, dev))
       SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(FbankSmem)));
-      attr_done = true;
-    }
     dim3 grid((unsigned)ceil_div(T, FRAMES_PER_CTA), (unsigned)B);
     fbank400_kernel<TS><<<grid, NT, sizeof(FbankSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
     return check_launch("fbank400_kernel");

@@ -258,16 +258,13 @@ extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
   if (run_clf && (!workspace || workspace_bytes < spanon_fcae_workspace_bytes(B, T))) return SPANON_ERR_WORKSPACE;
   if (run_clf && (reinterpret_cast<uintptr_t>(workspace) & 7)) return SPANON_ERR_MISALIGNED;
   cudaStream_t st = as_stream(stream);
-  static bool attr_done = false;
-  static int n_sm = 148;
-  if (!attr_done) {
+  static std::atomic<unsigned long long> attr_done{0};     // per device (one process may drive several GPUs)
+  int dev = 0;
+  const int n_sm = current_device_sms(&dev);
+  if (n_sm <= 0) return SPANON_ERR_CUDA;
+  if (first_use_on_device(attr_done, dev))
     SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sizeof(FcSmem)));
-    int dev = 0;
-    SPANON_CUDA_TRY(cudaGetDevice(&dev));
-    SPANON_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    attr_done = true;
-  }
   double* pool = reinterpret_cast<double*>(workspace);
   if (run_clf) SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
   const int64_t n_frames = B * T;

@@ -425,10 +425,12 @@ extern "C" int spanon_xvector_classify(const float* feats, const float* rel_len,
     xv_input_kernel<<<grid, 256, 0, st>>>(feats, ws.in, (int)T, Rp, (int)F);
     SPANON_TRY(check_launch("xv_input_kernel"));
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    SPANON_CUDA_TRY(cudaFuncSetAttribute(xv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XV_SMEM_LIMIT));
-    attr_done = true;
+  {
+    static std::atomic<unsigned long long> attr_done{0};   // per device (one process may drive several GPUs)
+    int dev = 0;
+    SPANON_CUDA_TRY(cudaGetDevice(&dev));
+    if (first_use_on_device(attr_done, dev))
+      SPANON_CUDA_TRY(cudaFuncSetAttribute(xv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XV_SMEM_LIMIT));
   }
   const __half* cur = ws.in;
   for (int l = 0; l < XV_NL; ++l) {

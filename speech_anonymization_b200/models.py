@@ -275,6 +275,11 @@ class ConvReconstruction(nn.Module):
             w.in_w[i], w.in_b[i] = _p(e[k].weight), _p(e[k].bias)
         return w
 
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d.pop("_ws_cache", None)
+        return d
+
     def opts(self):
         return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16, int(self.chunk_utts), 1, 0)
 
@@ -299,7 +304,16 @@ class ConvReconstruction(nn.Module):
             opts = self.opts()
             L = _lib.lib()
             ws_bytes = L.spanon_convrecon_workspace_bytes(B, T, F, C.byref(opts))
-            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+            # workspace (and the packed weights in it) kept between calls, as in ConvAutoencoder.forward
+            key = (B, T, F, opts.precision, opts.chunk_utts, str(dev),
+                   tuple((t.data_ptr(), t._version) for t in self.encoder.parameters()))
+            cache = self.__dict__.get("_ws_cache")
+            if cache is None or cache[0].numel() != ws_bytes or cache[0].device != dev:
+                cache = [torch.empty((ws_bytes,), dtype=torch.uint8, device=dev), None]
+                self.__dict__["_ws_cache"] = cache
+            ws = cache[0]
+            opts.weights_prepared = 1 if cache[1] == key else 0
+            cache[1] = key
             if fused_norm is None:
                 mean = std = umax = None
                 top_db, t_valid = 0.0, T
@@ -348,13 +362,16 @@ class Xvector(nn.Module):
     `blocks.{2,5,8,11,14}.norm.*`, `blocks.16.w.*`).  Computed inside XvectorClassifier."""
 
     def __init__(self, device="cpu", activation=nn.LeakyReLU, tdnn_blocks=5, tdnn_channels=[512, 512, 512, 512, 1500],
-                 tdnn_kernel_sizes=[5, 3, 3, 1, 1], tdnn_dilations=[1, 2, 3, 1, 1], lin_neurons=128, in_channels=80):
+                 tdnn_kernel_sizes=[5, 3, 3, 1, 1], tdnn_dilations=[1, 2, 3, 1, 1], lin_neurons=512, in_channels=40):
+        # (defaults = the reference's, Xvector.py:45-56, so a default-constructed module holds a default-constructed
+        # reference checkpoint; evaluator_inference.yaml:34-41 passes in_channels=80, lin_neurons=128, which is what the
+        # CUDA path computes -- XvectorClassifier checks that when it runs)
         super().__init__()
         if (activation is not nn.LeakyReLU or tdnn_blocks != 5 or list(tdnn_channels) != [512, 512, 512, 512, 1500]
-                or list(tdnn_kernel_sizes) != [5, 3, 3, 1, 1] or list(tdnn_dilations) != [1, 2, 3, 1, 1]
-                or lin_neurons != 128 or in_channels != 80):
-            raise NotImplementedError("the CUDA x-vector path is built for evaluator_inference.yaml's architecture "
-                                      "(80 -> 512,512,512,512,1500; k 5,3,3,1,1; dilation 1,2,3,1,1; LeakyReLU; 128-d)")
+                or list(tdnn_kernel_sizes) != [5, 3, 3, 1, 1] or list(tdnn_dilations) != [1, 2, 3, 1, 1]):
+            raise NotImplementedError("the CUDA x-vector path is built for evaluator_inference.yaml's TDNN "
+                                      "(512,512,512,512,1500; k 5,3,3,1,1; dilation 1,2,3,1,1; LeakyReLU)")
+        self.lin_neurons, self.in_channels = lin_neurons, in_channels
         self.blocks = nn.ModuleList()
         cin = in_channels
         for c, k, d in zip(tdnn_channels, tdnn_kernel_sizes, tdnn_dilations):
@@ -408,7 +425,8 @@ class XvectorClassifier(nn.Module):
 
     def __init__(self, embedding_model=None, classifier=None):
         super().__init__()
-        self.embedding_model = embedding_model if embedding_model is not None else Xvector()
+        self.embedding_model = (embedding_model if embedding_model is not None
+                                else Xvector(in_channels=80, lin_neurons=128))   # evaluator_inference.yaml:34-41
         self.classifier = classifier if classifier is not None else XvectorHead()
 
     def weight_struct(self):
@@ -434,6 +452,9 @@ class XvectorClassifier(nn.Module):
         _forward_only_guard(self, feats)
         if feats.dim() != 3 or feats.shape[2] != 80:
             raise ValueError("XvectorClassifier expects [batch, time, 80] features")
+        if self.embedding_model.lin_neurons != 128 or self.embedding_model.in_channels != 80:
+            raise NotImplementedError("the CUDA x-vector path computes evaluator_inference.yaml's model "
+                                      "(in_channels=80, lin_neurons=128)")
         x = feats.contiguous()
         B, T, F = x.shape
         dev = x.device

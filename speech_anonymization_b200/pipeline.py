@@ -109,11 +109,24 @@ class GraphedStep:
     `recon`, `logp` are the static output tensors every replay() overwrites."""
 
     def __init__(self, pipeline, wavs, wav_lens=None, pool_noise=None, warmup=2):
-        self.wavs = wavs
+        self.pipeline, self.wavs, self.wav_lens, self.pool_noise, self.warmup = pipeline, wavs, wav_lens, pool_noise, warmup
+        self._capture()
+
+    def _weights_key(self):
+        m = self.pipeline.model
+        return tuple((t.data_ptr(), t._version) for t in list(m.parameters()) + list(m.buffers()))
+
+    def _capture(self):
+        pipeline, wavs, wav_lens, pool_noise = self.pipeline, self.wavs, self.wav_lens, self.pool_noise
+        # The graph bakes in raw pointers into the model's workspace (packed weights included): give the captured step a
+        # PRIVATE workspace that this object keeps alive, so a later eager call with another shape cannot free or
+        # repurpose the memory the graph replays into.
+        model = pipeline.model
+        saved = model.__dict__.pop("_ws_cache", None)
         side = torch.cuda.Stream(device=wavs.device)
         side.wait_stream(torch.cuda.current_stream(wavs.device))
         with torch.cuda.stream(side):
-            for _ in range(warmup):      # first calls pack weights / set kernel attributes: keep them out of the graph
+            for _ in range(self.warmup):   # first calls pack weights / set kernel attributes: keep them out of the graph
                 pipeline(wavs, wav_lens, pool_noise=pool_noise)
         torch.cuda.current_stream(wavs.device).wait_stream(side)
         torch.cuda.synchronize(wavs.device)
@@ -122,10 +135,22 @@ class GraphedStep:
         with torch.cuda.graph(self.graph):
             self.recon, self.logp = pipeline(wavs, wav_lens, pool_noise=pool_noise)
         self.launches = int(_lib.lib().spanon_launch_count() - self.launches_before)   # kernels per replay
+        self._ws = model.__dict__.pop("_ws_cache", None)     # owned by this graph from here on
+        if saved is not None:
+            model.__dict__["_ws_cache"] = saved
+        self._key = self._weights_key()
 
-    def replay(self):
+    def replay(self, check_weights=True):
+        """Replays the captured step.  The graph holds the weights as packed at capture time; with `check_weights` a
+        changed parameter (load_state_dict, optimizer step, any versioned in-place write) triggers a re-capture.
+        Writes through `.data` do not bump the version counter -- call recapture() after those."""
+        if check_weights and self._key != self._weights_key():
+            self._capture()
         self.graph.replay()
         return self.recon, self.logp
+
+    def recapture(self):
+        self._capture()
 
 
 class StreamPipe:
@@ -164,6 +189,15 @@ class StreamPipe:
 
     def wait(self):
         _lib.check(_lib.lib().spanon_pipe_wait(self._h), "pipe_wait")
+
+    def weights_changed(self, model=None):
+        """Call after the model's parameters changed (or pass a new model): drains the pipe and makes every slot re-pack
+        its weights (and re-capture its graph) on next use.  The pipe otherwise keeps using the packed copies."""
+        w = None
+        if model is not None:
+            self._w = model.weight_struct()
+            w = C.cast(C.byref(self._w), C.c_void_p)
+        _lib.check(_lib.lib().spanon_pipe_weights_changed(self._h, w), "pipe_weights_changed")
 
     def drain(self):
         _lib.check(_lib.lib().spanon_pipe_drain(self._h), "pipe_drain")

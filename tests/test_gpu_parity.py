@@ -186,7 +186,7 @@ def test_convae_vs_golden(golden, precision, tol):
             rec, logp = m(x, pool_noise=cu(recipe.make_noise(seed, B, 128)))
         assert rec.shape == (B, T, 80) and logp.shape == (B, 2)
         assert rel_max(rec.cpu().numpy(), golden[name + "_recon"]) < tol
-        assert np.max(np.abs(logp.cpu().numpy() - golden[name + "_logp"])) < (1e-4 if precision == "fp32" else 2e-2)
+        assert np.max(np.abs(logp.cpu().numpy() - golden[name + "_logp"])) < (1e-4 if precision == "fp32" else 2e-3)
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("fp16", 1e-2)])
@@ -203,7 +203,7 @@ def test_convae_vs_oracle_10s(precision, tol):
     with torch.no_grad():
         r_ref, l_ref = anonymizer_ref.convae_forward(x, w, noise)
     assert rel_max(rec.cpu().numpy(), r_ref.numpy()) < tol
-    assert np.max(np.abs(logp.cpu().numpy() - l_ref.numpy())) < (1e-4 if precision == "fp32" else 2e-2)
+    assert np.max(np.abs(logp.cpu().numpy() - l_ref.numpy())) < (1e-4 if precision == "fp32" else 2e-3)
 
 
 def test_convae_composed_decoder_edges():
