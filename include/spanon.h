@@ -39,7 +39,8 @@ typedef enum SpanonStatus {
   SPANON_ERR_WORKSPACE = -4,     /* workspace smaller than *_workspace_bytes()    */
   SPANON_ERR_UNSUPPORTED = -5,   /* configuration outside what the kernels cover  */
   SPANON_ERR_CUDA = -6,          /* a CUDA runtime call / kernel launch failed    */
-  SPANON_ERR_ARCH = -7           /* device is not sm_100                          */
+  SPANON_ERR_ARCH = -7,          /* device is not sm_100                          */
+  SPANON_ERR_STATIC_LIMIT = -8   /* size beyond the built-in scratch of a *_static entry point */
 } SpanonStatus;
 
 SPANON_API const char* spanon_strerror(int status);
@@ -156,6 +157,21 @@ SPANON_API int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
                     const float* norm_mean, const float* norm_std, const int32_t* utt_max,
                     float top_db, float* recon, float* logp, void* workspace,
                     size_t workspace_bytes, int64_t B, int64_t T, void* stream);
+
+/* spanon_fcae_fwd for callers that must not allocate and have no workspace to pass (code under CUDA-graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as spanon_fcae_fwd minus the workspace: the pooling accumulators
+ * ([B][40][2] fp64, this path's only scratch) live in a file-scope `static __device__` array inside the library,
+ * sized for SPANON_FCAE_STATIC_MAX_B utterances (160 KB, held by every GPU that loads the library until exit).
+ * B > SPANON_FCAE_STATIC_MAX_B returns SPANON_ERR_STATIC_LIMIT.  The call path contains no cudaMalloc / cudaFree /
+ * allocating library routine.  All calls on one device share the array (it is cleared on `stream` before use):
+ * calls that OVERLAP on the same GPU (different streams, or threads) race on it -- serialise them, or use
+ * spanon_fcae_fwd with one workspace per stream. */
+#define SPANON_FCAE_STATIC_MAX_B 256
+SPANON_API int64_t spanon_fcae_static_max_batch(void);
+SPANON_API int spanon_fcae_fwd_static(const float* feats, const SpanonFcaeWeights* w, const float* pool_noise,
+                           const float* norm_mean, const float* norm_std, const int32_t* utt_max,
+                           float top_db, float* recon, float* logp, int64_t B, int64_t T, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * ConvAutoencoder forward (eval-mode BatchNorm in the TDNN sex classifier)

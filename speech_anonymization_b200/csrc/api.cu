@@ -84,6 +84,7 @@ extern "C" const char* spanon_strerror(int status) {
     case SPANON_ERR_UNSUPPORTED: return "configuration not supported by the sm_100a kernels";
     case SPANON_ERR_CUDA: return "CUDA runtime error (see spanon_last_cuda_error)";
     case SPANON_ERR_ARCH: return "device is not sm_100";
+    case SPANON_ERR_STATIC_LIMIT: return "size exceeds the built-in static scratch of this *_static entry point (use the workspace form)";
     default: return "unknown status";
   }
 }

@@ -279,3 +279,72 @@ extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
   }
   return SPANON_OK;
 }
+
+
+// ====================================================================================================================
+// spanon_fcae_fwd_static -- the same forward with NO allocation anywhere on the call path (include/spanon.h).
+// The pooling accumulators ([B][40][2] fp64, the only scratch memory of this path) live in a file-scope device array
+// of a fixed, modest size instead of a caller-provided workspace.  Every GPU that loads the library holds the array
+// until the process exits; all calls on one device share it (it keeps the last call's contents, so it is cleared on
+// the stream before the kernel runs), hence two calls that overlap on one GPU race on it.
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: the address is taken once per
+// device with cudaGetSymbolAddress while that device is current, and that pointer is what the kernels receive.
+static __device__ __align__(256) double g_fcae_static_pool[(size_t)SPANON_FCAE_STATIC_MAX_B * 40 * 2];   // 160 KB
+
+namespace spanon {
+namespace {
+std::atomic<double*> g_fcae_static_ptr[64];     // per device: address of g_fcae_static_pool on that device
+std::atomic<unsigned long long> g_fcae_static_attr{0};
+
+// launch bookkeeping without the profiler hook (check_launch() may create an event when a profile is being recorded)
+inline int check_launch_static(const char* what) {
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_last_cuda_error(what, e); return SPANON_ERR_CUDA; }
+  return SPANON_OK;
+}
+}  // namespace
+}  // namespace spanon
+
+extern "C" int64_t spanon_fcae_static_max_batch(void) { return SPANON_FCAE_STATIC_MAX_B; }
+
+extern "C" int spanon_fcae_fwd_static(const float* feats, const SpanonFcaeWeights* w, const float* pool_noise,
+                                      const float* norm_mean, const float* norm_std, const int32_t* utt_max,
+                                      float top_db, float* recon, float* logp, int64_t B, int64_t T, void* stream) {
+  if (!w) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || T < 0) return SPANON_ERR_BAD_SHAPE;
+  if (B > SPANON_FCAE_STATIC_MAX_B) return SPANON_ERR_STATIC_LIMIT;     // beyond the built-in scratch array
+  if (w->in_dim != D_IN) return SPANON_ERR_UNSUPPORTED;
+  if (B == 0 || T == 0) return SPANON_OK;
+  if (!feats || !recon) return SPANON_ERR_NULL_POINTER;
+  if ((norm_mean == nullptr) != (norm_std == nullptr)) return SPANON_ERR_NULL_POINTER;
+  const int run_clf = logp != nullptr;
+  cudaStream_t st = as_stream(stream);
+  int dev = 0;
+  const int n_sm = current_device_sms(&dev);
+  if (n_sm <= 0 || dev < 0 || dev >= 64) return SPANON_ERR_CUDA;
+  // set-up, once per device, with that device current
+  double* pool = g_fcae_static_ptr[dev].load(std::memory_order_acquire);
+  if (!pool) {
+    void* sym = nullptr;
+    SPANON_CUDA_TRY(cudaGetSymbolAddress(&sym, g_fcae_static_pool));
+    if (!sym) return SPANON_ERR_CUDA;
+    pool = static_cast<double*>(sym);
+    g_fcae_static_ptr[dev].store(pool, std::memory_order_release);
+  }
+  if (first_use_on_device(g_fcae_static_attr, dev))
+    SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FcSmem)));
+  // the array holds whatever the previous call left: the accumulators of this batch must start at zero
+  if (run_clf) SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
+  const int64_t n_frames = B * T;
+  const int64_t n_tiles = ceil_div(n_frames, NTHR);
+  const unsigned grid = (unsigned)std::min<int64_t>(n_tiles, n_sm);
+  fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                  n_frames, (int)T, run_clf);
+  SPANON_TRY(check_launch_static("fcae_kernel"));
+  if (run_clf) {
+    fcae_head_kernel<<<(unsigned)B, 64, 0, st>>>(pool, pool_noise, *w, (int)T, logp);
+    SPANON_TRY(check_launch_static("fcae_head_kernel"));
+  }
+  return SPANON_OK;
+}
