@@ -170,7 +170,9 @@ class ClockSampler(threading.Thread):
 # per-utterance algorithmic flops of each conv launch (SURVEY.md 8a / DESIGN.md "Kernels"), L = 80640
 def convae_layer_flops(L=80640):
     mac = {"first_layer_kernel": L * 15 * 32,
-           "tapgemm:enc2": (L // 2) * 32 * 5 * 64, "tapgemm:enc5": (L // 2) * 64 * 5 * 64,
+           "tapgemm:enc2": (L // 2) * 32 * 5 * 64,
+           # encoder.0 generated inside encoder.2's launch: counted at the flops of the two reference layers
+           "tapgemm:enc02": L * 15 * 32 + (L // 2) * 32 * 5 * 64, "tapgemm:enc5": (L // 2) * 64 * 5 * 64,
            "tapgemm:enc8": (L // 4) * 64 * 5 * 128, "tapgemm:enc11": (L // 4) * 128 * 5 * 128,
            "tapgemm:tdnn0": (L // 4 - 4) * 128 * 5 * 128, "tapgemm:tdnn3": (L // 4 - 8) * 128 * 3 * 128,
            "tapgemm:tdnn6": (L // 4 - 14) * 128 * 3 * 128,

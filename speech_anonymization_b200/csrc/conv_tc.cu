@@ -62,7 +62,10 @@ constexpr int TC_EPI_THREADS = 128;       // Toeplitz epilogue (always four warp
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
 constexpr int TC_MAX_STAGES = 16;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
-enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8 };
+enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16 };
+constexpr int TC_GEN_SIG = 320;           // fp16 samples of one tile's signal window (XF_GEN)
+constexpr int TC_GEN_SLOTS = 4;           // signal windows in flight (filled by the loader warps, read by the transform warps)
+constexpr int TC_GEN_MAXF = 128;          // mel bins the per-warp (mean, 1/std) table holds
 __host__ __device__ constexpr int tc_epi_warps(int xf) { return (xf & XF_STATS) ? 8 : 4; }
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
@@ -80,13 +83,13 @@ __device__ __forceinline__ __half2 silu_from_half(__half2 hh) {
 }
 
 struct TcLayout {        // byte offsets inside dynamic shared memory
-  uint32_t w, a, epi, red, bars, total;
+  uint32_t w, a, epi, red, sig, bars, total;
   uint32_t w_bytes, stage_bytes, lbo_a;
   int n_stages, slab;
 };
 
 constexpr int TC_ST_PITCH = 17;              // fp32 row pitch of the statistics transpose buffer ([32 rows][16 columns] per warp)
-__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, bool stats) {
+__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, bool stats, bool gen = false) {
   TcLayout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;              // == 1 (mod 8): chunks start 16 B apart modulo 128 B
   L.lbo_a = (uint32_t)L.slab * 16u;
@@ -96,7 +99,10 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
   L.red = L.epi + 3u * cout_v * 4u;                   // Toeplitz epilogue: 2 x [128][17] fp32 copies of the tile;
                                                       // statistics: one [32][17] fp32 transpose buffer per epilogue warp
-  L.bars = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : stats ? 8u * 32u * TC_ST_PITCH * 4u : 0u);
+  L.sig = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : stats ? 8u * 32u * TC_ST_PITCH * 4u : 0u);
+  // XF_GEN: ring of TC_GEN_SLOTS signal windows (two fp16 copies each, the second shifted by one sample) + one
+  // (mean, 1/std) table per loader warp
+  L.bars = L.sig + (gen ? (uint32_t)TC_GEN_SLOTS * 2u * TC_GEN_SIG * 2u + (uint32_t)TC_LOAD_WARPS * 2u * TC_GEN_MAXF * 4u : 0u);
   L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
@@ -110,13 +116,13 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
 
 // barrier slots (8 B each): [0,16) raw (bulk copy landed), [16,32) full (transformed), [32,48) empty (MMAs read it),
 // [48,50) tmem_full, [50,52) tmem_empty, 52 weights; 54 = TMEM base pointer
-enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54 };
+enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54, B_SFULL = 56, B_SEMPTY = 60 };
 
 template <int COUT_V, int XF>
 __global__ void __launch_bounds__(tc_threads(XF), 1)
 tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int E = tc_epi_warps(XF), TC_MMA_WARP = E + 11;
   const int wd = warp - E;                                   // role index among the non-epilogue warps
@@ -141,6 +147,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
       for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), E); }
       mbar_init(BAR(B_W), 1);
+      if constexpr ((XF & XF_GEN) != 0)
+        for (int i = 0; i < TC_GEN_SLOTS; ++i) { mbar_init(BAR(B_SFULL + i), 1); mbar_init(BAR(B_SEMPTY + i), (uint32_t)(p.cin_v / TC_STAGE_CH)); }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       // resident weights: one bulk async copy per tap slice
       mbar_expect_tx(BAR(B_W), L.w_bytes);
@@ -173,7 +181,54 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   if (is_loader) {
     // =========================== LOADER ===========================
     // two bulk copies per stage (one per 8-channel chunk), issued by one elected lane of the converged warp
-    {
+    if constexpr ((XF & XF_GEN) != 0) {
+      // XF_GEN: no plane to load.  The loader warps prepare the SIGNAL WINDOW of each tile instead (loader l: tiles
+      // k == l mod 2): the clamped / normalised / zero-padded feature samples x[2*g0 - 7 ...] as fp16, twice (the second
+      // copy shifted by one sample, so that the odd half of the pair view also reads aligned 32-bit words).
+      const int lw = wd >> 2;
+      float* tbl = reinterpret_cast<float*>(smem + L.sig + (uint32_t)TC_GEN_SLOTS * 2u * TC_GEN_SIG * 2u) + lw * 2 * TC_GEN_MAXF;
+      const int F = p.gen_F;
+      if (p.gen_mean)
+        for (int f = lane; f < F; f += 32) { tbl[f] = __ldg(p.gen_mean + f); tbl[TC_GEN_MAXF + f] = 1.0f / __ldg(p.gen_std + f); }
+      __syncwarp();
+      const int Lfull = 2 * p.rows_in;
+      const int nvalid = (int)min((int64_t)Lfull, p.gen_nvalid);
+      for (int k = lw; k < n_my_tiles; k += TC_LOAD_WARPS) {
+        const int t = t_begin + k, b = t / tiles_per_utt, tin = t - b * tiles_per_utt;
+        const int origin = 2 * (tin * tile_step - halo_lo) - 7;       // x index of window sample 0
+        const float* xb = p.gen_feats + (int64_t)b * p.gen_bstride;
+        float xv[TC_GEN_SIG / 32];
+#pragma unroll
+        for (int q = 0; q < TC_GEN_SIG / 32; ++q) {                   // all loads in flight before any use
+          const int l = origin + q * 32 + lane;
+          xv[q] = (l >= 0 && l < nvalid) ? __ldg(xb + l) : 0.f;
+        }
+        if (p.gen_mean) {
+          const float floor_db = p.gen_umax ? key_to_float(__ldg(p.gen_umax + b)) - p.gen_topdb : -INFINITY;
+          int f = (origin + lane) % F;
+          if (f < 0) f += F;
+#pragma unroll
+          for (int q = 0; q < TC_GEN_SIG / 32; ++q) {
+            const int l = origin + q * 32 + lane;
+            if (l >= 0 && l < nvalid) xv[q] = (fmaxf(xv[q], floor_db) - tbl[f]) * tbl[TC_GEN_MAXF + f];
+            f += 32;
+            if (f >= F) f -= F;
+          }
+        }
+        const int slot = k % TC_GEN_SLOTS;
+        mbar_wait(BAR(B_SEMPTY + slot), (((uint32_t)k / TC_GEN_SLOTS) & 1u) ^ 1u);
+        __half* sa = reinterpret_cast<__half*>(smem + L.sig) + slot * 2 * TC_GEN_SIG;
+#pragma unroll
+        for (int q = 0; q < TC_GEN_SIG / 32; ++q) {
+          const __half hv = __float2half_rn(xv[q]);
+          const int j = q * 32 + lane;
+          sa[j] = hv;
+          if (j > 0) sa[TC_GEN_SIG + j - 1] = hv;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(BAR(B_SFULL + slot));
+      }
+    } else {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
       const int lw = wd >> 2;
       uint32_t stage = (uint32_t)lw, ph = 0;
@@ -232,6 +287,80 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       }
     }
     int b_const = -1;                                          // utterance whose t1 constants are in registers
+    if constexpr ((XF & XF_GEN) != 0) {
+      // ---- encoder.0 fused into encoder.2's operand production (models/ConvAutoEncoder.py:141-144: Conv1d(1->32,k15,p7),
+      // GLU, then the stride-2 conv with nothing in between).  Stage s of the pair view holds e0 rows 2r + half
+      // (half = s / 2) and channels ci0 .. ci0+15 (ci0 = 16 * (s & 1)); e0[l][c] = SiLU(b[c] + sum_t w[c][t] x[l+t-7]).
+      // A warp computes its stage with warp-level MMAs over a Toeplitz view of the signal, A[i][t] = x[l0 + 2i + t - 7]:
+      // with sig[j] = x[l0 - 7 + j] every A fragment register is one aligned 32-bit word of sig (rows advance by two
+      // samples), B = w/2 and the accumulators start at b/2, so the MMA gives h = y/2 and SiLU(y) = h + h*tanh(h).
+      const int half = (s_fix * TC_STAGE_CH) / p.cin_mod, ci0 = (s_fix * TC_STAGE_CH) % p.cin_mod;
+      const int g = lane >> 2, t4 = lane & 3;
+      uint32_t bw[2][2];
+      float bz[2][2];
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        const float* wc = p.gen_w + (ci0 + 8 * nt + g) * 15;
+        const int ta = 2 * t4, tb = 2 * t4 + 8;
+        const __half2 wl = __floats2half2_rn(0.5f * __ldg(wc + ta), 0.5f * __ldg(wc + ta + 1));
+        const __half2 wh = __floats2half2_rn(0.5f * __ldg(wc + tb), tb + 1 < 15 ? 0.5f * __ldg(wc + tb + 1) : 0.f);
+        bw[nt][0] = *reinterpret_cast<const uint32_t*>(&wl);
+        bw[nt][1] = *reinterpret_cast<const uint32_t*>(&wh);
+        bz[nt][0] = 0.5f * __ldg(p.gen_b + ci0 + 8 * nt + 2 * t4);
+        bz[nt][1] = 0.5f * __ldg(p.gen_b + ci0 + 8 * nt + 2 * t4 + 1);
+      }
+      for (; k < n_my_tiles; k += kstep) {
+        const int g0 = tin * tile_step - halo_lo;
+        const int lo = g0 < 0 ? -g0 : 0;
+        const int hi = min(slab_used, p.rows_in - g0);
+        const int slot = k % TC_GEN_SLOTS;
+        // window copy `half`: sig[j] = x[2*g0 + half - 7 + j]
+        const uint32_t* sig32 = reinterpret_cast<const uint32_t*>(smem + L.sig) + (slot * 2 + half) * (TC_GEN_SIG / 2);
+        mbar_wait(BAR(B_SFULL + slot), ((uint32_t)k / TC_GEN_SLOTS) & 1u);
+        mbar_wait(BAR(B_EMPTY + stage), ph ^ 1u);              // the MMAs of this slot's previous use have read it
+        const int it = k * n_stage_tile + s_fix;
+        if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
+        unsigned char* sbase = smem + L.a + stage * L.stage_bytes;
+#pragma unroll 3
+        for (int mt = 0; mt < 9; ++mt) {                       // 9 x 16 slab rows >= slab_used (130)
+          const uint32_t a0 = sig32[g + t4 + 16 * mt], a1 = sig32[g + 8 + t4 + 16 * mt];
+          const uint32_t a2 = sig32[g + 4 + t4 + 16 * mt], a3 = sig32[g + 12 + t4 + 16 * mt];
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            float acc[4] = {bz[nt][0], bz[nt][1], bz[nt][0], bz[nt][1]};
+            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(acc[0]), "+f"(acc[1]), "+f"(acc[2]), "+f"(acc[3])
+                         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(bw[nt][0]), "r"(bw[nt][1]));
+#pragma unroll
+            for (int hr = 0; hr < 2; ++hr) {
+              const int r = 16 * mt + g + 8 * hr;
+              if (r < slab_used) {
+                const __half2 y = silu_from_half(__floats2half2_rn(acc[2 * hr], acc[2 * hr + 1]));
+                *reinterpret_cast<__half2*>(sbase + (uint32_t)nt * L.lbo_a + (uint32_t)r * 16u + 4u * t4) = y;
+              }
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(BAR(B_SEMPTY + slot));      // this warp is done with the tile's signal window
+        if (lo > 0 || hi < slab_used) {             // rows outside the utterance are the stride-2 conv's zero padding
+          unsigned char* base = sbase + (uint32_t)lane * 16u;
+          for (int r = lane; r < slab_used; r += 32)
+            if (r < lo || r >= hi) {
+              *reinterpret_cast<uint4*>(base + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+              *reinterpret_cast<uint4*>(base + L.lbo_a + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(BAR(B_FULL + stage));
+        if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
+        stage += TC_XF_WARPS;
+        if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
+        tin += kstep;
+        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
+      }
+    } else
     for (; k < n_my_tiles; k += kstep) {
       const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
@@ -510,8 +639,11 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
   const int nst = p.cin_v / TC_STAGE_CH;
   if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
   if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
+  if ((XF & XF_GEN) && (slab_used > 144 || 2 * 143 + 17 > TC_GEN_SIG || p.gen_F > TC_GEN_MAXF || p.gen_F < 32 || p.cin_mod != 32 || p.cin_v != 64 || !p.gen_feats ||
+                        !p.gen_w || !p.gen_b || (p.gen_mean == nullptr) != (p.gen_std == nullptr)))
+    return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc_kernel<COUT_V, XF>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
   const int tiles_per_utt = (int)ceil_div(p.rows_out, tile_step);
@@ -577,6 +709,10 @@ int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int act = p.silu == 1 ? XF_SILU : p.silu == 2 ? XF_RELU : XF_IDENT;
   const int xf = act | (p.t2_scale ? XF_T2 : 0) | (p.stats ? XF_STATS : 0);
   if (act == XF_IDENT && (p.t1_scale || p.t2_scale)) return SPANON_ERR_UNSUPPORTED;
+  if (p.gen_feats) {      // encoder.0 generated inside encoder.2's transform warps
+    if (p.cout_v != 64 || act != XF_IDENT) return SPANON_ERR_UNSUPPORTED;
+    return p.stats ? launch_tc<64, XF_GEN | XF_STATS>(p, n_sm, st) : launch_tc<64, XF_GEN>(p, n_sm, st);
+  }
   if (p.cout_v == 16 && xf == XF_SILU) return launch_tc<16, XF_SILU>(p, n_sm, st);
   if (p.cout_v == 64 && xf == XF_IDENT) return launch_tc<64, XF_IDENT>(p, n_sm, st);
   if (p.cout_v == 64 && xf == XF_SILU) return launch_tc<64, XF_SILU>(p, n_sm, st);

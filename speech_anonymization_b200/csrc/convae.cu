@@ -784,6 +784,7 @@ struct LayerIO {
   const float* t1s = nullptr;        // tcgen05 path: per-channel affine on load (overrides in_norm), e.g. the
   const float* t1h = nullptr;        //   producer's bias as (ones, bias)
   int act = -1;                      // activation on load (TapGemmParams::silu); -1 = SiLU iff in_norm >= 0
+  const TapGemmParams* gen = nullptr; // tcgen05 path: gen_* fields of a launch that generates its input (encoder.0 fused)
 };
 
 int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
@@ -823,8 +824,13 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.out_fold = io.out_fold;
   p.out_plane_rows = io.out_fold == OUT_PAIR_FOLD ? p.rows_out / 2 : io.out_fold == OUT_PHASE_UNFOLD ? p.rows_out * 2 : p.rows_out;
   p.in_planar = c.tc ? 1 : 0;
+  if (io.gen) {
+    p.gen_feats = io.gen->gen_feats; p.gen_bstride = io.gen->gen_bstride; p.gen_nvalid = io.gen->gen_nvalid;
+    p.gen_F = io.gen->gen_F; p.gen_mean = io.gen->gen_mean; p.gen_std = io.gen->gen_std; p.gen_umax = io.gen->gen_umax;
+    p.gen_topdb = io.gen->gen_topdb; p.gen_w = io.gen->gen_w; p.gen_b = io.gen->gen_b;
+  }
   p.B = nb;
-  p.tag = kLayerTag[id];
+  p.tag = io.gen ? "tapgemm:enc02" : kLayerTag[id];   // enc02 = encoder.0 generated inside encoder.2's launch
   // InstanceNorm statistics of a tcgen05 layer's output: reduced by the producing kernel's epilogue (default), or by a
   // separate bandwidth-bound pass over the stored plane (instnorm_stats_kernel, $SPANON_FUSED_STATS=0).  Measured on
   // B200 (tools/ab_env.sh SPANON_FUSED_STATS 0 1, 60 x 10 s): +25..+48 us per producing launch against 66 + 6 us for
@@ -975,8 +981,18 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     const int nb = (int)std::min<int64_t>(chunk, B - b0);
     SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.stats[0], 0, stats_bytes, c.st));
     void** X = c.ws.act;
-    // encoder.0 + GLU
-    {
+    // encoder.0 + GLU.  16-bit path: generated inside encoder.2's operand production (conv_tc.cu, XF_GEN) -- the
+    // 32-channel plane (5.16 MB per utterance written and read back) never exists; $SPANON_FUSE_ENC0=0 keeps the
+    // separate first_layer_mma_kernel launch (A/B switch).
+    static const bool fuse_enc0_env = !(getenv("SPANON_FUSE_ENC0") && getenv("SPANON_FUSE_ENC0")[0] == '0');
+    const bool fuse_enc0 = c.tc && fuse_enc0_env && L >= 512;
+    TapGemmParams gen{};
+    if (fuse_enc0) {
+      const int64_t fstride = fused_norm ? T_valid * F : L;
+      gen.gen_feats = feats + b0 * fstride; gen.gen_bstride = fstride; gen.gen_nvalid = T_valid * F; gen.gen_F = (int)F;
+      gen.gen_mean = norm_mean; gen.gen_std = norm_std; gen.gen_umax = utt_max ? utt_max + b0 : nullptr;
+      gen.gen_topdb = top_db; gen.gen_w = w->enc_w[0]; gen.gen_b = w->enc_b[0];
+    } else {
       const int64_t fstride = fused_norm ? T_valid * F : L;
       const float* src = feats + b0 * fstride;
       dim3 grid((unsigned)ceil_div(L, FL_NT), (unsigned)nb);
@@ -996,7 +1012,11 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     const bool tcp = c.tc;
     auto nb_ = [&](const float* bias) { return tcp ? nullptr : bias; };
     //                         in    out   in_norm t2  bias          relu e_bn stats out_mode
-    SPANON_TRY(run_layer(c, L_ENC2, {X[0], X[1], -1, -1, nb_(w->enc_b[1]), 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2}, nb));
+    {
+      LayerIO e2{X[0], X[1], -1, -1, nb_(w->enc_b[1]), 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2};
+      if (fuse_enc0) e2.gen = &gen;
+      SPANON_TRY(run_layer(c, L_ENC2, e2, nb));
+    }
     SPANON_TRY(finalize_in(c, L_ENC2, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
     SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, nb_(w->enc_b[2]), 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
                                      OUT_PAIR_FOLD}, nb));

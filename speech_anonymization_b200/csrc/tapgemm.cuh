@@ -67,6 +67,16 @@ struct TapGemmParams {
   // [B][cout_mod] and zeroes `stats` (fin_counter == nullptr: the caller runs instnorm_finalize_kernel)
   unsigned* fin_counter; const float* fin_gamma; const float* fin_beta; float* fin_scale; float* fin_shift;
   double fin_count;
+  // tcgen05 kernel, XF_GEN launches (encoder.2 with encoder.0 fused into its operand production): the transform warps
+  // GENERATE the input plane -- SiLU(Conv1d(1 -> 32, k15, p7)(x) + b) of the clamped / normalised / zero-padded feature
+  // signal x -- straight into the operand ring instead of reading a stored plane (`in` is unused).
+  const float* gen_feats;          // [B][gen_bstride] fp32 features (raw Fbank dB when gen_mean != null)
+  int64_t gen_bstride;             // elements between utterances of gen_feats
+  int64_t gen_nvalid;              // samples of an utterance that exist (T_valid * F); the rest of [0, L) is zero padding
+  int gen_F;                       // mel bins (index of gen_mean / gen_std = sample % gen_F)
+  const float* gen_mean; const float* gen_std;   // [F] or null (plain features)
+  const int32_t* gen_umax; float gen_topdb;      // per-utterance top_db floor (with gen_mean)
+  const float* gen_w; const float* gen_b;        // encoder.0 weight [32][1][15], bias [32]
   long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]
   const char* tag;     // profile name of this launch ("tapgemm:<layer>")
 };
