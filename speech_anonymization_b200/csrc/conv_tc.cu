@@ -227,6 +227,8 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(BAR(B_SFULL + slot));
+        if (p.trace && lane == 0 && k * n_stage_tile < TRACE_N)
+          for (int s2 = 0; s2 < n_stage_tile; ++s2) p.trace[((int64_t)blockIdx.x * 6 + 3) * TRACE_N + k * n_stage_tile + s2] = clock64();
       }
     } else {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
@@ -321,25 +323,44 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         const int it = k * n_stage_tile + s_fix;
         if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 4) * TRACE_N + it] = clock64();
         unsigned char* sbase = smem + L.a + stage * L.stage_bytes;
-#pragma unroll 3
-        for (int mt = 0; mt < 9; ++mt) {                       // 9 x 16 slab rows >= slab_used (130)
-          const uint32_t a0 = sig32[g + t4 + 16 * mt], a1 = sig32[g + 8 + t4 + 16 * mt];
-          const uint32_t a2 = sig32[g + 4 + t4 + 16 * mt], a3 = sig32[g + 12 + t4 + 16 * mt];
+        // 9 x 16 slab rows >= slab_used (130), three 16-row tiles per round: all loads, then the six MMAs, then the
+        // twelve SiLUs and stores (the chain LDS -> HMMA -> cvt -> MUFU -> HFMA2 -> STS is latency-bound otherwise)
+#pragma unroll 1
+        for (int m3 = 0; m3 < 3; ++m3) {
+          uint32_t a[3][4];
 #pragma unroll
-          for (int nt = 0; nt < 2; ++nt) {
-            float acc[4] = {bz[nt][0], bz[nt][1], bz[nt][0], bz[nt][1]};
-            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                         : "+f"(acc[0]), "+f"(acc[1]), "+f"(acc[2]), "+f"(acc[3])
-                         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(bw[nt][0]), "r"(bw[nt][1]));
-#pragma unroll
-            for (int hr = 0; hr < 2; ++hr) {
-              const int r = 16 * mt + g + 8 * hr;
-              if (r < slab_used) {
-                const __half2 y = silu_from_half(__floats2half2_rn(acc[2 * hr], acc[2 * hr + 1]));
-                *reinterpret_cast<__half2*>(sbase + (uint32_t)nt * L.lbo_a + (uint32_t)r * 16u + 4u * t4) = y;
-              }
-            }
+          for (int u = 0; u < 3; ++u) {
+            const int o = g + t4 + 16 * (3 * m3 + u);
+            a[u][0] = sig32[o]; a[u][1] = sig32[o + 8]; a[u][2] = sig32[o + 4]; a[u][3] = sig32[o + 12];
           }
+          float acc[3][2][4];
+#pragma unroll
+          for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+              acc[u][nt][0] = bz[nt][0]; acc[u][nt][1] = bz[nt][1]; acc[u][nt][2] = bz[nt][0]; acc[u][nt][3] = bz[nt][1];
+              asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                  : "+f"(acc[u][nt][0]), "+f"(acc[u][nt][1]), "+f"(acc[u][nt][2]), "+f"(acc[u][nt][3])
+                  : "r"(a[u][0]), "r"(a[u][1]), "r"(a[u][2]), "r"(a[u][3]), "r"(bw[nt][0]), "r"(bw[nt][1]));
+            }
+          __half2 y[3][2][2];
+#pragma unroll
+          for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+              for (int hr = 0; hr < 2; ++hr)
+                y[u][nt][hr] = silu_from_half(__floats2half2_rn(acc[u][nt][2 * hr], acc[u][nt][2 * hr + 1]));
+#pragma unroll
+          for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+              for (int hr = 0; hr < 2; ++hr) {
+                const int r = 16 * (3 * m3 + u) + g + 8 * hr;
+                if (r < slab_used)
+                  *reinterpret_cast<__half2*>(sbase + (uint32_t)nt * L.lbo_a + (uint32_t)r * 16u + 4u * t4) = y[u][nt][hr];
+              }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(BAR(B_SEMPTY + slot));      // this warp is done with the tile's signal window
