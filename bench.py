@@ -176,6 +176,8 @@ def convae_layer_flops(L=80640):
            "tapgemm:enc8": (L // 4) * 64 * 5 * 128, "tapgemm:enc11": (L // 4) * 128 * 5 * 128,
            "tapgemm:tdnn0": (L // 4 - 4) * 128 * 5 * 128, "tapgemm:tdnn3": (L // 4 - 8) * 128 * 3 * 128,
            "tapgemm:tdnn6": (L // 4 - 14) * 128 * 3 * 128,
+           # the three TDNN convolutions as one dataflow launch
+           "tapgemm:tdnn036": (L // 4 - 4) * 128 * 5 * 128 + (L // 4 - 8) * 128 * 3 * 128 + (L // 4 - 14) * 128 * 3 * 128,
            "tapgemm:dec0": (L // 4) * 128 * 5 * 128, "tapgemm:dec1": (L // 4) * 128 * 5 * 64,
            "tapgemm:dec4": (L // 2) * 64 * 5 * 64, "tapgemm:dec5": (L // 2) * 64 * 5 * 32,
            # decoder.4 o decoder.5 run as one composed layer: counted at the ALGORITHMIC flops of the two reference layers

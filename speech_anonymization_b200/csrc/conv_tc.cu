@@ -62,7 +62,7 @@ constexpr int TC_EPI_THREADS = 128;       // Toeplitz epilogue (always four warp
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
 constexpr int TC_MAX_STAGES = 16;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
-enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16 };
+enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16, XF_DYN = 32, XF_FLOW = 64 };
 constexpr int TC_GEN_SIG = 320;           // fp16 samples of one tile's signal window (XF_GEN)
 constexpr int TC_GEN_SLOTS = 4;           // signal windows in flight (filled by the loader warps, read by the transform warps)
 constexpr int TC_GEN_MAXF = 128;          // mel bins the per-warp (mean, 1/std) table holds
@@ -71,6 +71,9 @@ constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
 constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
 constexpr int TC_TOEP_STEP = TC_M - (TC_TOEP_TAPS - 1);   // complete outputs per 128-row tile
+// stages the MMA issuer handles per round (compile-time: the issue loop must stay in uniform registers); divides the
+// stages per tile of every layer of that width (N = 16: 2 stages; N = 64: 4; N = 128: 8)
+__host__ __device__ constexpr int tc_mma_group(int cout_v) { return cout_v == 16 ? 2 : 4; }
 __host__ __device__ constexpr int TC_TMEM_COLS(int cout_v) { return 2 * cout_v < 32 ? 32 : 2 * cout_v; }
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory"); }
@@ -118,9 +121,12 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
 // [48,50) tmem_full, [50,52) tmem_empty, 52 weights; 54 = TMEM base pointer
 enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54, B_SFULL = 56, B_SEMPTY = 60 };
 
-template <int COUT_V, int XF>
-__global__ void __launch_bounds__(tc_threads(XF), 1)
-tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step) {
+// One CTA's work on one layer.  cta_idx / n_cta: this CTA's index among the CTAs working on the layer.  rr_group == 0: the
+// CTA walks a CONTIGUOUS run of tiles; rr_group = G > 0: groups of G consecutive tiles are dealt round-robin to the
+// layer's CTAs (multi-layer dataflow launches: every layer then advances through the tile sequence at the same pace).
+template <int COUT_V, int XF, int MG>
+__device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles,
+                                        int tile_step, int cta_idx, int n_cta, int rr_group, int mma_group) {
   extern __shared__ __align__(128) unsigned char smem[];
   const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -135,8 +141,33 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
   const int n_stage_tile = p.cin_v / TC_STAGE_CH;     // 2, 4 or 8
   // contiguous run of tiles per CTA: consecutive tiles of one utterance share halo rows (L2) and the per-utterance
   // InstanceNorm constants, which a transform warp then reloads only when the utterance changes
-  const int t_begin = (int)((int64_t)blockIdx.x * total_tiles / (int64_t)gridDim.x);
-  const int n_my_tiles = (int)((int64_t)(blockIdx.x + 1) * total_tiles / (int64_t)gridDim.x) - t_begin;
+  // (dataflow-launch code -- round-robin tile groups, flag polls, flag publication -- exists only in XF_FLOW instantiations:
+  // the four roles share a small instruction cache and the small-tile layers are sensitive to every extra instruction)
+  constexpr bool flow = (XF & XF_FLOW) != 0;
+  if constexpr (!flow) rr_group = 0;
+  int t_begin = 0, n_my_tiles = 0;
+  if (rr_group <= 0) {
+    t_begin = (int)((int64_t)cta_idx * total_tiles / (int64_t)n_cta);
+    n_my_tiles = (int)((int64_t)(cta_idx + 1) * total_tiles / (int64_t)n_cta) - t_begin;
+  } else {
+    const int n_groups = (total_tiles + rr_group - 1) / rr_group;
+    const int my_groups = cta_idx < n_groups ? (n_groups - cta_idx + n_cta - 1) / n_cta : 0;
+    n_my_tiles = my_groups * rr_group;
+    if (my_groups > 0 && (n_groups - 1) % n_cta == cta_idx) n_my_tiles -= n_groups * rr_group - total_tiles;   // the last group is short
+  }
+  auto tile_of = [&](int k) {
+    return rr_group <= 0 ? t_begin + k : ((k / rr_group) * n_cta + cta_idx) * rr_group + k % rr_group;
+  };
+  // (utterance, tile in utterance) of local tile k: one division at the start of a role's loop, then incremental in the
+  // contiguous mode (the small-tile layers run ~700 cycles per tile: a division per tile and role shows)
+  auto locate = [&](int k, int& b, int& tin) {
+    const int t = tile_of(k);
+    b = t / tiles_per_utt; tin = t - b * tiles_per_utt;
+  };
+  auto advance = [&](int k_next, int step, int& b, int& tin) {
+    if (rr_group <= 0) { tin += step; while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; } }
+    else if (k_next < n_my_tiles) locate(k_next, b, tin);
+  };
 
   if (warp == TC_MMA_WARP) {
     if (lane == 0) {
@@ -193,8 +224,9 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       __syncwarp();
       const int Lfull = 2 * p.rows_in;
       const int nvalid = (int)min((int64_t)Lfull, p.gen_nvalid);
-      for (int k = lw; k < n_my_tiles; k += TC_LOAD_WARPS) {
-        const int t = t_begin + k, b = t / tiles_per_utt, tin = t - b * tiles_per_utt;
+      int b = 0, tin = 0;
+      if (lw < n_my_tiles) locate(lw, b, tin);
+      for (int k = lw; k < n_my_tiles; k += TC_LOAD_WARPS, advance(k, TC_LOAD_WARPS, b, tin)) {
         const int origin = 2 * (tin * tile_step - halo_lo) - 7;       // x index of window sample 0
         const float* xb = p.gen_feats + (int64_t)b * p.gen_bstride;
         float xv[TC_GEN_SIG / 32];
@@ -234,11 +266,33 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
       const int lw = wd >> 2;
       uint32_t stage = (uint32_t)lw, ph = 0;
-      int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
-      for (int k = 0; k < n_my_tiles; ++k) {
+      int b = 0, tin = 0;
+      if (n_my_tiles > 0) locate(0, b, tin);
+      for (int k = 0; k < n_my_tiles; ++k, advance(k, 1, b, tin)) {
         const int g0 = tin * tile_step - halo_lo;                      // global row of slab row 0
         const int lo = g0 < 0 ? -g0 : 0;                               // first valid slab row
         const int hi = min(slab_used, p.rows_in - g0);                 // one past the last valid slab row
+        if (flow && p.flag_in && hi > lo) {
+          // dataflow launch: the rows [g0+lo, g0+hi) of this utterance come from the PRODUCER layer's tiles j0..j1, written by
+          // other CTAs of the same launch; each of the producer's epilogue warps bumps the tile's counter after its
+          // stores (release), the poll below acquires, and the proxy fence orders the bulk (async-proxy) reads after it
+          const int j0 = (g0 + lo) / TC_M, j1 = (g0 + hi - 1) / TC_M;
+          for (int j = j0; j <= j1; ++j) {
+            const unsigned* f = p.flag_in + (int64_t)b * p.flag_in_tpu + j;
+            unsigned v, spins = 0;
+            for (;;) {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+              if (v >= p.flag_target) break;
+              __nanosleep(64);
+              // never hang the GPU: after ~0.3 s (or as soon as any CTA has given up) flag the error and go on
+              if (++spins > (1u << 22) || (p.err_flag && (spins & 1023u) == 0 && *reinterpret_cast<volatile unsigned*>(p.err_flag))) {
+                if (lane == 0 && p.err_flag) atomicExch(p.err_flag, 1u);
+                break;
+              }
+            }
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
         const int64_t plane_stride = (int64_t)p.rows_in * 8;
         const __half* src = in_base + (((int64_t)b * planes_in + lw * (TC_STAGE_CH / 8)) * p.rows_in + (g0 + lo)) * 8;
@@ -255,7 +309,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           stage += TC_LOAD_WARPS;
           if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
         }
-        if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
     }
   } else if (is_xform) {
@@ -268,15 +321,18 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     // i.e. per 8 elements 4 HFMA2 + 4 MUFU + 4 HFMA2 (+ 4 HFMA2).  Rows outside the utterance (= the conv's zero
     // padding of the already activated tensor) exist only in an utterance's first / last tile and are zeroed there.
     const int xw = wd - (wd >> 2);
-    constexpr bool do_silu = (XF & 3) == XF_SILU, do_relu = (XF & 3) == XF_RELU, has_t2 = (XF & XF_T2) != 0;
-    constexpr bool ident = (XF & 7) == XF_IDENT;
+    // (XF_DYN: the activation is the layer's own, a launch may mix SiLU and ReLU layers; otherwise compile-time)
+    constexpr bool dyn = (XF & XF_DYN) != 0, has_t2 = (XF & XF_T2) != 0;
+    const bool do_silu = dyn ? p.silu == 1 : (XF & 3) == XF_SILU, do_relu = dyn ? p.silu == 2 : (XF & 3) == XF_RELU;
+    constexpr bool ident = (XF & 7) == XF_IDENT && !dyn;
     const bool has_t1 = p.t1_scale != nullptr;
     const float pre = do_silu ? 0.5f : 1.f;                    // SiLU works on x/2: fold the 1/2 into the affine
     const int s_fix = xw % n_stage_tile;                       // stage-in-tile of this warp (n_stage_tile is 2, 4 or 8)
     const int kstep = TC_XF_WARPS / n_stage_tile;              // tiles between two stages of this warp
     int k = xw / n_stage_tile;
     uint32_t stage = (uint32_t)xw, ph = 0;                     // n_stages is 8 or 16
-    int b = (t_begin + k) / tiles_per_utt, tin = (t_begin + k) - b * tiles_per_utt;
+    int b = 0, tin = 0;
+    if (k < n_my_tiles) locate(k, b, tin);
     const int cm = (s_fix * TC_STAGE_CH) % p.cin_mod;          // this warp's 16 channels
     __half2 s1[8], h1[8], s2[8], h2[8];
 #pragma unroll
@@ -311,7 +367,7 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         bz[nt][0] = 0.5f * __ldg(p.gen_b + ci0 + 8 * nt + 2 * t4);
         bz[nt][1] = 0.5f * __ldg(p.gen_b + ci0 + 8 * nt + 2 * t4 + 1);
       }
-      for (; k < n_my_tiles; k += kstep) {
+      for (; k < n_my_tiles; k += kstep, advance(k, kstep, b, tin)) {
         const int g0 = tin * tile_step - halo_lo;
         const int lo = g0 < 0 ? -g0 : 0;
         const int hi = min(slab_used, p.rows_in - g0);
@@ -378,11 +434,9 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
         stage += TC_XF_WARPS;
         if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
-        tin += kstep;
-        while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
       }
     } else
-    for (; k < n_my_tiles; k += kstep) {
+    for (; k < n_my_tiles; k += kstep, advance(k, kstep, b, tin)) {
       const int g0 = tin * tile_step - halo_lo;
       const int lo = g0 < 0 ? -g0 : 0;
       const int hi = min(slab_used, p.rows_in - g0);
@@ -441,8 +495,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 0) * TRACE_N + it] = clock64();
       stage += TC_XF_WARPS;
       if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
-      tin += kstep;
-      while (tin >= tiles_per_utt) { tin -= tiles_per_utt; ++b; }
     }
   } else if (warp == TC_MMA_WARP) {
     // =========================== MMA ISSUER ===========================
@@ -461,12 +513,19 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
       const uint32_t idesc_full = umma_idesc(COUT_V), idesc_tap0 = umma_idesc(p.tap_nmax[0]);
       const int s_short = p.tap_kmax[p.ntaps - 1] / TC_STAGE_CH;  // stages >= s_short skip the last tap
       const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const int last_tap = p.ntaps - 1;
       uint32_t it = 0, stage = 0, ph = 0;
+      (void)mma_group;
+      // The wait -> fence -> descriptor set-up -> commit sequence around a stage's MMAs costs the issuer ~140 cycles during
+      // which the tensor pipe drains (a 16-channel stage is only ntaps MMAs = 190..340 cycles of work), so MG
+      // consecutive stages are handled per round: one set of waits, the MMAs of all of them tap by tap, then the commits.
+      // (groups never straddle the ring's wrap: ring size and stages per tile are multiples of the group)
       for (int k = 0; k < n_my_tiles; ++k) {
         const uint32_t buf = (uint32_t)k & 1u;
         mbar_wait(BAR(B_TEMPTY + buf), (((uint32_t)k >> 1) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_u + buf * (uint32_t)COUT_V;
+        if constexpr (MG == 1) {
         for (int s = 0; s < n_stage_tile; ++s, ++it) {
           uint32_t a_lo = a_lo_const + ((s_base + L.a + stage * L.stage_bytes) >> 4);
           uint32_t b_lo = b_lo_const + (uint32_t)s * b_stage;
@@ -474,7 +533,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           mbar_wait(BAR(B_FULL + stage), ph);
           tc_fence_after();
           if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
-          // tap 0 (the first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
           umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo,
                          s == 0 ? idesc_full : idesc_tap0, s != 0);
 #pragma unroll 1
@@ -486,6 +544,44 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           tc_commit_elect(BAR(B_EMPTY + stage));    // slot free once these MMAs have read it
           if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
           if (++stage == (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
+        }
+        } else
+        for (int s = 0; s < n_stage_tile; s += MG, it += MG) {
+#pragma unroll
+          for (int g = 0; g < MG; ++g) mbar_wait(BAR(B_FULL + stage + g), ph);
+          tc_fence_after();
+          if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 5) * TRACE_N + it] = clock64();
+          uint32_t a_lo[MG], b_lo[MG];
+#pragma unroll
+          for (int g = 0; g < MG; ++g) {
+            a_lo[g] = a_lo_const + ((s_base + L.a + (stage + g) * L.stage_bytes) >> 4);
+            b_lo[g] = b_lo_const + (uint32_t)(s + g) * b_stage;
+          }
+          // tap 0 (the first MMA of a tile initialises all columns; otherwise it may cover fewer columns)
+#pragma unroll
+          for (int g = 0; g < MG; ++g)
+            umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo[g], ((uint64_t)desc_hi << 32) | b_lo[g],
+                           (s + g) == 0 ? idesc_full : idesc_tap0, (uint32_t)((s + g) != 0));
+#pragma unroll 1
+          for (int tap = 1; tap < last_tap; ++tap) {
+#pragma unroll
+            for (int g = 0; g < MG; ++g) {
+              a_lo[g] += dil;
+              b_lo[g] += b_tap;
+              umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo[g], ((uint64_t)desc_hi << 32) | b_lo[g], idesc_full, 1u);
+            }
+          }
+          if (last_tap >= 1) {   // stages >= s_short skip the last tap (the non-existent sixth tap of a stride-2 k5 conv)
+#pragma unroll
+            for (int g = 0; g < MG; ++g)
+              if (s + g < s_short)
+                umma_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo[g] + dil), ((uint64_t)desc_hi << 32) | (b_lo[g] + b_tap), idesc_full, 1u);
+          }
+#pragma unroll
+          for (int g = 0; g < MG; ++g) tc_commit_elect(BAR(B_EMPTY + stage + g));    // slots free once these MMAs have read them
+          if (p.trace && lane == 0 && it < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 1) * TRACE_N + it] = clock64();
+          stage += (uint32_t)MG;
+          if (stage >= (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
         }
         tc_commit_elect(BAR(B_TFULL + buf));        // accumulator complete
       }
@@ -499,13 +595,14 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
     constexpr int CPW = COUT_V / (E / 4);     // columns per warp
     constexpr int NCH = COUT_V / 8;     // output chunks
     const bool cl = p.out_mode == OUT_CHANNELS_LAST;
-    int b = t_begin / tiles_per_utt, tin = t_begin - b * tiles_per_utt;
     if constexpr (COUT_V == 16) {
       // ---- Toeplitz epilogue (decoder.8, 32 -> 1 channel, 15 taps): the GEMM produced D[r][t] = sum_c a[r][c] w[c][t]
       //      for the 128 slab rows; out[l] = bias + sum_t D[l - m0 + t][t]  (slab row 0 = global row m0 - 7)
       float* dt = reinterpret_cast<float*>(smem + L.red);
       const float bias0 = ec[0];
-      for (int k = 0; k < n_my_tiles; ++k) {
+      int b = 0, tin = 0;
+      if (n_my_tiles > 0) locate(0, b, tin);
+      for (int k = 0; k < n_my_tiles; ++k, advance(k, 1, b, tin)) {
         const int m0 = tin * tile_step;
         const uint32_t buf = (uint32_t)k & 1u;
         mbar_wait(BAR(B_TFULL + buf), ((uint32_t)k >> 1) & 1u);
@@ -526,7 +623,6 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
           for (int t = 0; t < TC_TOEP_TAPS; ++t) acc += d[(mloc + t) * 17 + t];
           reinterpret_cast<float*>(p.out)[(int64_t)b * p.out_bstride + m] = acc;
         }
-        if (++tin == tiles_per_utt) { tin = 0; ++b; }
       }
     } else {
     // ---- InstanceNorm statistics of the output from the accumulator itself (XF_STATS): after a 32-column block is
@@ -544,7 +640,11 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         es[i] = 0.f; eq[i] = 0.f;
       }
     };
-    for (int k = 0; k < n_my_tiles; ++k) {
+    int b_prev = -1, b = 0, tin = 0;
+    if (n_my_tiles > 0) locate(0, b, tin);
+    for (int k = 0; k < n_my_tiles; ++k, advance(k, 1, b, tin)) {
+      if constexpr (e_stats) { if (b_prev >= 0 && b != b_prev) e_flush(b_prev); }
+      b_prev = b;
       const int m0 = tin * tile_step;
       const int m = m0 + mloc;
       const bool valid = m < p.rows_out;
@@ -631,12 +731,13 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
         }
       }
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();
-      if (++tin == tiles_per_utt) {
-        if constexpr (e_stats) e_flush(b);
-        tin = 0; ++b;
+      if (flow && p.flag_out) {      // dataflow launch: publish this warp's part of tile t to the consumer layer's loaders
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(p.flag_out + (int64_t)b * tiles_per_utt + tin, 1u);
       }
     }
-    if constexpr (e_stats) { if (tin != 0) e_flush(b); }
+    if constexpr (e_stats) { if (b_prev >= 0) e_flush(b_prev); }
     }
   }
 
@@ -649,8 +750,40 @@ tapgemm_tc_kernel(TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt
 
 }
 
-template <int COUT_V, int XF>
-int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
+template <int COUT_V, int XF, int MG>
+__global__ void __launch_bounds__(tc_threads(XF), 1)
+tapgemm_tc_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int tile_step,
+                  int mma_group) {
+  tc_body<COUT_V, XF, MG>(p, halo_lo, slab_used, tiles_per_utt, total_tiles, tile_step, (int)blockIdx.x, (int)gridDim.x, 0, mma_group);
+}
+
+// Several layers of a chain in ONE launch (dataflow through global memory / L2): the CTAs [cta0, cta0 + n_cta) work on
+// layer i (its weights resident in their shared memory); a consumer layer's loaders wait on the per-tile counters its
+// producer's epilogue warps bump.  Producers have the lower block indices and never wait on consumers, and the grid is
+// one CTA per SM, so every CTA a waiting CTA depends on is resident or already finished.
+struct TcSeg { TapGemmParams p; int halo_lo, slab_used, tiles_per_utt, total_tiles, tile_step, cta0, n_cta; };
+struct TcMulti { TcSeg seg[3]; int n_seg, rr_group, mma_group; };
+
+template <int COUT_V, int XF, int MG>
+__global__ void __launch_bounds__(tc_threads(XF), 1)
+tapgemm_tc_multi_kernel(const __grid_constant__ TcMulti mp) {
+  const int bx = (int)blockIdx.x;
+  // (three static copies of the body: each reads its layer's parameters straight from the constant bank)
+  if (mp.n_seg > 2 && bx >= mp.seg[2].cta0) {
+    const TcSeg& g = mp.seg[2];
+    tc_body<COUT_V, XF, MG>(g.p, g.halo_lo, g.slab_used, g.tiles_per_utt, g.total_tiles, g.tile_step, bx - g.cta0, g.n_cta, mp.rr_group, mp.mma_group);
+  } else if (mp.n_seg > 1 && bx >= mp.seg[1].cta0) {
+    const TcSeg& g = mp.seg[1];
+    tc_body<COUT_V, XF, MG>(g.p, g.halo_lo, g.slab_used, g.tiles_per_utt, g.total_tiles, g.tile_step, bx - g.cta0, g.n_cta, mp.rr_group, mp.mma_group);
+  } else {
+    const TcSeg& g = mp.seg[0];
+    tc_body<COUT_V, XF, MG>(g.p, g.halo_lo, g.slab_used, g.tiles_per_utt, g.total_tiles, g.tile_step, bx - g.cta0, g.n_cta, mp.rr_group, mp.mma_group);
+  }
+}
+
+
+template <int COUT_V, int XF, int MG>
+int launch_tc_mg(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   int lo = 0, hi = 0;
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
   const bool toeplitz = COUT_V == 16;
@@ -665,14 +798,16 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if ((XF & XF_GEN) && (slab_used > 144 || 2 * 143 + 17 > TC_GEN_SIG || p.gen_F > TC_GEN_MAXF || p.gen_F < 32 || p.cin_mod != 32 || p.cin_v != 64 || !p.gen_feats ||
                         !p.gen_w || !p.gen_b || (p.gen_mean == nullptr) != (p.gen_std == nullptr)))
     return SPANON_ERR_UNSUPPORTED;
-  auto kern = tapgemm_tc_kernel<COUT_V, XF>;
+  auto kern = tapgemm_tc_kernel<COUT_V, XF, MG>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+  const int mma_group = MG;
+  if (nst % MG != 0 || L.n_stages % MG != 0) return SPANON_ERR_UNSUPPORTED;
   const int tiles_per_utt = (int)ceil_div(p.rows_out, tile_step);
   const int total = tiles_per_utt * p.B;
   const int grid = std::min(total, n_sm);
   static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
   if (!trace_on) {
-    kern<<<grid, tc_threads(XF), L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step);
+    kern<<<grid, tc_threads(XF), L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step, mma_group);
     return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   }
   // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch
@@ -682,7 +817,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
   TapGemmParams q = p;
   q.trace = dbuf;
-  kern<<<grid, tc_threads(XF), L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total, tile_step);
+  kern<<<grid, tc_threads(XF), L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total, tile_step, mma_group);
   int rc = check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   SPANON_CUDA_TRY(cudaStreamSynchronize(st));
   std::vector<long long> h((size_t)6 * TRACE_N);
@@ -704,7 +839,69 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   return rc;
 }
 
+// Stages per issue round: 4 where the ring holds two tiles or more (16 stages), fewer where the resident weights leave
+// room for one tile only (the 128 -> 128 k5 layers: a round then has to wait for -- and frees -- half the ring at once).
+template <int COUT_V, int XF>
+int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
+  if constexpr (COUT_V == 16) return launch_tc_mg<COUT_V, XF, 2>(p, n_sm, st);
+  else {
+    int lo = 0, hi = 0;
+    for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
+    const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, TC_M - lo + hi, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
+    // measured per layer on B200 (same-box A/B): rounds of 4 stages pay on decoder.4 o 5 (7 taps) and tdnn.3 / tdnn.6
+    // (-5 .. -12 us), and cost 3 .. 10 us on the layers whose epilogue reduces statistics or whose ring holds one tile
+    if (p.mma_group >= 4 && L.n_stages >= 16) {
+      if constexpr (XF == (XF_RELU | XF_T2) || (COUT_V == 64 && XF == (XF_SILU | XF_STATS))) return launch_tc_mg<COUT_V, XF, 4>(p, n_sm, st);
+    }
+    return launch_tc_mg<COUT_V, XF, 1>(p, n_sm, st);
+  }
+}
+
 }  // namespace
+
+namespace {
+int tc_geometry(const TapGemmParams& p, int* halo_lo, int* slab_used) {
+  int lo = 0, hi = 0;
+  for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
+  *halo_lo = -lo;
+  *slab_used = TC_M + *halo_lo + hi;
+  return *slab_used <= 160 ? SPANON_OK : SPANON_ERR_UNSUPPORTED;
+}
+}  // namespace
+
+// ps[0..n): the layers of a chain (ps[i+1] reads what ps[i] writes; flag_in / flag_out / flag_target set by the caller),
+// all 128 -> 128 channels with an activation + folded BatchNorm on load; ctas[i] = CTAs working on layer i.
+int launch_tapgemm_tc_chain(const TapGemmParams* ps, int n, const int* ctas, int rr_group, cudaStream_t st) {
+  if (n < 1 || n > 3 || rr_group < 1) return SPANON_ERR_UNSUPPORTED;
+  constexpr int XF = XF_DYN | XF_T2 | XF_FLOW;
+  TcMulti mp{};
+  mp.n_seg = n; mp.rr_group = rr_group; mp.mma_group = tc_mma_group(128);
+  int cta = 0;
+  uint32_t smem_max = 0;
+  for (int i = 0; i < n; ++i) {
+    const TapGemmParams& p = ps[i];
+    if (!tapgemm_tc_supported(p) || p.B < 1 || p.cout_v != 128 || p.stats || p.gen_feats || !p.t2_scale || (p.silu != 1 && p.silu != 2) ||
+        ctas[i] < 1)
+      return SPANON_ERR_UNSUPPORTED;
+    TcSeg& g = mp.seg[i];
+    g.p = p;
+    SPANON_TRY(tc_geometry(p, &g.halo_lo, &g.slab_used));
+    const int nst = p.cin_v / TC_STAGE_CH;
+    if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
+    const TcLayout L = tc_layout(p.ntaps, p.cin_v, 128, g.slab_used, false, false);
+    if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
+    smem_max = std::max(smem_max, L.total);
+    g.tile_step = TC_M;
+    g.tiles_per_utt = (int)ceil_div(p.rows_out, TC_M);
+    g.total_tiles = g.tiles_per_utt * p.B;
+    g.cta0 = cta; g.n_cta = ctas[i];
+    cta += ctas[i];
+  }
+  auto kern = tapgemm_tc_multi_kernel<128, XF, 2>;
+  SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+  kern<<<cta, tc_threads(XF), smem_max, st>>>(mp);
+  return check_launch(ps[0].tag ? ps[0].tag : "tapgemm_tc_chain");
+}
 
 bool tapgemm_tc_supported(const TapGemmParams& p) {
   if (p.out_mode == OUT_CH0_F32)   // Toeplitz form of a C -> 1 channel conv: one "tap" at shift -(k-1)/2, 16 columns = the taps

@@ -529,7 +529,7 @@ __device__ __forceinline__ float bn_eval(float x, const SpanonBatchNorm& bn, int
 // classify: Linear(256,128) ReLU BN | Linear(128,64) ReLU BN | Linear(64,2) | log_softmax.  grid = B, block = 128
 __global__ void __launch_bounds__(128)
 clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise, int64_t n /*L3*/,
-                SpanonConvAEWeights w, float* __restrict__ logp) {
+                SpanonConvAEWeights w, float* __restrict__ logp, const unsigned* __restrict__ err_flag) {
   __shared__ float s0[256], s1[128], s2[64], s3[2];
   const int b = blockIdx.x, tid = threadIdx.x;
   {
@@ -565,7 +565,8 @@ clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise
   if (tid < 2) {
     const float m = fmaxf(s3[0], s3[1]);
     const float lse = m + logf(expf(s3[0] - m) + expf(s3[1] - m));
-    logp[(int64_t)b * 2 + tid] = s3[tid] - lse;
+    // a dataflow wait of the TDNN launch timed out: its planes are incomplete, say so instead of returning numbers
+    logp[(int64_t)b * 2 + tid] = (err_flag && *err_flag) ? NAN : s3[tid] - lse;
   }
 }
 
@@ -691,6 +692,8 @@ struct Workspace {
   double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
   float* in_scale[6]; float* in_shift[6];      // [chunk][C]
   double* pool;                                // [chunk][128][2]
+  unsigned* flags;                             // [2][chunk * ceil(L/4 / 128)] per-tile counters of the TDNN dataflow launch
+  size_t zero_bytes;                           // stats[0] .. end of flags: cleared per chunk
   unsigned* counter;                           // last-CTA ticket of the tcgen05 kernel's fused finalize
   void* act[4];                                // activation ring, each chunk*L*32 elements
   float* tdnn_out;                             // [chunk][128][L4-14] fp32
@@ -724,9 +727,12 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
   ws.ones = (float*)take(128 * 4);
   ws.bias45 = (float*)take(64 * 4);
   ws.edge45 = (float*)take(EDGE45_FLOATS * 4);
-  // stats are contiguous so one memset clears them
+  // stats, pool and flags are contiguous so one memset clears them
+  const size_t stats_off = off;
   for (int i = 0; i < 6; ++i) ws.stats[i] = (double*)take((size_t)chunk * inC[i] * 2 * sizeof(double));
   ws.pool = (double*)take((size_t)chunk * 128 * 2 * sizeof(double));
+  ws.flags = (unsigned*)take(with_tdnn ? 2 * (size_t)chunk * (size_t)ceil_div(std::max<int64_t>(L / 4, 1), 128) * sizeof(unsigned) : 0);
+  ws.zero_bytes = off - stats_off;
   ws.counter = (unsigned*)take(256);
   for (int i = 0; i < 6; ++i) {
     ws.in_scale[i] = (float*)take((size_t)chunk * inC[i] * 4);
@@ -787,7 +793,7 @@ struct LayerIO {
   const TapGemmParams* gen = nullptr; // tcgen05 path: gen_* fields of a launch that generates its input (encoder.0 fused)
 };
 
-int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
+TapGemmParams make_params(const Ctx& c, int id, const LayerIO& io, int nb) {
   const bool on_tc = layer_on_tc(c, id);
   LayerSpec s = make_spec(id, on_tc);
   TapGemmParams p{};
@@ -830,7 +836,15 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
     p.gen_topdb = io.gen->gen_topdb; p.gen_w = io.gen->gen_w; p.gen_b = io.gen->gen_b;
   }
   p.B = nb;
+  p.mma_group = (id == L_DEC45 || id == L_TD3 || id == L_TD6) ? 4 : 1;
   p.tag = io.gen ? "tapgemm:enc02" : kLayerTag[id];   // enc02 = encoder.0 generated inside encoder.2's launch
+  return p;
+}
+
+int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
+  const bool on_tc = layer_on_tc(c, id);
+  LayerSpec s = make_spec(id, on_tc);
+  TapGemmParams p = make_params(c, id, io, nb);
   // InstanceNorm statistics of a tcgen05 layer's output: reduced by the producing kernel's epilogue (default), or by a
   // separate bandwidth-bound pass over the stored plane (instnorm_stats_kernel, $SPANON_FUSED_STATS=0).  Measured on
   // B200 (tools/ab_env.sh SPANON_FUSED_STATS 0 1, 60 x 10 s): +25..+48 us per producing launch against 66 + 6 us for
@@ -974,8 +988,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   }
   }
   const int64_t L2 = L / 2, L4 = L / 4;
-  const size_t stats_bytes = reinterpret_cast<char*>(c.ws.pool) + align_up((size_t)chunk * 128 * 2 * sizeof(double), 256) -
-                             reinterpret_cast<char*>(c.ws.stats[0]);
+  const size_t stats_bytes = c.ws.zero_bytes;
   SPANON_CUDA_TRY(cudaMemsetAsync(c.ws.counter, 0, 256, c.st));
   for (int64_t b0 = 0; b0 < B; b0 += chunk) {
     const int nb = (int)std::min<int64_t>(chunk, B - b0);
@@ -1030,13 +1043,41 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       const int64_t L3 = L4 - 14;
       if (c.tc) {
         LayerIO t0{X[0], X[1], 3, 0, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
-        SPANON_TRY(run_layer(c, L_TD0, t0, nb));
         LayerIO t3{X[1], X[2], -1, 1, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
         t3.t1s = c.ws.ones; t3.t1h = w->tdnn_b[0]; t3.act = 2;     // ReLU(x + b0) -> BatchNorm 1
-        SPANON_TRY(run_layer(c, L_TD3, t3, nb));
         LayerIO t6{X[2], X[3], -1, 2, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};   // fp16 planes (X[3] is free here)
         t6.t1s = c.ws.ones; t6.t1h = w->tdnn_b[1]; t6.act = 2;     // ReLU(x + b1) -> BatchNorm 2
+        // tdnn.0 -> tdnn.3 -> tdnn.6 as ONE dataflow launch (conv_tc.cu, launch_tapgemm_tc_chain): three groups of CTAs,
+        // each with one layer's weights resident, the intermediate planes handed over tile by tile through L2 with
+        // per-tile counters, so the two planes are read back from L2 while they are hot instead of from HBM after a
+        // launch boundary.  $SPANON_TDNN_CHAIN=0: three launches; $SPANON_TDNN_SPLIT=a,b,c: CTAs per layer;
+        // $SPANON_TDNN_GROUP: tiles per round-robin group.
+        static const bool chain_env = getenv("SPANON_TDNN_CHAIN") && getenv("SPANON_TDNN_CHAIN")[0] == '1';
+        if (chain_env && c.n_sm >= 12) {
+          TapGemmParams ps[3] = {make_params(c, L_TD0, t0, nb), make_params(c, L_TD3, t3, nb), make_params(c, L_TD6, t6, nb)};
+          const int tpu0 = (int)ceil_div(ps[0].rows_out, 128), tpu1 = (int)ceil_div(ps[1].rows_out, 128);
+          unsigned* f0 = c.ws.flags;
+          unsigned* f1 = c.ws.flags + (size_t)chunk * (size_t)ceil_div(L4, 128);
+          ps[0].flag_out = f0;
+          ps[1].flag_in = f0; ps[1].flag_in_tpu = tpu0; ps[1].flag_target = 4; ps[1].flag_out = f1;
+          ps[2].flag_in = f1; ps[2].flag_in_tpu = tpu1; ps[2].flag_target = 4;
+          for (int i = 0; i < 3; ++i) ps[i].err_flag = c.ws.counter + 1;
+          ps[0].tag = "tapgemm:tdnn036";
+          // CTAs per layer in proportion to the measured per-tile cost (5 taps : 3 taps : 3 taps of 128 x 128 MMAs)
+          int ctas[3] = {(c.n_sm * 46 + 50) / 100, 0, 0};
+          ctas[1] = (c.n_sm - ctas[0]) / 2; ctas[2] = c.n_sm - ctas[0] - ctas[1];
+          if (const char* e = getenv("SPANON_TDNN_SPLIT")) {
+            int a = 0, b = 0, d = 0;
+            if (sscanf(e, "%d,%d,%d", &a, &b, &d) == 3 && a > 0 && b > 0 && d > 0 && a + b + d <= c.n_sm) { ctas[0] = a; ctas[1] = b; ctas[2] = d; }
+          }
+          int group = 8;
+          if (const char* e = getenv("SPANON_TDNN_GROUP")) { const int g = atoi(e); if (g >= 1 && g <= 64) group = g; }
+          SPANON_TRY(launch_tapgemm_tc_chain(ps, 3, ctas, group, c.st));
+        } else {
+        SPANON_TRY(run_layer(c, L_TD0, t0, nb));
+        SPANON_TRY(run_layer(c, L_TD3, t3, nb));
         SPANON_TRY(run_layer(c, L_TD6, t6, nb));
+        }
         // (pooling in tdnn.6's epilogue instead -- a lane rotation per column hands each value to the lane owning its bin
         // -- was measured at +140 us on that launch against 85 us for this pass: ~20 dependent instructions per column on
         // two warps per TMEM lane quarter run at ~3 cycles each)
@@ -1053,7 +1094,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       }
       SPANON_TRY(check_launch("pool_kernel"));
       clf_head_kernel<<<(unsigned)nb, 128, 0, c.st>>>(c.ws.pool, pool_noise ? pool_noise + b0 * 128 : nullptr, L3, *w,
-                                                      logp + b0 * 2);
+                                                      logp + b0 * 2, c.ws.counter + 1);
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));

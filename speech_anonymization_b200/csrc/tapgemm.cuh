@@ -77,6 +77,11 @@ struct TapGemmParams {
   const float* gen_mean; const float* gen_std;   // [F] or null (plain features)
   const int32_t* gen_umax; float gen_topdb;      // per-utterance top_db floor (with gen_mean)
   const float* gen_w; const float* gen_b;        // encoder.0 weight [32][1][15], bias [32]
+  // tcgen05 kernel, dataflow (chain) launches: per-tile counters [B * tiles_per_utt] of this layer's OUTPUT (bumped once by
+  // each of the 4 epilogue warps) and of its INPUT's producer (flag_in_tpu = the producer's tiles per utterance)
+  unsigned* flag_out; const unsigned* flag_in; int flag_in_tpu; unsigned flag_target;
+  int mma_group;       // tcgen05 kernel: stages per MMA issue round the caller asks for (0/1 = one; 4 where it pays)
+  unsigned* err_flag;  // set to 1 if a dataflow wait timed out (results are then invalid; the consumer kernels report it)
   long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]
   const char* tag;     // profile name of this launch ("tapgemm:<layer>")
 };
@@ -88,6 +93,8 @@ int launch_tapgemm_simt(const TapGemmParams& p, cudaStream_t st);
 // tcgen05 family (conv_tc.cu).  fp16 activations; packed weights: fp16 UMMA core-matrix
 // layout [ntaps][cin_v/8][cout_v][8].
 int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st);
+// A chain of up to three 128 -> 128 layers (the TDNN) in one launch, see conv_tc.cu.
+int launch_tapgemm_tc_chain(const TapGemmParams* ps, int n, const int* ctas, int rr_group, cudaStream_t st);
 bool tapgemm_tc_supported(const TapGemmParams& p);
 
 }  // namespace spanon
