@@ -272,6 +272,59 @@ SPANON_API int spanon_xvector_classify(const float* feats, const float* rel_len,
                             void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * Training step of the ConvAutoencoder path (fp32, channels-last [utterance][row][channel] tensors)
+ * replaces  the autograd graph of ConvAutoencoder.forward in TRAIN mode   models/ConvAutoEncoder.py:178-200
+ *           that `(loss / gradient_accumulation).backward()` walks       speechbrain_convae_train.py:238-241
+ *           nn.Conv1d / nn.ConvTranspose1d forward + backward            models/ConvAutoEncoder.py:141-172, 33-43
+ *           nn.InstanceNorm1d(affine) / train-mode nn.BatchNorm1d + GLU  :146-169, :36-44, :113-120
+ *           reshape + StatisticsPooling forward + backward               :61-65, speechbrain/nnet/pooling.py:263-312
+ * The host (speech_anonymization_b200/train.py) chains these as torch.autograd.Function nodes, so the reference's
+ * requires_grad toggling per epoch parity (speechbrain_convae_train.py:212-235) prunes the same sub-graphs.
+ * ------------------------------------------------------------------------- */
+typedef struct SpanonTapConv {
+  int32_t kind;       /* 0: Conv1d stride 1 (any dilation / padding); 1: Conv1d k5 s2 p2; 2: ConvTranspose1d k5 s2 p2 op1 */
+  int32_t cin, cout;  /* real channels: cin in {32, 64, 128}, cout in {1 (kind 0, cin 32, k15, p7), 32 (kind 2), 64, 128} */
+  int32_t k, dilation, padding;
+} SpanonTapConv;
+SPANON_API size_t spanon_tapconv_workspace_bytes(const SpanonTapConv* cv);
+/* in [B][rows_in][cin] -> out [B][rows_out][cout] ([B][rows_out] for cout == 1), + bias, optional ReLU; stats != NULL:
+ * [B][cout][2] fp64 sums / sums of squares of the stored values are ADDED (clear them first): the statistics of the
+ * InstanceNorm / BatchNorm that follows.  w, bias: the module's parameters in PyTorch layout. */
+SPANON_API int spanon_tapconv_fwd(const float* in, const float* w, const float* bias, float* out, double* stats, int relu,
+                       void* workspace, size_t workspace_bytes, int64_t B, int64_t rows_in, const SpanonTapConv* cv,
+                       void* stream);
+/* gout = dL/d out -> gin = dL/d in, gw = dL/d w (PyTorch layout), gb = dL/d bias; each may be NULL (frozen / not needed). */
+SPANON_API int spanon_tapconv_bwd(const float* in, const float* w, const float* gout, float* gin, float* gw, float* gb,
+                       void* workspace, size_t workspace_bytes, int64_t B, int64_t rows_in, const SpanonTapConv* cv,
+                       void* stream);
+/* encoder.0: Conv1d(1 -> 32, k15, p7) on the flattened feature signal x [B][L] -> out [B][L][32] (raw, no activation);
+ * backward: gw [32][1][15], gb [32] (the input signal needs no gradient on this path); scratch: 32 doubles. */
+SPANON_API int spanon_conv1_fwd(const float* x, const float* w, const float* bias, float* out, int64_t B, int64_t L, void* stream);
+SPANON_API int spanon_conv1_bwd(const float* x, const float* gout, float* gw, float* gb, double* scratch, int64_t B, int64_t L,
+                     void* stream);
+/* stats [B][C][2] = per (utterance, channel) sum and sum of squares of x [B][rows][C] (C divides 256). */
+SPANON_API int spanon_colstats(const float* x, double* stats, int64_t B, int64_t rows, int64_t C, void* stream);
+/* out = act(gamma * (z - mean) * rstd + beta) from the sums in `stats`; per_batch = 0: InstanceNorm1d (statistics per
+ * utterance and channel, biased variance); per_batch = 1: BatchNorm1d in training mode (statistics per channel over the
+ * batch; running_mean / running_var updated in place with `momentum`, unbiased variance, when not NULL).
+ * act: 0 none, 1 SiLU ("GLU" of the reference).  gamma == NULL: no normalisation, out = act(z).
+ * save_mean / save_rstd ([B][C] or [C]) are kept for the backward pass. */
+SPANON_API int spanon_norm_act_fwd(const float* z, const double* stats, const float* gamma, const float* beta, int per_batch,
+                        int act, float eps, float* running_mean, float* running_var, float momentum, float* out,
+                        float* save_mean, float* save_rstd, int64_t B, int64_t rows, int64_t C, void* stream);
+/* gz = dL/dz, ggamma / gbeta (may be NULL).  relu_mask = 1: z is a stored ReLU output and gz is the gradient in FRONT of
+ * that ReLU (zero where z <= 0).  scratch: [B][C][2] fp64. */
+SPANON_API int spanon_norm_act_bwd(const float* z, const float* gout, const float* gamma, const float* beta, const float* save_mean,
+                        const float* save_rstd, int per_batch, int act, int relu_mask, float* gz, float* ggamma,
+                        float* gbeta, double* scratch, int64_t B, int64_t rows, int64_t C, void* stream);
+/* x [B][rows][128] channels-last -> out [B][256] = [mean + noise | unbiased std + 1e-5] over the columns of the reference's
+ * reshape(B, L, C) of the channels-first tensor; save [B][256] = [mean | std] for the backward; scratch [B][128][2] fp64. */
+SPANON_API int spanon_pool_reinterp_fwd(const float* x, const float* noise, float* out, float* save, double* scratch, int64_t B,
+                             int64_t rows, int64_t C, void* stream);
+SPANON_API int spanon_pool_reinterp_bwd(const float* x, const float* save, const float* gout, float* gx, int64_t B, int64_t rows,
+                             int64_t C, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Loss statistics
  * replaces  CosineSimilarityLoss.forward   utils/cosine_similarity_loss.py:53-56
  *           _pairwise_dists / ClusterMI._mutual_information  utils/ClusterMI.py:12-63,88-121

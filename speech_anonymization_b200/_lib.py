@@ -71,6 +71,11 @@ class ConvAEOpts(C.Structure):
                 ("weights_prepared", C.c_int32)]
 
 
+class TapConv(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32), ("k", C.c_int32), ("dilation", C.c_int32),
+                ("padding", C.c_int32)]
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 56), ("launches", C.c_uint64), ("ms_total", C.c_double)]
 
@@ -118,6 +123,25 @@ SIGNATURES = {
     "spanon_xvector_classify": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(XvectorWeights), C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int32,
                                           C.c_void_p]),
+    "spanon_tapconv_workspace_bytes": (C.c_size_t, [C.POINTER(TapConv)]),
+    "spanon_tapconv_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                     C.c_size_t, C.c_int64, C.c_int64, C.POINTER(TapConv), C.c_void_p]),
+    "spanon_tapconv_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_size_t, C.c_int64, C.c_int64, C.POINTER(TapConv), C.c_void_p]),
+    "spanon_conv1_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_conv1_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                   C.c_void_p]),
+    "spanon_colstats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_norm_act_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                      C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_norm_act_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_pool_reinterp_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                           C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_pool_reinterp_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                           C.c_int64, C.c_void_p]),
     "spanon_cosine_loss": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_float,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "spanon_cosine_loss_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,

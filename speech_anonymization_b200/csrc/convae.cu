@@ -14,6 +14,7 @@
 // Utterances are processed in chunks sized so that a layer's output is still in the 126 MB L2
 // when the next layer reads it.
 #include "tapgemm.cuh"
+#include "pack.cuh"
 #include <algorithm>
 #include <math.h>
 #include <stdlib.h>
@@ -23,31 +24,7 @@ int fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 
 namespace {
 
-// ------------------------------------------------------------------ weight packing
-enum PackMode { PACK_CONV_S1 = 0, PACK_CONV_S2 = 1, PACK_CONVT_S2 = 2, PACK_TOEPLITZ = 3, PACK_COMPOSED = 4 };
-
-// Source value of packed element (tap, civ, cov); cin/cout/k are the REAL layer sizes.
-__device__ __forceinline__ float packed_src(const float* __restrict__ w, int mode, int cin, int cout, int k,
-                                            int tap, int civ, int cov) {
-  if (mode == PACK_CONV_S1) {            // Conv1d weight [cout][cin][k]
-    if (cov >= cout) return 0.f;         // padded output channels (decoder.8)
-    return w[((int64_t)cov * cin + civ) * k + tap];
-  } else if (mode == PACK_CONV_S2) {     // input pair rows: civ = half*cin + ci, t = 2*tap + half
-    const int half = civ / cin, ci = civ - half * cin;
-    const int t = 2 * tap + half;
-    if (t >= k) return 0.f;
-    return w[((int64_t)cov * cin + ci) * k + t];
-  } else if (mode == PACK_TOEPLITZ) {    // Conv1d weight [1][cin][k] as a [cin] x [k taps (+ zero columns)] matrix
-    if (cov >= k) return 0.f;
-    return w[(int64_t)civ * k + cov];
-  } else {                               // ConvTranspose1d weight [cin][cout][k]; cov = phase*cout + co
-    const int phase = cov / cout, co = cov - phase * cout;
-    const int t = 4 - 2 * tap + phase;   // shifts -1,0,+1 <-> taps (4|-), (2|3), (0|1)
-    if (t >= k) return 0.f;
-    return w[((int64_t)civ * cout + co) * k + t];
-  }
-}
-
+// ------------------------------------------------------------------ weight packing (pack.cuh: PackMode, packed_src)
 // fp32 [ntaps][cin_v][cout_v]
 __global__ void pack_f32_kernel(const float* __restrict__ w, float* __restrict__ dst, int mode, int cin, int cout,
                                 int k, int ntaps, int cin_v, int cout_v) {

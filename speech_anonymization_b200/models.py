@@ -190,9 +190,22 @@ class ConvAutoencoder(nn.Module):
         top_db, T_pad): `input` is then RAW Fbank dB [B,T,F] and clamp + normalisation + zero padding to
         T_pad run inside the first layer's load (used by AnonymizerPipeline)."""
         _lib.require_cuda(input, "input")
-        _forward_only_guard(self, input)
         if input.dim() != 3:
             raise ValueError("ConvAutoencoder expects [batch, time, features]")
+        # TRAIN mode (batch-statistics BatchNorm in the sex classifier) or a graph is being recorded: the training kernels
+        # (fp32, with a backward pass; train.py).  Otherwise the inference kernels below.
+        bn_training = any(isinstance(m, nn.modules.batchnorm._BatchNorm) and m.training for m in self.modules())
+        wants_grad = torch.is_grad_enabled() and (input.requires_grad or any(p.requires_grad for p in self.parameters()))
+        if bn_training or wants_grad:
+            if not bn_training:
+                raise NotImplementedError("ConvAutoencoder: a backward pass through eval-mode BatchNorm is not built; call "
+                                          ".train() (the reference trains in TRAIN mode) or use torch.no_grad()")
+            if fused_norm is not None:
+                raise NotImplementedError("the fused normalisation load is an inference path; pass normalised features")
+            if (input.shape[1] * input.shape[2]) % 4 != 0:
+                raise RuntimeError("shape '[%d, %d, %d]' is invalid: time*features must be a multiple of 4" % tuple(input.shape))
+            from .train import convae_train_forward
+            return convae_train_forward(self, input.to(torch.float32).contiguous(), pool_noise)
         x = input.contiguous()
         B, T_in, F = x.shape
         T = T_in if fused_norm is None else int(fused_norm[4])

@@ -1,0 +1,170 @@
+"""GPU parity tests of the training step (scope rows f-1, a5-speaker): the training kernels (csrc/train.cu through
+speech_anonymization_b200/train.py's autograd nodes) against gradients the REFERENCE's own modules produced with torch
+autograd on CPU (tests/golden/make_golden_v3.py -> golden_v3.npz).
+
+Tolerances: outputs <= 1e-4 rel. (the fp32 bar of BASELINE.json); gradients <= 1e-3, measured per parameter as
+max|g - g_ref| / max|g_ref| (and on the gradient norms for the cases whose full gradients are not stored)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import recipe
+from conftest import GOLDEN_DIR, rel_max
+
+import speech_anonymization_b200 as sab
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+GRAD_TOL = 1e-3
+GRAD_FLOOR = 1e-5
+IN_BIASES = ("encoder.2.bias", "encoder.5.bias", "encoder.8.bias", "encoder.11.bias", "decoder.1.bias", "decoder.5.bias")
+TRAIN_CASES = {"train_a": (21, 8, 36, 1.0, 0.8), "train_b": (22, 6, 72, 0.5, 0.5), "train_c": (23, 4, 1008, 1.0, 0.8)}
+
+
+@pytest.fixture(scope="module")
+def golden3():
+    return dict(np.load(os.path.join(GOLDEN_DIR, "golden_v3.npz")))
+
+
+def cu(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).to(DEV)
+
+
+def build_model():
+    m = sab.ConvAutoencoder()
+    w = recipe.make_weights(recipe.CONVAE_SHAPES, 8886)
+    m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in w.items()})
+    return m.to(DEV).train()
+
+
+def labels_for(seed, B):
+    return torch.from_numpy((np.arange(B) + seed) % 2).long().to(DEV)
+
+
+@pytest.mark.parametrize("name", list(TRAIN_CASES))
+def test_train_step_gradients_vs_reference(golden3, name):
+    seed, B, T, w_rec, w_sex = TRAIN_CASES[name]
+    m = build_model()
+    x = cu(recipe.make_feats(seed, B, T))
+    rec, logp = m(x, pool_noise=cu(recipe.make_noise(seed, B, 128)))
+    assert rec.requires_grad and logp.requires_grad
+    recon_loss = torch.nn.MSELoss()(rec.view(B, -1), x.view(B, -1))
+    sex_loss = torch.nn.NLLLoss()(logp, labels_for(seed, B))
+    loss = w_rec * recon_loss + w_sex * sex_loss
+    loss.backward()
+    torch.cuda.synchronize()
+    ref_rec = golden3[name + "_recon"]
+    got_rec = rec.detach().cpu().numpy()
+    assert rel_max(got_rec if T <= 72 else got_rec[:, :8], ref_rec) < 1e-4
+    assert np.max(np.abs(logp.detach().cpu().numpy() - golden3[name + "_logp"])) < 1e-4
+    ref_losses = golden3[name + "_loss"]
+    assert abs(float(loss) - ref_losses[0]) < 1e-4 * max(1.0, abs(ref_losses[0]))
+    worst = (0.0, "")
+    grads = {k: p.grad.detach().cpu().numpy() for k, p in m.named_parameters()}
+    for k, p in m.named_parameters():
+        assert p.grad is not None, k
+        g = grads[k]
+        if k in IN_BIASES:
+            # A bias directly in front of an InstanceNorm has an EXACTLY zero gradient (the norm removes the mean again);
+            # the reference's values (~1e-8) and ours (the fp32 rounding of the saved mean times the row count) are both
+            # rounding noise: require "zero" relative to the layer's weight gradient instead of comparing noise with noise.
+            assert float(np.max(np.abs(g))) < 1e-3 * float(np.max(np.abs(grads[k.replace(".bias", ".weight")]))), k
+            continue
+        # (a bias in front of an InstanceNorm has an exactly zero gradient -- the norm removes the mean again --, the
+        # reference's ~1e-8 values are rounding noise: the denominators are floored at GRAD_FLOOR)
+        if name == "train_a":
+            ref = golden3["%s_grad:%s" % (name, k)]
+            err = float(np.max(np.abs(g - ref))) / max(float(np.max(np.abs(ref))), GRAD_FLOOR)
+        else:
+            # Gradient NORMS at the 1e-3 bar.  Individual elements are held to 3e-2 only: on 4 x 80 640-sample inputs a
+            # handful of ReLU gates in the TDNN sit within fp32 rounding of zero, and one gate that opens in the fp32
+            # forward but not in the reference's double-precision forward moves a bias gradient by that single element's
+            # gradient (measured: 2.5e-3 of a 3.3e-2 sum from ONE element; torch's own fp32 kernels flip 2 - 6 gates per
+            # layer on the same input).  tests/test_gpu_train_primitives.py holds every kernel to 2e-4 at these sizes.
+            gn = float(golden3["%s_gnorm:%s" % (name, k)])
+            err = abs(np.linalg.norm(g.astype(np.float64)) - gn) / max(gn, GRAD_FLOOR * np.sqrt(g.size))
+            head = float(np.max(np.abs(g.reshape(-1)[:64] - golden3["%s_ghead:%s" % (name, k)]))) / max(float(np.max(np.abs(g))), GRAD_FLOOR)
+            assert head < (GRAD_TOL if T <= 72 else 3e-2), (k, head)
+        worst = max(worst, (err, k))
+        assert err < GRAD_TOL, (k, err)
+    print("worst gradient error", worst)
+    if T <= 72:      # train-mode BatchNorm updates its running statistics like torch (momentum 0.1, unbiased variance)
+        for k, b in m.named_buffers():
+            if "running" in k:
+                assert rel_max(b.detach().cpu().numpy(), golden3["%s_buf:%s" % (name, k)]) < 1e-4, k
+            if k.endswith("num_batches_tracked"):
+                assert int(b) == 1
+
+
+def test_fit_batch_schedule_vs_reference(golden3):
+    """speechbrain_convae_train.py:195-259: even epochs train the autoencoder with the classifier frozen, odd epochs the
+    classifier alone; loss / gradient_accumulation, an optimizer step (after clipping at 5.0) every third batch."""
+    m = build_model()
+    opt = torch.optim.SGD(m.parameters(), lr=1e-2)
+    accum, losses = 3, []
+    for step in range(1, 7):
+        epoch = 0 if step <= 3 else 1
+        if epoch % 2 == 0:
+            w_rec, w_sex = 1.0, 0.8
+            for n, p in m.named_parameters():
+                p.requires_grad = "sex_classifier" not in n
+        else:
+            w_rec, w_sex = 0.0, 0.5
+            for n, p in m.named_parameters():
+                p.requires_grad = "sex_classifier" in n
+        B, T = 8, 36
+        x = cu(recipe.make_feats(100 + step, B, T))
+        rec, logp = m(x, pool_noise=cu(recipe.make_noise(100 + step, B, 128)))
+        loss = w_rec * torch.nn.MSELoss()(rec.view(B, -1), x.view(B, -1)) + w_sex * torch.nn.NLLLoss()(logp, labels_for(step, B))
+        (loss / accum).backward()
+        if step <= 3:      # frozen classifier: its weight-gradient kernels are not even launched
+            assert m.sex_classifier.tdnn[0].weight.grad is None and m.encoder[2].weight.grad is not None
+        if step % accum == 0:
+            torch.nn.utils.clip_grad_norm_((p for p in m.parameters()), 5.0)
+            opt.step()
+            opt.zero_grad()
+        losses.append(float(loss))
+    # (plain SGD, see make_golden_v3.py: the schedule is what is under test, not the optimizer)
+    dl = np.abs(np.array(losses) - golden3["fit_losses"]) / np.maximum(np.abs(golden3["fit_losses"]), 1.0)
+    assert dl[:3].max() < 1e-4 and dl.max() < 1e-3, dl
+    sd = m.state_dict()
+    for key in golden3:
+        if key.startswith("fit_param:"):
+            k = key[len("fit_param:"):]
+            assert rel_max(sd[k].detach().cpu().numpy(), golden3[key]) < 1e-3, k
+
+
+def test_train_mode_without_grad_and_eval_roundtrip():
+    """model.train() under no_grad still uses batch statistics (and updates the running ones); .eval() goes back to the
+    inference kernels and sees the updated buffers."""
+    m = build_model()
+    x = cu(recipe.make_feats(5, 2, 36))
+    noise = cu(recipe.make_noise(5, 2, 128))
+    before = m.sex_classifier.norm.running_mean.clone()
+    with torch.no_grad():
+        rec_t, logp_t = m(x, pool_noise=noise)
+    assert not rec_t.requires_grad and not torch.equal(before, m.sex_classifier.norm.running_mean)
+    m.eval()
+    m.precision = "fp32"
+    with torch.no_grad():
+        rec_e, logp_e = m(x, pool_noise=noise)
+    assert rel_max(rec_e.cpu().numpy(), rec_t.cpu().numpy()) < 1e-4      # the autoencoder has no BatchNorm
+    assert float((logp_e - logp_t).abs().max()) > 1e-6                   # the classifier does
+
+
+def test_input_normalization_speaker_vs_reference(golden3):
+    """processing/features.py:1031-1080 (norm_type="speaker"): per-speaker running statistics in train mode, stored
+    statistics (or the utterance's own for an unseen speaker) in eval mode."""
+    feats, feats2 = cu(recipe.make_feats(31, 4, 51)), cu(recipe.make_feats(32, 4, 51))
+    lens = cu(np.array([1.0, 0.8, 0.6, 0.9], np.float32))
+    n = sab.InputNormalization(norm_type="speaker").to(DEV)
+    n.train()
+    assert rel_max(n(feats.clone(), lens, spk_ids=torch.tensor([[3], [5], [3], [7]])).cpu().numpy(), golden3["spk_train_call1"]) < 1e-5
+    assert rel_max(n(feats2.clone(), lens, spk_ids=torch.tensor([[5], [5], [9], [3]])).cpu().numpy(), golden3["spk_train_call2"]) < 1e-5
+    assert rel_max(n.spk_dict_mean[3].cpu().numpy(), golden3["spk_mean_3"]) < 1e-5
+    assert rel_max(n.spk_dict_std[5].cpu().numpy(), golden3["spk_std_5"]) < 1e-5
+    assert [n.spk_dict_count[k] for k in (3, 5, 7, 9)] == golden3["spk_count"].tolist()
+    n.eval()
+    assert rel_max(n(feats.clone(), lens, spk_ids=torch.tensor([[3], [11], [9], [5]])).cpu().numpy(), golden3["spk_eval_call3"]) < 1e-5

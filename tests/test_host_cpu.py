@@ -185,3 +185,18 @@ def test_two_rank_gloo_sharding():
         p.join(timeout=120)
         assert p.exitcode == 0
     assert owned == [1.0] * 13 and tmax == 12.0
+
+
+def test_similarity_metrics_stats_vs_reference():
+    """utils/utility_similarity_aggregator.py:4-52 (golden_v3.npz: the reference class run by make_golden_v3.py)."""
+    g = dict(np.load(os.path.join(ROOT, "tests", "golden", "golden_v3.npz")))
+    scores = torch.from_numpy(g["sim_scores"])
+    st = sab.SimilarityMetricsStats()
+    st.append(scores[:5])
+    assert abs(float(st.peek()) - float(g["sim_peek1"])) < 1e-7
+    st.append(scores[5:])
+    assert abs(float(st.peek()) - float(g["sim_peek2"])) < 1e-7
+    assert abs(float(st.summarize()) - float(g["sim_summary"])) < 1e-7
+    assert st.summary["average"] == st.summarize()
+    st.clear()
+    assert st.scores == [] and st.denom == 0 and st.value == 0
