@@ -308,15 +308,21 @@ SPANON_API int spanon_colstats(const float* x, double* stats, int64_t B, int64_t
  * utterance and channel, biased variance); per_batch = 1: BatchNorm1d in training mode (statistics per channel over the
  * batch; running_mean / running_var updated in place with `momentum`, unbiased variance, when not NULL).
  * act: 0 none, 1 SiLU ("GLU" of the reference).  gamma == NULL: no normalisation, out = act(z).
- * save_mean / save_rstd ([B][C] or [C]) are kept for the backward pass. */
+ * save_mean / save_rstd ([B][C] or [C]) are kept for the backward pass.
+ * SyncBatchNorm (speechbrain/core.py:1156 converts the classifier's BatchNorms under DDP): `stats` then holds the sums of
+ * ALL ranks' utterances (all-gathered, stats_B rows) and stats_count their element count per channel; 0 / 0.0 = local. */
 SPANON_API int spanon_norm_act_fwd(const float* z, const double* stats, const float* gamma, const float* beta, int per_batch,
                         int act, float eps, float* running_mean, float* running_var, float momentum, float* out,
-                        float* save_mean, float* save_rstd, int64_t B, int64_t rows, int64_t C, void* stream);
+                        float* save_mean, float* save_rstd, int64_t B, int64_t rows, int64_t C, int64_t stats_B,
+                        double stats_count, void* stream);
 /* gz = dL/dz, ggamma / gbeta (may be NULL).  relu_mask = 1: z is a stored ReLU output and gz is the gradient in FRONT of
- * that ReLU (zero where z <= 0).  scratch: [B][C][2] fp64. */
+ * that ReLU (zero where z <= 0).  scratch: [B][C][2] fp64.
+ * phase 0: everything.  SyncBatchNorm: phase 1 = the two reductions (scratch[0][C][2] = this rank's sums, ggamma / gbeta
+ * written), the caller all-reduces scratch[0], phase 2 = the element-wise pass with count = the global element count. */
 SPANON_API int spanon_norm_act_bwd(const float* z, const float* gout, const float* gamma, const float* beta, const float* save_mean,
                         const float* save_rstd, int per_batch, int act, int relu_mask, float* gz, float* ggamma,
-                        float* gbeta, double* scratch, int64_t B, int64_t rows, int64_t C, void* stream);
+                        float* gbeta, double* scratch, int64_t B, int64_t rows, int64_t C, int phase, double count,
+                        void* stream);
 /* x [B][rows][128] channels-last -> out [B][256] = [mean + noise | unbiased std + 1e-5] over the columns of the reference's
  * reshape(B, L, C) of the channels-first tensor; save [B][256] = [mean | std] for the backward; scratch [B][128][2] fp64. */
 SPANON_API int spanon_pool_reinterp_fwd(const float* x, const float* noise, float* out, float* save, double* scratch, int64_t B,

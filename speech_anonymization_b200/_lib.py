@@ -134,10 +134,10 @@ SIGNATURES = {
     "spanon_colstats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "spanon_norm_act_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                       C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                                      C.c_int64, C.c_int64, C.c_void_p]),
+                                      C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_void_p]),
     "spanon_norm_act_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                       C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                                      C.c_int64, C.c_int64, C.c_void_p]),
+                                      C.c_int64, C.c_int64, C.c_int, C.c_double, C.c_void_p]),
     "spanon_pool_reinterp_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                            C.c_int64, C.c_int64, C.c_void_p]),
     "spanon_pool_reinterp_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,

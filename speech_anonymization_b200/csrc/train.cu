@@ -272,7 +272,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-
 // sums [B][C][2] (fp64) -> mean / rstd.  per_batch = 1: one (mean, rstd) per channel over all utterances (BatchNorm1d in
 // training mode, biased variance for the normalisation, UNBIASED for the running estimate, torch semantics), also updates
 // the running statistics;  per_batch = 0: per (utterance, channel) (InstanceNorm1d).
-__global__ void norm_finalize_kernel(const double* __restrict__ stats, int B, int C, double rows, float eps, int per_batch,
+__global__ void norm_finalize_kernel(const double* __restrict__ stats, int B, int C, double rows, double count, float eps, int per_batch,
                                      float* __restrict__ mean_out, float* __restrict__ rstd_out, float* __restrict__ running_mean,
                                      float* __restrict__ running_var, float momentum) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -287,7 +287,7 @@ __global__ void norm_finalize_kernel(const double* __restrict__ stats, int B, in
     if (i >= C) return;
     double s = 0.0, q = 0.0;
     for (int b = 0; b < B; ++b) { s += stats[2 * ((int64_t)b * C + i)]; q += stats[2 * ((int64_t)b * C + i) + 1]; }
-    const double n = rows * B, m = s / n;
+    const double n = count > 0.0 ? count : rows * B, m = s / n;   // count: elements per channel behind the sums (SyncBN)
     double var = q / n - m * m;
     if (var < 0.0) var = 0.0;
     mean_out[i] = (float)m;
@@ -678,7 +678,8 @@ extern "C" int spanon_colstats(const float* x, double* stats, int64_t B, int64_t
 
 extern "C" int spanon_norm_act_fwd(const float* z, const double* stats, const float* gamma, const float* beta, int per_batch,
                                    int act, float eps, float* running_mean, float* running_var, float momentum, float* out,
-                                   float* save_mean, float* save_rstd, int64_t B, int64_t rows, int64_t C, void* stream) {
+                                   float* save_mean, float* save_rstd, int64_t B, int64_t rows, int64_t C, int64_t stats_B,
+                                   double stats_count, void* stream) {
   if (B < 0 || rows <= 0 || C <= 0 || C % 4 != 0) return SPANON_ERR_BAD_SHAPE;
   if (B == 0) return SPANON_OK;
   if (!z || !out) return SPANON_ERR_NULL_POINTER;
@@ -686,8 +687,9 @@ extern "C" int spanon_norm_act_fwd(const float* z, const double* stats, const fl
   cudaStream_t st = as_stream(stream);
   if (gamma) {
     const int n = per_batch ? (int)C : (int)(B * C);
-    norm_finalize_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, st>>>(stats, (int)B, (int)C, (double)rows, eps, per_batch, save_mean,
-                                                                     save_rstd, running_mean, running_var, momentum);
+    if (stats_B <= 0 || !per_batch) { stats_B = B; stats_count = 0.0; }
+    norm_finalize_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, st>>>(stats, (int)stats_B, (int)C, (double)rows, stats_count, eps, per_batch,
+                                                                     save_mean, save_rstd, running_mean, running_var, momentum);
     SPANON_TRY(check_launch("train:norm_finalize"));
   }
   const int64_t total4 = B * rows * C / 4;
@@ -698,14 +700,16 @@ extern "C" int spanon_norm_act_fwd(const float* z, const double* stats, const fl
 
 extern "C" int spanon_norm_act_bwd(const float* z, const float* gout, const float* gamma, const float* beta, const float* save_mean,
                                    const float* save_rstd, int per_batch, int act, int relu_mask, float* gz, float* ggamma,
-                                   float* gbeta, double* scratch, int64_t B, int64_t rows, int64_t C, void* stream) {
+                                   float* gbeta, double* scratch, int64_t B, int64_t rows, int64_t C, int phase, double count,
+                                   void* stream) {
   if (B < 0 || rows <= 0 || C <= 0 || C % 4 != 0 || B > 65535) return SPANON_ERR_BAD_SHAPE;
   if (B == 0) return SPANON_OK;
   if (!z || !gout || !gz) return SPANON_ERR_NULL_POINTER;
   if (gamma && (!beta || !save_mean || !save_rstd || !scratch || C > 256 || 256 % C != 0)) return SPANON_ERR_NULL_POINTER;
   cudaStream_t st = as_stream(stream);
   const int sb = per_batch ? 0 : (int)C;
-  if (gamma) {
+  if (phase < 0 || phase > 2) return SPANON_ERR_UNSUPPORTED;
+  if (gamma && phase != 2) {
     SPANON_CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)B * C * 2 * sizeof(double), st));
     const int rpc = 2048;
     dim3 grid((unsigned)ceil_div(rows, rpc), (unsigned)B);
@@ -714,10 +718,11 @@ extern "C" int spanon_norm_act_bwd(const float* z, const float* gout, const floa
     norm_bwd_params_kernel<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(scratch, (int)B, (int)C, per_batch, ggamma, gbeta);
     SPANON_TRY(check_launch("train:norm_bwd_params"));
   }
+  if (phase == 1) return SPANON_OK;     // the caller all-reduces scratch[0][C][2] across ranks, then calls phase 2
   const int64_t total4 = B * rows * C / 4;
+  const double n = per_batch ? (count > 0.0 ? count : (double)(rows * B)) : (double)rows;
   norm_bwd_apply_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total4, 256), 148 * 16), 256, 0, st>>>(
-      z, gout, save_mean, save_rstd, sb, gamma, beta, act, scratch, per_batch ? 0 : (int)C, per_batch ? (double)(rows * B) : (double)rows,
-      relu_mask, gz, rows, (int)C, total4);
+      z, gout, save_mean, save_rstd, sb, gamma, beta, act, scratch, per_batch ? 0 : (int)C, n, relu_mask, gz, rows, (int)C, total4);
   return check_launch("train:norm_bwd_apply");
 }
 

@@ -205,7 +205,8 @@ class ConvAutoencoder(nn.Module):
             if (input.shape[1] * input.shape[2]) % 4 != 0:
                 raise RuntimeError("shape '[%d, %d, %d]' is invalid: time*features must be a multiple of 4" % tuple(input.shape))
             from .train import convae_train_forward
-            return convae_train_forward(self, input.to(torch.float32).contiguous(), pool_noise)
+            return convae_train_forward(self, input.to(torch.float32).contiguous(), pool_noise,
+                                        on_encoder_grad=self.__dict__.get("_on_encoder_grad"))
         x = input.contiguous()
         B, T_in, F = x.shape
         T = T_in if fused_norm is None else int(fused_norm[4])

@@ -108,27 +108,39 @@ class _Conv1(torch.autograd.Function):
 
 class _NormAct(torch.autograd.Function):
     """InstanceNorm1d(affine) (per_batch = 0) or train-mode BatchNorm1d (per_batch = 1) from the producer's sums, then
-    SiLU (act = 1) or nothing; gamma None: activation only (spanon_norm_act_fwd / _bwd)."""
+    SiLU (act = 1) or nothing; gamma None: activation only (spanon_norm_act_fwd / _bwd).
+    `group` (per_batch only): a torch.distributed process group -> SyncBatchNorm semantics (speechbrain/core.py:1156,
+    `SyncBatchNorm.convert_sync_batchnorm` under DDP): the per-utterance sums are all-gathered in the forward, the two
+    backward sums all-reduced, so the statistics are those of the GLOBAL batch.  Ranks must hold equal batch shapes."""
 
     @staticmethod
-    def forward(ctx, z, stats, gamma, beta, per_batch, act, relu_mask, running_mean, running_var, momentum, eps):
+    def forward(ctx, z, stats, gamma, beta, per_batch, act, relu_mask, running_mean, running_var, momentum, eps, group):
         L = _lib.lib()
         B, rows, Cc = z.shape
         dev = z.device
         out = torch.empty_like(z)
+        stats_B, count, world = 0, 0.0, 1
         if gamma is not None:
             n_stat = Cc if per_batch else B * Cc
             mean = torch.empty((n_stat,), dtype=torch.float32, device=dev)
             rstd = torch.empty((n_stat,), dtype=torch.float32, device=dev)
+            if per_batch and group is not None:
+                import torch.distributed as dist
+                world = dist.get_world_size(group)
+                if world > 1:
+                    gathered = torch.empty((world * B, Cc, 2), dtype=torch.float64, device=dev)
+                    dist.all_gather_into_tensor(gathered, stats.contiguous(), group=group)
+                    stats, stats_B, count = gathered, world * B, float(world * B * rows)
         else:
             mean = rstd = None
         with torch.cuda.device(dev):
             _call(L.spanon_norm_act_fwd, _lib.ptr(z), _lib.ptr(stats) if gamma is not None else None, _lib.ptr(gamma),
                   _lib.ptr(beta), int(per_batch), int(act), float(eps), _lib.ptr(running_mean), _lib.ptr(running_var),
-                  float(momentum), _lib.ptr(out), _lib.ptr(mean), _lib.ptr(rstd), B, rows, Cc, _lib.stream_ptr(dev),
-                  what="norm_act_fwd")
+                  float(momentum), _lib.ptr(out), _lib.ptr(mean), _lib.ptr(rstd), B, rows, Cc, stats_B, count,
+                  _lib.stream_ptr(dev), what="norm_act_fwd")
         ctx.save_for_backward(z, gamma, beta, mean, rstd)
         ctx.cfg = (int(per_batch), int(act), int(relu_mask))
+        ctx.group, ctx.world = (group if world > 1 else None), world
         return out
 
     @staticmethod
@@ -144,11 +156,20 @@ class _NormAct(torch.autograd.Function):
         gg = torch.empty((Cc,), dtype=torch.float32, device=dev) if has and ctx.needs_input_grad[2] else None
         gbeta = torch.empty((Cc,), dtype=torch.float32, device=dev) if has and ctx.needs_input_grad[3] else None
         scratch = torch.empty((B, Cc, 2), dtype=torch.float64, device=dev) if has else None
-        with torch.cuda.device(dev):
-            _call(L.spanon_norm_act_bwd, _lib.ptr(z), _lib.ptr(gout), _lib.ptr(gamma), _lib.ptr(beta), _lib.ptr(mean),
-                  _lib.ptr(rstd), per_batch, act, relu_mask, _lib.ptr(gz), _lib.ptr(gg), _lib.ptr(gbeta), _lib.ptr(scratch),
-                  B, rows, Cc, _lib.stream_ptr(dev), what="norm_act_bwd")
-        return gz, None, gg, gbeta, None, None, None, None, None, None, None
+
+        def run(phase, count):
+            with torch.cuda.device(dev):
+                _call(L.spanon_norm_act_bwd, _lib.ptr(z), _lib.ptr(gout), _lib.ptr(gamma), _lib.ptr(beta), _lib.ptr(mean),
+                      _lib.ptr(rstd), per_batch, act, relu_mask, _lib.ptr(gz), _lib.ptr(gg), _lib.ptr(gbeta),
+                      _lib.ptr(scratch), B, rows, Cc, phase, count, _lib.stream_ptr(dev), what="norm_act_bwd")
+        if ctx.group is None:
+            run(0, 0.0)
+        else:       # SyncBatchNorm: this rank's two sums -> all-reduce -> element-wise pass with the global count
+            import torch.distributed as dist
+            run(1, 0.0)
+            dist.all_reduce(scratch[0], group=ctx.group)
+            run(2, float(ctx.world * B * rows))
+        return gz, None, gg, gbeta, None, None, None, None, None, None, None, None
 
 
 class _PoolReinterp(torch.autograd.Function):
@@ -200,21 +221,71 @@ def _conv(x, m, kind, relu=0, want_stats=False):
 
 
 def _inorm_silu(z, stats, m):
-    return _NormAct.apply(z, stats, m.weight, m.bias, 0, 1, 0, None, None, 0.0, m.eps)
+    return _NormAct.apply(z, stats, m.weight, m.bias, 0, 1, 0, None, None, 0.0, m.eps, None)
 
 
-def _bnorm(z, stats, m, relu_mask):
+def _bnorm(z, stats, m, relu_mask, group=None):
     """train-mode BatchNorm1d on a channels-last tensor (running statistics and num_batches_tracked updated like torch)."""
     if m.momentum is None:
         raise NotImplementedError("BatchNorm1d(momentum=None) (cumulative average) is not used by the reference models")
     out = _NormAct.apply(z, stats, m.weight, m.bias, 1, 0, relu_mask, m.running_mean if m.track_running_stats else None,
-                         m.running_var if m.track_running_stats else None, m.momentum, m.eps)
+                         m.running_var if m.track_running_stats else None, m.momentum, m.eps, group)
     if m.track_running_stats and m.num_batches_tracked is not None:
         m.num_batches_tracked.add_(1)
     return out
 
 
-def convae_train_forward(model, feats, pool_noise=None, _taps=None):
+def _classify_head(classify, pooled, group):
+    """The three-layer head on the pooled [B, 256] statistics (ConvAutoEncoder.py:47-55).  With a process group its two
+    BatchNorm1d layers use global-batch statistics like the SyncBatchNorm the reference's DDP wrap converts them to."""
+    if group is None:
+        return classify(pooled)
+    import torch.distributed as dist
+    if dist.get_world_size(group) == 1:
+        return classify(pooled)
+    x = pooled
+    for m in classify:
+        if isinstance(m, torch.nn.BatchNorm1d):
+            x = _sync_bn_rows(x, m, group)
+        else:
+            x = m(x)
+    return x
+
+
+class _AllReduceSum(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, group):
+        import torch.distributed as dist
+        ctx.group = group
+        y = x.clone()
+        dist.all_reduce(y, group=group)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        import torch.distributed as dist
+        g = g.clone()
+        dist.all_reduce(g, group=ctx.group)
+        return g, None
+
+
+def _sync_bn_rows(x, m, group):
+    """train-mode BatchNorm1d on [B, C] rows with the statistics of all ranks' rows (tiny: B x 128 values)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    n = x.shape[0] * world
+    s = _AllReduceSum.apply(torch.stack((x.sum(0), (x * x).sum(0))), group)
+    mean = s[0] / n
+    var = (s[1] / n - mean * mean).clamp_min(0.0)
+    if m.track_running_stats:
+        with torch.no_grad():
+            m.running_mean.mul_(1 - m.momentum).add_(m.momentum * mean)
+            m.running_var.mul_(1 - m.momentum).add_(m.momentum * var * n / max(n - 1, 1))
+            m.num_batches_tracked.add_(1)
+    return (x - mean) * torch.rsqrt(var + m.eps) * m.weight + m.bias
+
+
+def convae_train_forward(model, feats, pool_noise=None, _taps=None, on_encoder_grad=None):
     """ConvAutoencoder.forward in TRAIN mode (batch-statistics BatchNorm in the sex classifier) with a backward pass.
     feats [B, T, F] fp32 CUDA -> (reconstruction [B, T, F], sex log-probs [B, 2]), both attached to the autograd graph."""
     from .models import GradReverse
@@ -224,7 +295,7 @@ def convae_train_forward(model, feats, pool_noise=None, _taps=None):
     x = feats.reshape(B, Lf).contiguous()
     # ---- encoder (models/ConvAutoEncoder.py:141-157)
     z = _Conv1.apply(x, e[0].weight, e[0].bias)
-    a = _NormAct.apply(z, None, None, None, 0, 1, 0, None, None, 0.0, 0.0)          # GLU = x * sigmoid(x)
+    a = _NormAct.apply(z, None, None, None, 0, 1, 0, None, None, 0.0, 0.0, None)    # GLU = x * sigmoid(x)
     z, st = _conv(a, e[2], 1, want_stats=True)
     a = _inorm_silu(z, st, e[3])
     z, st = _conv(a, e[5], 0, want_stats=True)
@@ -234,19 +305,23 @@ def convae_train_forward(model, feats, pool_noise=None, _taps=None):
     z, st = _conv(a, e[11], 0, want_stats=True)
     enc = _inorm_silu(z, st, e[12])                                                    # [B, L/4, 128]
     # ---- adversarial sex classifier (:57-69): GradReverse -> BatchNorm -> 3 x (conv, ReLU, BatchNorm) -> pooling -> MLP
+    group = getattr(model, "sync_bn_group", None)      # set by distributed.DataParallelTrainer (SyncBatchNorm under DDP)
+    if on_encoder_grad is not None and enc.requires_grad:
+        # fires when both branches' gradients have reached the bottleneck: every decoder / classifier gradient is final
+        enc.register_hook(lambda g: (on_encoder_grad(), g)[1])
     c = GradReverse.apply(enc)
-    c = _bnorm(c, colstats(c.detach()), s.norm, 0)
+    c = _bnorm(c, colstats(c.detach()), s.norm, 0, group)
     if _taps is not None:      # (debugging aid: intermediate tensors, channels-last)
         _taps["enc"], _taps["norm"] = enc, c
     for i in (0, 3, 6):
         r, st = _conv(c, s.tdnn[i], 0, relu=1, want_stats=True)
-        c = _bnorm(r, st, s.tdnn[i + 2], 1)
+        c = _bnorm(r, st, s.tdnn[i + 2], 1, group)
         if _taps is not None:
             _taps["relu%d" % i], _taps["bn%d" % (i + 2)] = r, c
     if pool_noise is None:
         pool_noise = s.stats_pooling._get_gauss_noise((B, 128), device=feats.device)
     pooled = _PoolReinterp.apply(c, pool_noise.to(device=feats.device, dtype=torch.float32).contiguous())
-    logp = F.log_softmax(s.classify(pooled), 1)
+    logp = F.log_softmax(_classify_head(s.classify, pooled, group), 1)
     # ---- decoder (:160-172)
     z, _ = _conv(enc, d[0], 0)
     z, st = _conv(z, d[1], 2, want_stats=True)

@@ -200,3 +200,68 @@ def test_similarity_metrics_stats_vs_reference():
     assert st.summary["average"] == st.summarize()
     st.clear()
     assert st.scores == [] and st.denom == 0 and st.value == 0
+
+
+def _dp_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+
+    class Toy(torch.nn.Module):     # parameter names like the ConvAutoencoder's: "encoder.*" is final last in backward
+        def __init__(self):
+            super().__init__()
+            self.encoder = torch.nn.Linear(4, 4)
+            self.decoder = torch.nn.Linear(4, 2)
+
+        def forward(self, x, hook=None):
+            h = torch.tanh(self.encoder(x))
+            if hook is not None:
+                h.register_hook(lambda g: (hook(), g)[1])
+            return self.decoder(h)
+    m = Toy()
+    from speech_anonymization_b200.distributed import DataParallelTrainer, gather_for_mi
+    dp = DataParallelTrainer(m, sync_bn=False)
+    assert dp.grads.n_early == 4 * 2 + 2 and dp.grads.n_total == 30      # decoder first, then the encoder
+    g = torch.Generator().manual_seed(5)
+    xs = torch.randn(3, 2 * world, 4, generator=g)
+    dp.prepare()
+    fired = []
+    for i in range(3):                              # two accumulation micro-batches without communication, then one with
+        x = xs[i, rank * 2:(rank + 1) * 2]
+        with (dp.no_sync() if i < 2 else __import__("contextlib").nullcontext()):
+            (m(x, hook=lambda: (fired.append(i), dp._on_encoder_grad())).pow(2).mean() / 3).backward()
+            dp.finish_backward()
+    got = dp.grads.flat.clone()
+    ref = Toy()
+    ref.load_state_dict(m.state_dict())
+    for i in range(3):
+        (ref(xs[i]).pow(2).mean() / 3).backward()    # mean over the global batch == average of the ranks' means
+    want = torch.cat([ref.decoder.weight.grad.reshape(-1), ref.decoder.bias.grad.reshape(-1),
+                      ref.encoder.weight.grad.reshape(-1), ref.encoder.bias.grad.reshape(-1)])
+    m.encoder.weight.requires_grad = False           # the reference's freeze schedule: a frozen parameter has grad None
+    dp.zero_grad()
+    X, y = gather_for_mi(torch.full((2, 3), float(rank)), torch.full((2,), rank))
+    q.put((rank, float((got - want).abs().max()), fired, m.encoder.weight.grad is None, m.decoder.weight.grad is not None,
+           float(dp.grads.flat.abs().max()), X[:, 0].tolist(), y.tolist()))
+    dist.destroy_process_group()
+
+
+def test_data_parallel_trainer_gloo_world2():
+    """Host logic of the training collectives on CPU (gloo, world size 2): flat gradient buffer, accumulation without
+    communication, early bucket on the bottleneck hook, averaged gradients == global-batch gradients, freeze handling,
+    MI gather."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29400 + os.getpid() % 500
+    procs = [ctx.Process(target=_dp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    for rank, err, fired, frozen_none, dec_has, flat_max, Xcol, y in res:
+        assert err < 1e-6, err
+        assert fired == [0, 1, 2] and frozen_none and dec_has and flat_max == 0.0
+        assert Xcol == [0.0, 0.0, 1.0, 1.0] and y == [0, 0, 1, 1]
