@@ -37,7 +37,8 @@ def parse():
     ap.add_argument("--ramp-seconds", type=float, default=0.5, help="untimed pre-warm before the warm-up steps")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="convae", choices=["convae", "fcae"])
+    ap.add_argument("--workload", default="convae", choices=["convae", "fcae", "train"])
+    ap.add_argument("--train-batch", type=int, default=8, help="utterances per GPU and training step (BASELINE configs[3])")
     ap.add_argument("--batch", type=int, default=60)
     ap.add_argument("--pool", type=int, default=360)
     ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"])
@@ -431,6 +432,7 @@ def run_ours(a):
         extras = time_extras(sab, _lib, recipe, dev, B, T)
         extras["library_gpu_convae_fwd"] = time_library_gpu(recipe, dev, B, T)
         extras.update(time_config_lines(sab, _lib, recipe, dev, dev_pool, pk))
+        extras["config3_train_step_b8"] = time_train_steps(sab, recipe, dev, 1, 8, 5, 3, host_pool)
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -633,8 +635,102 @@ def workload_config(a, world):
             "launch": "direct kernel launches" if getattr(a, "no_graphs", False) else "one CUDA graph replay per step (device arm)"}
 
 
+# --------------------------------------------------------------------------- training step (BASELINE configs[3])
+def time_train_steps(sab, recipe, dev, world, B, steps, warmup, host_pool):
+    """One step = speechbrain_convae_train.py:195-259 on B x 10 s utterances per GPU: Fbank -> normalise -> pad ->
+    ConvAutoencoder in TRAIN mode -> recon (MSE) + sex (NLL) + cosine-similarity losses, backward on the training kernels,
+    flat gradient all-reduce (+ SyncBatchNorm statistics) over NCCL, Adam step; the kNN-MI statistic of the batch's
+    (gathered) sex log-probabilities is computed alongside (the reference's MI term is not differentiable)."""
+    pipe = build_pipeline("convae", "fp32", dev)
+    model = pipe.model.train()
+    dp = sab.DataParallelTrainer(model)
+    dp.prepare()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    cos = sab.CosineSimilarityLoss()
+    n_b = host_pool.shape[0] // B
+    pool = host_pool[:n_b * B].to(dev)
+    T = 1 + N_SAMPLES // 160
+    lens = torch.ones(B, device=dev)
+    noise = torch.from_numpy(recipe.make_noise(11, B, 128)).to(dev)
+    y = (torch.arange(B, device=dev) % 2).long()
+    ev = []
+
+    def step(i):
+        wav = pool[(i % n_b) * B:(i % n_b + 1) * B]
+        with torch.no_grad():                                     # compute_forward :58-63 (features carry no graph)
+            feats = sab.pad_time(pipe.normalize(pipe.compute_features(wav), lens))
+        rec, logp = model(feats, pool_noise=noise)
+        loss = (torch.nn.functional.mse_loss(rec.view(B, -1), feats.view(B, -1)) + 0.8 * torch.nn.functional.nll_loss(logp, y)
+                + 0.2 * cos(rec, feats) / B)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        loss.backward()
+        e0.record()
+        dp.finish_backward()                                      # waits for the early bucket, all-reduces the encoder's
+        e1.record()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)   # core.py check_gradients
+        opt.step()
+        dp.zero_grad()
+        Xg, yg = sab.gather_for_mi(logp.detach(), y)              # MI statistic of the global batch
+        mi = sab.knn_mi(Xg, yg, k=3)[0] if Xg.shape[0] >= 8 else None
+        e2.record()
+        ev.append((e0, e1))
+        return loss, mi
+
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    barrier(world)
+    torch.cuda.synchronize()
+    ev.clear()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(steps):
+        loss, mi = step(warmup + i)
+    t1.record()
+    torch.cuda.synchronize()
+    ms = max_over_ranks(t0.elapsed_time(t1), world, dev) / steps
+    comm = sum(a_.elapsed_time(b_) for a_, b_ in ev) / steps
+    return {"ms_per_step": ms, "batch_per_gpu": B, "audio_s_per_s": world * B * UTT_SECONDS / (ms * 1e-3),
+            "exposed_allreduce_ms_per_step": comm, "allreduce_share": comm / ms, "gradient_bytes": dp.grads.n_total * 4,
+            "early_bucket_bytes": dp.grads.n_early * 4, "final_loss": float(loss),
+            "dtype": "fp32", "what": "Fbank + normalise + pad + ConvAutoencoder TRAIN forward/backward (csrc/train.cu), recon + sex + "
+                                     "cosine losses, flat-gradient all-reduce + SyncBatchNorm over NCCL, clip, Adam"}
+
+
+def run_train(a):
+    import recipe
+    import speech_anonymization_b200 as sab
+    world, rank, local = dist_setup(a.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a CUDA device: there is no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    B = a.train_batch
+    host_pool = make_wavs(max(B, 4 * B), 1234 + rank)
+    sampler = ClockSampler(local)
+    sampler.start()
+    r = time_train_steps(sab, recipe, dev, world, B, a.steps, max(a.warmup, 3), host_pool)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    if rank == 0:
+        line = {"metric": "audio-sec/sec trained (Fbank+ConvAE training step)", "value": r["audio_s_per_s"], "unit": "audio-s/s",
+                "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+                "config": {"workload": "training step, %d x 10 s @16 kHz utterances per GPU (BASELINE configs[3]), data-parallel "
+                                       "x%d with NCCL gradient all-reduce" % (B, world), "batch_per_gpu": B,
+                           "parallelism": "data-parallel x%d" % world, "weights": "random-init seed 8886",
+                           "l2": "per-step working set (saved activations) %.1f GB > L2" % (B * 80640 * 32 * 4 * 20 / 1e9)},
+                "clocks": sampler.summary(), "train": r, "gpu_launches": None, "e2e": None, "roofline": None, "cpu_baseline": None}
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 # --------------------------------------------------------------------------- reference arm
 def run_reference(a):
+    if a.workload == "train":
+        a.workload = "convae"     # the CPU arm times the forward path
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
@@ -666,5 +762,7 @@ if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "train":
+        run_train(args)
     else:
         run_ours(args)
