@@ -24,6 +24,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 
 SAMPLE_RATE, N_SAMPLES, UTT_SECONDS = 16000, 160000, 10.0
+HOST_PLACEMENT = None
 # algorithmic work per 10 s utterance
 FLOP_CONVAE_UTT = 22.28e9          # 15.02 GFLOP autoencoder + 7.26 GFLOP TDNN classifier
 BYTES_FBANK_UTT = 960320           # 640000 B PCM in + 320320 B features out
@@ -187,10 +188,37 @@ def convae_layer_flops(L=80640):
     return {k: 2.0 * v for k, v in mac.items()}
 
 
+def bind_rank_to_cores(local, n_local):
+    """Host-side placement for the end-to-end arm: every rank streams tens of MB per step through pinned host buffers, so
+    the rank's thread (and, by first touch, its pinned pages) go onto a core set of its own inside the GPU's NUMA-local
+    CPU set instead of all ranks sharing (and migrating over) one affinity mask.  Returns a description or None."""
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+        near = allowed
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(allowed) // 64) + 1)
+            mask = [c for c in allowed if (words[c // 64] >> (c % 64)) & 1]
+            if len(mask) >= n_local:
+                near = mask
+        except Exception:
+            pass
+        per = max(1, len(near) // max(n_local, 1))
+        mine = near[local * per:(local + 1) * per] or near
+        os.sched_setaffinity(0, set(mine))
+        return {"cores": [mine[0], mine[-1]], "numa_local_set": len(near), "allowed": len(allowed)}
+    except Exception as e:      # (not fatal: placement is an optimisation)
+        return {"error": str(e)[:80]}
+
+
 def dist_setup(n_gpus):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    global HOST_PLACEMENT
+    HOST_PLACEMENT = bind_rank_to_cores(local, int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))) if world > 1 else None
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -331,22 +359,38 @@ def run_ours(a):
     # two batches are in flight so those copies overlap the kernels of the neighbouring step. The one-shot
     # synchronous call (spanon_anonymize_host) is timed next to it.
     depth = 2
-    rec_h = [torch.empty((B, Tp, 80), dtype=torch.float32).pin_memory() for _ in range(depth + 1)]
     logp_h = [torch.empty((B, 2), dtype=torch.float32).pin_memory() for _ in range(depth + 1)]
-    sp = pipe.stream_pipe(B, N_SAMPLES, dev, depth=depth)
-    for i in range(a.warmup):
-        sp.submit(host_pool[(i % n_batches) * B:(i % n_batches + 1) * B], rec_h[i % (depth + 1)], logp_h[i % (depth + 1)],
-                  pool_noise=noise)
-    sp.drain()
-    barrier(world)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for i in range(a.steps):
-        k = (a.warmup + i) % n_batches
-        sp.submit(host_pool[k * B:(k + 1) * B], rec_h[i % (depth + 1)], logp_h[i % (depth + 1)], pool_noise=noise)
-    sp.drain()
-    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev) / a.steps
-    sp.close()
+
+    def time_pipe(pool_h, out_dtype):
+        """Streaming host-buffer arm: `pool_h` pinned PCM (fp32 or int16), reconstruction returned as `out_dtype`."""
+        rec_h = [torch.empty((B, Tp, 80), dtype=out_dtype).pin_memory() for _ in range(depth + 1)]
+        if a.workload == "convae":
+            pipe.model.recon_fp16 = out_dtype == torch.float16
+        sp = pipe.stream_pipe(B, N_SAMPLES, dev, depth=depth)
+        for i in range(a.warmup):
+            sp.submit(pool_h[(i % n_batches) * B:(i % n_batches + 1) * B], rec_h[i % (depth + 1)], logp_h[i % (depth + 1)],
+                      pool_noise=noise)
+        sp.drain()
+        barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(a.steps):
+            k = (a.warmup + i) % n_batches
+            sp.submit(pool_h[k * B:(k + 1) * B], rec_h[i % (depth + 1)], logp_h[i % (depth + 1)], pool_noise=noise)
+        sp.drain()
+        ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev) / a.steps
+        sp.close()
+        if a.workload == "convae":
+            pipe.model.recon_fp16 = False
+        return ms, rec_h
+
+    # headline e2e: the audio file's own sample format in (int16 PCM, converted by the Fbank kernel exactly like the
+    # reference's read_audio does on the host) and, for the 16-bit ConvAutoencoder mode, its fp16 reconstruction out;
+    # the fp32-in / fp32-out wire of the reference's tensors is timed next to it
+    host_pool16 = torch.clamp(torch.round(host_pool * 32768.0), -32768, 32767).to(torch.int16).pin_memory()
+    out16 = a.workload == "convae" and a.precision == "fp16"
+    ms_e2e, rec_h = time_pipe(host_pool16, torch.float16 if out16 else torch.float32)
+    ms_e2e_f32, rec_h = time_pipe(host_pool, torch.float32)
     ws = pipe.host_workspace(B, N_SAMPLES, dev)
     pipe.anonymize_host(host_pool[:B], rec_h[0], logp_h[0], ws, pool_noise=noise)
     torch.cuda.synchronize()
@@ -360,9 +404,14 @@ def run_ours(a):
     sampler.join(timeout=2)
     gc.enable()
     e2e = {"value": world * B * UTT_SECONDS / (ms_e2e * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_e2e,
-           "h2d_bytes_per_step": B * N_SAMPLES * 4, "d2h_bytes_per_step": B * Tp * 80 * 4 + B * 8,
-           "api": "spanon_pipe_submit/wait (pinned host buffers in/out, %d batches in flight over H2D|kernel|D2H streams)" % depth,
+           "h2d_bytes_per_step": B * N_SAMPLES * 2, "d2h_bytes_per_step": B * Tp * 80 * (2 if out16 else 4) + B * 8,
+           "wire": "int16 PCM in, %s features out" % ("fp16" if out16 else "fp32"),
+           "api": "spanon_pipe_submit_i16/wait (pinned host buffers in/out, %d batches in flight over H2D|kernel|D2H streams)" % depth,
            "timer": "host wall clock between synchronisation points, max over ranks",
+           "host_placement": HOST_PLACEMENT,
+           "fp32_wire": {"api": "spanon_pipe_submit (fp32 PCM in, fp32 features out)", "ms_per_step": ms_e2e_f32,
+                         "value": world * B * UTT_SECONDS / (ms_e2e_f32 * 1e-3), "h2d_bytes_per_step": B * N_SAMPLES * 4,
+                         "d2h_bytes_per_step": B * Tp * 80 * 4 + B * 8},
            "one_shot_sync_call": {"api": "spanon_anonymize_host", "ms_per_step": ms_sync,
                                   "value": world * B * UTT_SECONDS / (ms_sync * 1e-3)}}
 

@@ -207,6 +207,9 @@ typedef struct SpanonConvAEOpts {
   int32_t skip_classifier;/* 1 = do not run the sex classifier (logp untouched)                */
   int32_t weights_prepared;/* 1 = `workspace` still holds the packed weights / folded BatchNorms written by an earlier
                              call with the same workspace, weights, B, T, F and opts: skip the per-call preparation */
+  int32_t recon_fp16;     /* 1 (SPANON_PREC_FP16 ConvAutoencoder only): `recon` (and `recon_host` of the host-buffer /
+                             pipe entry points) is an IEEE half buffer, B*T*F*2 bytes, passed through the float* argument:
+                             the 16-bit mode's own precision on the wire, half the device-to-host bytes (ABI v3) */
 } SpanonConvAEOpts;
 
 SPANON_API size_t spanon_convae_workspace_bytes(int64_t B, int64_t T, int64_t F, const SpanonConvAEOpts* opts);

@@ -68,7 +68,7 @@ class XvectorWeights(C.Structure):
 
 class ConvAEOpts(C.Structure):
     _fields_ = [("precision", C.c_int32), ("chunk_utts", C.c_int32), ("skip_classifier", C.c_int32),
-                ("weights_prepared", C.c_int32)]
+                ("weights_prepared", C.c_int32), ("recon_fp16", C.c_int32)]
 
 
 class TapConv(C.Structure):

@@ -88,7 +88,7 @@ extern "C" const char* spanon_strerror(int status) {
     default: return "unknown status";
   }
 }
-extern "C" int spanon_abi_version(void) { return 2; }
+extern "C" int spanon_abi_version(void) { return 3; }
 extern "C" uint64_t spanon_launch_count(void) { return spanon::g_launch_count.load(); }
 extern "C" const char* spanon_last_cuda_error(void) {
   static thread_local std::string copy;

@@ -621,7 +621,8 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
           float acc = bias0;
 #pragma unroll
           for (int t = 0; t < TC_TOEP_TAPS; ++t) acc += d[(mloc + t) * 17 + t];
-          reinterpret_cast<float*>(p.out)[(int64_t)b * p.out_bstride + m] = acc;
+          if (p.out_half) reinterpret_cast<__half*>(p.out)[(int64_t)b * p.out_bstride + m] = __float2half_rn(acc);
+          else reinterpret_cast<float*>(p.out)[(int64_t)b * p.out_bstride + m] = acc;
         }
       }
     } else {

@@ -767,6 +767,7 @@ struct LayerIO {
   const float* t1s = nullptr;        // tcgen05 path: per-channel affine on load (overrides in_norm), e.g. the
   const float* t1h = nullptr;        //   producer's bias as (ones, bias)
   int act = -1;                      // activation on load (TapGemmParams::silu); -1 = SiLU iff in_norm >= 0
+  int out_half = 0;                  // tcgen05 path, OUT_CH0_F32: fp16 output (recon_fp16)
   const TapGemmParams* gen = nullptr; // tcgen05 path: gen_* fields of a launch that generates its input (encoder.0 fused)
 };
 
@@ -807,6 +808,7 @@ TapGemmParams make_params(const Ctx& c, int id, const LayerIO& io, int nb) {
   p.out_fold = io.out_fold;
   p.out_plane_rows = io.out_fold == OUT_PAIR_FOLD ? p.rows_out / 2 : io.out_fold == OUT_PHASE_UNFOLD ? p.rows_out * 2 : p.rows_out;
   p.in_planar = c.tc ? 1 : 0;
+  p.out_half = io.out_half;
   if (io.gen) {
     p.gen_feats = io.gen->gen_feats; p.gen_bstride = io.gen->gen_bstride; p.gen_nvalid = io.gen->gen_nvalid;
     p.gen_F = io.gen->gen_F; p.gen_mean = io.gen->gen_mean; p.gen_std = io.gen->gen_std; p.gen_umax = io.gen->gen_umax;
@@ -911,6 +913,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   if (!fused_norm) T_valid = T;
   if (T_valid < 0 || T_valid > T) return SPANON_ERR_BAD_SHAPE;
   const bool run_clf = logp != nullptr && !(opts && opts->skip_classifier);
+  const bool recon_half = opts && opts->recon_fp16;
+  if (recon_half && (!opts || opts->precision != SPANON_PREC_FP16)) return SPANON_ERR_UNSUPPORTED;   // the 16-bit mode's output
   if (run_clf && L / 4 < 16) return SPANON_ERR_BAD_SHAPE;  // TDNN (k5, k3 d2, k3 d3) needs >= 15 rows
   Ctx c{};
   int chunk;
@@ -1087,7 +1091,11 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
                                        OUT_PHASE_UNFOLD}, nb));
       SPANON_TRY(finalize_in(c, L_DEC5, 5, w->dec_in_w[1], w->dec_in_b[1], nb, (double)L));
     }
-    SPANON_TRY(run_layer(c, L_DEC8, {X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32}, nb));
+    {
+      LayerIO d8{X[3], recon + b0 * L, 5, -1, w->dec_b[4], 0, -1, -1, OUT_CH0_F32};
+      if (recon_half) { d8.out = reinterpret_cast<__half*>(recon) + b0 * L; d8.out_half = 1; }
+      SPANON_TRY(run_layer(c, L_DEC8, d8, nb));
+    }
   }
   return SPANON_OK;
 }
@@ -1124,6 +1132,7 @@ extern "C" int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWei
   const bool fused_norm = norm_mean != nullptr;
   if (!fused_norm) T_valid = T;
   if (T_valid < 0 || T_valid > T) return SPANON_ERR_BAD_SHAPE;
+  if (opts && opts->recon_fp16) return SPANON_ERR_UNSUPPORTED;   // fp16 output: ConvAutoencoder entry point only
   Ctx c{};
   int chunk;
   SPANON_TRY(resolve_opts(opts, L, &c.tc, &chunk));

@@ -82,7 +82,8 @@ int enqueue_batch(int kind, const void* pcm_host, int fmt, int64_t B, int64_t n_
     SPANON_CUDA_TRY(cudaEventRecord(ln.ev_compute, ln.compute));
     SPANON_CUDA_TRY(cudaStreamWaitEvent(ln.d2h, ln.ev_compute, 0));
   }
-  SPANON_CUDA_TRY(cudaMemcpyAsync(recon_host, c.recon, (size_t)B * Tp * F * 4, cudaMemcpyDeviceToHost, ln.d2h));
+  const size_t out_elem = (kind == 0 && opts && opts->recon_fp16) ? 2 : 4;     // recon_fp16: half on the wire
+  SPANON_CUDA_TRY(cudaMemcpyAsync(recon_host, c.recon, (size_t)B * Tp * F * out_elem, cudaMemcpyDeviceToHost, ln.d2h));
   if (logp_host) SPANON_CUDA_TRY(cudaMemcpyAsync(logp_host, c.logp, (size_t)B * 2 * 4, cudaMemcpyDeviceToHost, ln.d2h));
   return SPANON_OK;
 }

@@ -80,6 +80,7 @@ struct TapGemmParams {
   // tcgen05 kernel, dataflow (chain) launches: per-tile counters [B * tiles_per_utt] of this layer's OUTPUT (bumped once by
   // each of the 4 epilogue warps) and of its INPUT's producer (flag_in_tpu = the producer's tiles per utterance)
   unsigned* flag_out; const unsigned* flag_in; int flag_in_tpu; unsigned flag_target;
+  int out_half;        // tcgen05 kernel, OUT_CH0_F32: store fp16 instead of fp32 (recon_fp16)
   int mma_group;       // tcgen05 kernel: stages per MMA issue round the caller asks for (0/1 = one; 4 where it pays)
   unsigned* err_flag;  // set to 1 if a dataflow wait timed out (results are then invalid; the consumer kernels report it)
   long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]

@@ -154,6 +154,7 @@ class ConvAutoencoder(nn.Module):
         self.sex_classifier = TDNNSexClassifier(2)
         self.precision = _precision_from_env()
         self.chunk_utts = 0  # 0 = library default (L2-resident chunks)
+        self.recon_fp16 = False  # fp16 mode only: return the reconstruction as a half tensor (the mode's own precision)
 
     def weight_struct(self):
         e, d, s = self.encoder, self.decoder, self.sex_classifier
@@ -182,7 +183,8 @@ class ConvAutoencoder(nn.Module):
 
     def opts(self, skip_classifier=False):
         return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16,
-                               int(self.chunk_utts), int(skip_classifier), 0)
+                               int(self.chunk_utts), int(skip_classifier), 0,
+                               int(bool(self.__dict__.get("recon_fp16", False)) and self.precision != "fp32"))
 
     def forward(self, input, pool_noise=None, fused_norm=None):
         """`pool_noise` [B,128]: the tensor StatisticsPooling adds to the pooled mean (default: drawn
@@ -214,7 +216,8 @@ class ConvAutoencoder(nn.Module):
             raise RuntimeError("shape '[%d, %d, %d]' is invalid for input of size %d: time*features must be a "
                                "multiple of 4" % (B, T, F, B * 4 * (-(-T * F // 4))))
         dev = x.device
-        recon = torch.empty((B, T, F), dtype=torch.float32, device=dev)
+        half_out = bool(self.__dict__.get("recon_fp16", False)) and self.precision != "fp32"
+        recon = torch.empty((B, T, F), dtype=torch.float16 if half_out else torch.float32, device=dev)
         logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
         if B == 0:
             return recon, logp
@@ -295,7 +298,7 @@ class ConvReconstruction(nn.Module):
         return d
 
     def opts(self):
-        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16, int(self.chunk_utts), 1, 0)
+        return _lib.ConvAEOpts(_lib.PREC_FP32 if self.precision == "fp32" else _lib.PREC_FP16, int(self.chunk_utts), 1, 0, 0)
 
     def forward(self, input, fused_norm=None):
         """`fused_norm` = (mean [F], std [F], utt_max [B], top_db, T_pad) as in ConvAutoencoder.forward."""

@@ -69,7 +69,7 @@ class AnonymizerPipeline(torch.nn.Module):
 
     # -- host-buffer path through the single C entry point (bench.py's e2e leg)
     def host_workspace(self, B, n_samples, device):
-        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0, 0)
         nbytes = _lib.lib().spanon_anonymize_workspace_bytes(0 if self.is_conv else 1, B, n_samples,
                                                              self.compute_features.hop_length,
                                                              self.compute_features.n_mels, C.byref(opts))
@@ -87,7 +87,9 @@ class AnonymizerPipeline(torch.nn.Module):
         mean = n.glob_mean.to(device=dev, dtype=torch.float32).contiguous()
         std = n.glob_std.to(device=dev, dtype=torch.float32).contiguous()
         w = self.model.weight_struct()
-        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        opts = self.model.opts() if self.is_conv else _lib.ConvAEOpts(0, 0, 0, 0, 0)
+        if recon_host.dtype != (torch.float16 if opts.recon_fp16 else torch.float32):
+            raise TypeError("recon_host dtype does not match model.recon_fp16")
         B, ns = pcm_host.shape
         fn = _lib.lib().spanon_anonymize_host_i16 if pcm_host.dtype == torch.int16 else _lib.lib().spanon_anonymize_host
         with torch.cuda.device(dev):
@@ -169,7 +171,8 @@ class StreamPipe:
         self._mean = n.glob_mean.to(device=self.device, dtype=torch.float32).contiguous()
         self._std = n.glob_std.to(device=self.device, dtype=torch.float32).contiguous()
         self._w = pipeline.model.weight_struct()
-        opts = pipeline.model.opts() if pipeline.is_conv else _lib.ConvAEOpts(0, 0, 0, 0)
+        opts = pipeline.model.opts() if pipeline.is_conv else _lib.ConvAEOpts(0, 0, 0, 0, 0)
+        self.recon_dtype = torch.float16 if opts.recon_fp16 else torch.float32     # what submit()'s recon_host must be
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().spanon_pipe_create(
@@ -180,6 +183,9 @@ class StreamPipe:
 
     def submit(self, pcm_host, recon_host, logp_host, pool_noise=None):
         # int16 PCM (the audio file's own sample format) halves the host-to-device bytes; the Fbank kernel converts
+        if recon_host.dtype != self.recon_dtype:
+            raise TypeError("recon_host must be %s for this pipe (model.recon_fp16 at creation time), got %s"
+                            % (self.recon_dtype, recon_host.dtype))
         fn = _lib.lib().spanon_pipe_submit_i16 if pcm_host.dtype == torch.int16 else _lib.lib().spanon_pipe_submit
         with torch.cuda.device(self.device):
             _lib.check(fn(self._h, _lib.ptr(pcm_host), pcm_host.shape[0], _lib.ptr(pool_noise), _lib.ptr(recon_host),

@@ -144,3 +144,41 @@ def test_fp16_bench_shape_vs_oracle(golden):
     rec_g2, _ = step.replay()
     torch.cuda.synchronize()
     assert abs(float((rec_g2[sel] - 1.0).cpu().sub(torch.from_numpy(r_ref)).abs().max()) / np.max(np.abs(r_ref))) < TOL16
+
+
+def test_fp16_reconstruction_output(golden):
+    """recon_fp16: the 16-bit mode returns its reconstruction as fp16 (half the device-to-host bytes of bench.py's e2e arm):
+    device call, one-shot host call and streaming pipe == the fp32-output result rounded to half, and within the mode's bar."""
+    m, w = _model("fp16")
+    pipe = _pipeline(m, golden)
+    B, n = 3, 16000
+    wav, _ = recipe.make_wav(81, B, n)
+    noise = recipe.make_noise(81, B, 128)
+    r_ref, l_ref = _oracle(wav, w, noise, golden)
+    nz = cu(noise)
+    rec32, logp32 = pipe(cu(wav), pool_noise=nz)
+    m.recon_fp16 = True
+    rec16, logp16 = pipe(cu(wav), pool_noise=nz)
+    assert rec16.dtype == torch.float16 and torch.equal(rec16, rec32.half()) and torch.equal(logp16, logp32)
+    assert rel_max(rec16.float().cpu().numpy(), r_ref) < TOL16
+    dev = torch.device(DEV)
+    pcm16 = torch.from_numpy(np.clip(np.round(wav * 32768.0), -32768, 32767).astype(np.int16)).pin_memory()
+    r_ref16, _ = _oracle(pcm16.numpy().astype(np.float32) / 32768.0, w, noise, golden)
+    rec_h = torch.empty(r_ref.shape, dtype=torch.float16).pin_memory()
+    logp_h = torch.empty((B, 2), dtype=torch.float32).pin_memory()
+    pipe.anonymize_host(pcm16, rec_h, logp_h, pipe.host_workspace(B, n, dev), pool_noise=nz)
+    assert rel_max(rec_h.float().numpy(), r_ref16) < TOL16
+    sp = pipe.stream_pipe(B, n, dev, depth=2)
+    with pytest.raises(TypeError):
+        sp.submit(pcm16, torch.empty(r_ref.shape, dtype=torch.float32).pin_memory(), logp_h, pool_noise=nz)
+    outs = []
+    for _ in range(4):
+        r = torch.full(r_ref.shape, float("nan"), dtype=torch.float16).pin_memory()
+        sp.submit(pcm16, r, logp_h, pool_noise=nz)
+        outs.append(r)
+    sp.drain()
+    sp.close()
+    for r in outs:
+        assert torch.equal(r, rec_h)
+    m.precision = "fp32"        # the fp32 parity mode keeps its fp32 output
+    assert pipe(cu(wav), pool_noise=nz)[0].dtype == torch.float32

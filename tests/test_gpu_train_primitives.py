@@ -81,7 +81,7 @@ def test_norm_act_fwd_bwd_vs_torch(per_batch, act, relu_mask, C, rows):
     z = (F.relu(z0) if relu_mask else z0).detach().requires_grad_(True)     # relu_mask: z is a stored ReLU output
     stats = T.colstats(z.detach())
     rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
-    out = T._NormAct.apply(z, stats, gamma, beta, per_batch, act, relu_mask, rm if per_batch else None, rv if per_batch else None, 0.1, 1e-5)
+    out = T._NormAct.apply(z, stats, gamma, beta, per_batch, act, relu_mask, rm if per_batch else None, rv if per_batch else None, 0.1, 1e-5, None)
     pre = z0.detach().double().requires_grad_(True)
     zd = F.relu(pre) if relu_mask else pre
     gd, bd = gamma.detach().double().requires_grad_(True), beta.detach().double().requires_grad_(True)
@@ -107,7 +107,7 @@ def test_norm_act_fwd_bwd_vs_torch(per_batch, act, relu_mask, C, rows):
 
 def test_silu_only_fwd_bwd_vs_torch():
     z = rnd(2, 5000, 32, seed=9).requires_grad_(True)
-    out = T._NormAct.apply(z, None, None, None, 0, 1, 0, None, None, 0.0, 0.0)
+    out = T._NormAct.apply(z, None, None, None, 0, 1, 0, None, None, 0.0, 0.0, None)
     zd = z.detach().double().requires_grad_(True)
     ref = zd * torch.sigmoid(zd)
     g = rnd(2, 5000, 32, seed=10)

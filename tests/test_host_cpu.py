@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(handle, n), n
     assert sorted(_lib.SIGNATURES) == names          # the ctypes binding covers the whole header
-    assert _lib.lib().spanon_abi_version() == 2
+    assert _lib.lib().spanon_abi_version() == 3
     assert _lib.lib().spanon_strerror(-4).decode().startswith("workspace")
 
 
@@ -47,7 +47,7 @@ def test_c_abi_argument_validation_without_device():
     assert L.spanon_fbank_i16(None, 1, 10, 10, None, None, C.byref(cfg), None) == -2
     assert L.spanon_pipe_submit_i16(None, None, 1, None, None, None) == -2
     assert L.spanon_norm_apply(None, None, None, None, 3, None, 80.0, 1, 4, 4, 80, None) == -1
-    opts = _lib.ConvAEOpts(_lib.PREC_FP16, 0, 0, 0)
+    opts = _lib.ConvAEOpts(_lib.PREC_FP16, 0, 0, 0, 0)
     assert L.spanon_convae_workspace_bytes(8, 1008, 80, C.byref(opts)) > 8 * 80640 * 32 * 2
     assert L.spanon_convae_workspace_bytes(0, 1008, 80, C.byref(opts)) == 0
     assert L.spanon_convae_fwd(None, None, None, None, None, None, 0.0, 0, None, None, None, 0, 1, 36, 80,
