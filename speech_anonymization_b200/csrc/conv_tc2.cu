@@ -1,0 +1,459 @@
+// Two-SM (cta_group::2) form of the tcgen05 tap GEMM for the 128-column layers (conv_tc.cu describes the one-SM kernel,
+// the data layout and the warp roles; this file only states what differs).
+//
+// Why: an M=128 N=128 K=16 UMMA fetches 8 KB of operands from shared memory = 64 cycles at 128 B/clk, exactly its math
+// time, and the bulk copies + the in-place operand transform use the same port (~100 cycles per 16-channel stage): the
+// 128 -> 128 layers run at ~2x their math time on one SM.  A CTA PAIR (two SMs of a TPC, cluster of 2) executes one
+// M=256 MMA over two adjacent row tiles: each CTA stages and transforms the A slab of ITS tile as before, but holds only
+// HALF of the weights (64 of the 128 output columns, all taps) -- the tensor cores of both SMs read both halves -- so the
+// B fetch per SM and MMA halves (6 KB -> 48 cycles < 64 of math) and 80 KB of shared memory are freed: the 128 -> 128 k5
+// layers get a two-tile operand ring instead of one.
+//
+//   both CTAs   loaders, transform warps, epilogue warps exactly as in conv_tc.cu, on their own tile (tile 2j + rank)
+//   leader      (cluster rank 0) the only MMA issuer: waits until BOTH CTAs' transform warps have filled a stage (the
+//               peer's warps arrive on the leader's `full` barrier through the cluster address), issues
+//               tcgen05.mma.cta_group::2 (M = 256: rows 0..127 from its own shared memory / TMEM, 128..255 from the
+//               peer's at the same offsets), and commits with .multicast::cluster so that `empty` / `tmem_full` fire in
+//               both CTAs.  The epilogue warps of both CTAs hand the accumulator back on the leader's `tmem_empty`.
+#include "tapgemm.cuh"
+#include "tc_prims.cuh"
+#include <cuda_fp16.h>
+#include <algorithm>
+#include <stdlib.h>
+#include <stdio.h>
+
+namespace spanon {
+namespace {
+
+using namespace tc;
+constexpr int T2_N = 128;                   // output columns of the layer (both CTAs together)
+constexpr int T2_NH = T2_N / 2;             // weight columns resident per CTA
+constexpr int T2_XF_WARPS = 8, T2_LOAD_WARPS = 2, T2_STAGE_CH = 16, T2_MAX_STAGES = 16, T2_E = 4;
+constexpr int T2_THREADS = (T2_E + 12) * 32;
+#ifndef T2_MG_VALUE
+#define T2_MG_VALUE 2
+#endif
+constexpr int T2_MG = T2_MG_VALUE;            // stages per MMA issue round (divides the 8 stages of a tile)
+constexpr size_t T2_SMEM_LIMIT = 232448;
+constexpr int T2_TRACE_N = 64;
+enum { X2_IDENT = 0, X2_SILU = 1, X2_RELU = 2, X2_T2 = 4 };
+enum { C_RAW = 0, C_FULL = 16, C_EMPTY = 32, C_TFULL = 48, C_TEMPTY = 50, C_W = 52, C_TPTR = 54 };
+
+struct T2Layout { uint32_t w, epi, bars, a, total, w_bytes, stage_bytes, lbo_a; int n_stages, slab; };
+
+__host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_used) {
+  T2Layout L;
+  L.slab = (slab_used + 7) / 8 * 8 + 1;
+  L.lbo_a = (uint32_t)L.slab * 16u;
+  L.stage_bytes = (uint32_t)(T2_STAGE_CH / 8) * L.lbo_a;
+  L.w_bytes = (uint32_t)ntaps * cin_v * T2_NH * 2u;
+  L.w = 0;
+  L.epi = L.w + L.w_bytes;                               // bias [128] fp32
+  L.bars = L.epi + T2_N * 4u;
+  L.a = (L.bars + 512u + 127u) / 128u * 128u;
+  const size_t avail = T2_SMEM_LIMIT > L.a ? T2_SMEM_LIMIT - L.a : 0;
+  int ns = (int)(avail / L.stage_bytes);
+  L.n_stages = (ns > T2_MAX_STAGES ? T2_MAX_STAGES : ns) / T2_XF_WARPS * T2_XF_WARPS;
+  L.total = L.a + (uint32_t)L.n_stages * L.stage_bytes;
+  return L;
+}
+
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at local offset `bar` (shared::cta address) of CTA `rank` of the cluster.  Default semantics
+// (release at CTA scope, the form CUTLASS's ClusterBarrier::arrive uses): with .release.cluster every arrival cost the
+// transform warps ~3 000 cycles; what the waiter's MMA reads is this SM's own shared memory through the async proxy, which
+// the fence.proxy.async in front of the arrive orders.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar), "r"(rank)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // (plain wait, as CUTLASS's ClusterBarrier::wait)
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void umma2_f16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+      "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc2_commit_elect(uint32_t bar) {     // arrives on `bar` in BOTH CTAs of the pair
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t.reg .b16 m;\n\t"
+      "mov.b16 m, 3;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(bar)
+      : "memory");
+}
+// kind::f16 instruction descriptor: fp16 A/B, fp32 D, K-major, M = 256 (two CTAs x 128 rows)
+__device__ __forceinline__ uint32_t umma2_idesc(int n) { return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(256 >> 4) << 24); }
+
+__device__ __forceinline__ __half2 silu_from_half2(__half2 hh) {
+  uint32_t t, in = *reinterpret_cast<uint32_t*>(&hh);
+  asm("tanh.approx.f16x2 %0, %1;" : "=r"(t) : "r"(in));
+  return __hfma2(hh, *reinterpret_cast<__half2*>(&t), hh);
+}
+
+template <int XF>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2_THREADS, 1)
+tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int E = T2_E, MMA_WARP = E + 11;
+  const int wd = warp - E;
+  const bool is_loader = wd == 3 || wd == 7, is_xform = wd >= 0 && wd < 10 && !is_loader;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
+  const uint32_t s_base = smem_u32(smem);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
+  const uint32_t bar0 = s_base + L.bars;
+  auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(bars + C_TPTR);
+  const int n_stage_tile = p.cin_v / T2_STAGE_CH;       // 8
+  // contiguous run of tile PAIRS per cluster; this CTA works on tile 2*pair + rank (a pair's second tile may lie past
+  // the end: it then has no valid rows -- nothing is loaded, everything is zero-filled, nothing is stored)
+  const int n_pairs_total = (total_tiles + 1) / 2;
+  const int n_clusters = (int)gridDim.x / 2, cid = (int)blockIdx.x / 2;
+  const int pair_begin = (int)((int64_t)cid * n_pairs_total / n_clusters);
+  const int n_my = (int)((int64_t)(cid + 1) * n_pairs_total / n_clusters) - pair_begin;
+  auto locate = [&](int k, int& b, int& tin) {
+    const int t = 2 * (pair_begin + k) + (int)rank;
+    if (t >= total_tiles) { b = p.B - 1; tin = tiles_per_utt; }          // the empty tile
+    else { b = t / tiles_per_utt; tin = t - b * tiles_per_utt; }
+  };
+
+  if (warp == MMA_WARP) {
+    if (lane == 0) {
+      for (int i = 0; i < L.n_stages; ++i) {
+        mbar_init(BAR(C_RAW + i), 1);
+        mbar_init(BAR(C_FULL + i), 2);        // one arrival per CTA of the pair (used in the leader only)
+        mbar_init(BAR(C_EMPTY + i), 1);
+      }
+      for (int i = 0; i < 2; ++i) { mbar_init(BAR(C_TFULL + i), 1); mbar_init(BAR(C_TEMPTY + i), 2 * E); }
+      mbar_init(BAR(C_W), 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      // this CTA's half of the weights: columns [64 * rank, +64) of every (tap, 8-channel chunk) slice, 1 KB each
+      mbar_expect_tx(BAR(C_W), L.w_bytes);
+      const int n_slices = p.ntaps * (p.cin_v / 8);
+      for (int i = 0; i < n_slices; ++i)
+        bulk_g2s(s_base + L.w + (uint32_t)i * (T2_NH * 16u),
+                 reinterpret_cast<const char*>(p.w) + ((size_t)i * T2_N + (size_t)rank * T2_NH) * 16u, T2_NH * 16u, BAR(C_W));
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_ptr_smem)),
+                 "r"(2 * T2_N)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    mbar_wait(BAR(C_W), 0);                   // (before the cluster barrier below: the peer's half is then in place too)
+  }
+  if (warp < E) {
+    float* ec = reinterpret_cast<float*>(smem + L.epi);
+    for (int c = threadIdx.x; c < T2_N; c += E * 32) ec[c] = p.bias ? p.bias[c % p.cout_mod] : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                         // both CTAs' barriers initialised and weights landed before any remote access
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const int planes_in = p.cin_v / 8;
+
+  if (is_loader) {
+    const __half* in_base = reinterpret_cast<const __half*>(p.in);
+    const int lw = wd >> 2;
+    uint32_t stage = (uint32_t)lw, ph = 0;
+    for (int k = 0; k < n_my; ++k) {
+      int b, tin;
+      locate(k, b, tin);
+      const int g0 = tin * TC_M - halo_lo;
+      const int lo = g0 < 0 ? -g0 : 0;
+      const int hi = min(slab_used, p.rows_in - g0);
+      const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
+      const int64_t plane_stride = (int64_t)p.rows_in * 8;
+      const __half* src = in_base + (((int64_t)b * planes_in + lw * (T2_STAGE_CH / 8)) * p.rows_in + (g0 + lo)) * 8;
+      if (p.trace && lane == 0 && lw == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 3) * T2_TRACE_N + k] = clock64();
+      for (int s = lw; s < n_stage_tile; s += T2_LOAD_WARPS) {
+        mbar_wait_cluster(BAR(C_EMPTY + stage), ph ^ 1u);
+        mbar_expect_tx_elect(BAR(C_RAW + stage), bytes * (T2_STAGE_CH / 8));
+        if (bytes) {
+          const uint32_t dst = s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u;
+          bulk_g2s_elect(dst, src, bytes, BAR(C_RAW + stage));
+          bulk_g2s_elect(dst + L.lbo_a, src + plane_stride, bytes, BAR(C_RAW + stage));
+        }
+        src += (int64_t)(T2_LOAD_WARPS * T2_STAGE_CH / 8) * plane_stride;
+        stage += T2_LOAD_WARPS;
+        if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
+      }
+    }
+  } else if (is_xform) {
+    const int xw = wd - (wd >> 2);
+    constexpr bool do_silu = (XF & 3) == X2_SILU, do_relu = (XF & 3) == X2_RELU, has_t2 = (XF & X2_T2) != 0;
+    constexpr bool ident = (XF & 7) == X2_IDENT;
+    const bool has_t1 = p.t1_scale != nullptr;
+    const float pre = do_silu ? 0.5f : 1.f;
+    const int s_fix = xw % n_stage_tile, kstep = T2_XF_WARPS / n_stage_tile;
+    uint32_t stage = (uint32_t)xw, ph = 0;
+    const int cm = (s_fix * T2_STAGE_CH) % p.cin_mod;
+    __half2 s1[8], h1[8], s2[8], h2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s1[j] = __float2half2_rn(pre); h1[j] = __float2half2_rn(0.f); s2[j] = s1[j]; h2[j] = h1[j]; }
+    if (has_t2) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s2[j] = __floats2half2_rn(__ldg(p.t2_scale + cm + 2 * j), __ldg(p.t2_scale + cm + 2 * j + 1));
+        h2[j] = __floats2half2_rn(__ldg(p.t2_shift + cm + 2 * j), __ldg(p.t2_shift + cm + 2 * j + 1));
+      }
+    }
+    int b_const = -1;
+    for (int k = xw / n_stage_tile; k < n_my; k += kstep) {
+      int b, tin;
+      locate(k, b, tin);
+      const int g0 = tin * TC_M - halo_lo;
+      const int lo = g0 < 0 ? -g0 : 0;
+      const int hi = min(slab_used, p.rows_in - g0);
+      if (!ident && has_t1 && b_const != b && (b_const < 0 || p.t1_bstride != 0)) {
+        const float4* sp = reinterpret_cast<const float4*>(p.t1_scale + (int64_t)b * p.t1_bstride + cm);
+        const float4* hp = reinterpret_cast<const float4*>(p.t1_shift + (int64_t)b * p.t1_bstride + cm);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 a = __ldg(sp + q), c = __ldg(hp + q);
+          s1[2 * q] = __floats2half2_rn(a.x * pre, a.y * pre); s1[2 * q + 1] = __floats2half2_rn(a.z * pre, a.w * pre);
+          h1[2 * q] = __floats2half2_rn(c.x * pre, c.y * pre); h1[2 * q + 1] = __floats2half2_rn(c.z * pre, c.w * pre);
+        }
+        b_const = b;
+      }
+      mbar_wait(BAR(C_RAW + stage), ph);
+      if (p.trace && lane == 0 && xw == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 4) * T2_TRACE_N + k] = clock64();
+      unsigned char* base = smem + L.a + stage * L.stage_bytes + (uint32_t)lane * 16u;
+      if (!ident && hi > lo) {
+        const bool tail = lane + 128 < slab_used;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          unsigned char* cb = base + (uint32_t)c * L.lbo_a;
+          uint4 v[5];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) v[q] = *reinterpret_cast<const uint4*>(cb + q * 512);
+          v[4] = make_uint4(0u, 0u, 0u, 0u);
+          if (tail) v[4] = *reinterpret_cast<const uint4*>(cb + 4 * 512);
+#pragma unroll
+          for (int q = 0; q < 5; ++q) {
+            __half2* hv = reinterpret_cast<__half2*>(&v[q]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              __half2 y = __hfma2(hv[j], s1[4 * c + j], h1[4 * c + j]);
+              if (do_silu) y = silu_from_half2(y);
+              if (do_relu) y = __hmax2(y, __float2half2_rn(0.f));
+              if (has_t2) y = __hfma2(y, s2[4 * c + j], h2[4 * c + j]);
+              hv[j] = y;
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(cb + q * 512) = v[q];
+          if (tail) *reinterpret_cast<uint4*>(cb + 4 * 512) = v[4];
+        }
+      }
+      if (lo > 0 || hi < slab_used) {
+        for (int r = lane; r < slab_used; r += 32)
+          if (r < lo || r >= hi) {
+            *reinterpret_cast<uint4*>(base + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(base + L.lbo_a + (uint32_t)(r - lane) * 16u) = make_uint4(0u, 0u, 0u, 0u);
+          }
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(BAR(C_FULL + stage), 0u);     // the LEADER's barrier counts both CTAs
+      if (p.trace && lane == 0 && xw == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 5) * T2_TRACE_N + k] = clock64();
+      stage += T2_XF_WARPS;
+      if (stage >= (uint32_t)L.n_stages) { stage -= (uint32_t)L.n_stages; ph ^= 1u; }
+    }
+  } else if (warp == MMA_WARP) {
+    if (leader) {
+      const uint32_t desc_hi = (uint32_t)(umma_desc(0, 0) >> 32);
+      const uint32_t a_lo_const = (uint32_t)umma_desc(0, L.lbo_a);
+      const uint32_t b_lo_const = (uint32_t)umma_desc(s_base + L.w, (uint32_t)T2_NH * 16u);
+      const uint32_t b_tap = (uint32_t)(p.cin_v / 8) * T2_NH, b_stage = (uint32_t)(T2_STAGE_CH / 8) * T2_NH;
+      const uint32_t dil = (uint32_t)p.tap_step;
+      const uint32_t idesc = umma2_idesc(T2_N);
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const int ntaps = p.ntaps;
+      uint32_t stage = 0, ph = 0;
+      for (int k = 0; k < n_my; ++k) {
+        const uint32_t buf = (uint32_t)k & 1u;
+        if (p.trace && lane == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 6) * T2_TRACE_N + k] = clock64();
+        mbar_wait_cluster(BAR(C_TEMPTY + buf), (((uint32_t)k >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        if (p.trace && lane == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 0) * T2_TRACE_N + k] = clock64();
+        const uint32_t d_tmem = tmem_u + buf * (uint32_t)T2_N;
+        // rounds of T2_MG stages: the waits (cluster-scope acquires; half of the arrivals come from the peer SM) and the
+        // multicast commits cost several hundred cycles per round, a 16-channel stage is only ntaps MMAs of work
+        for (int s = 0; s < n_stage_tile; s += T2_MG) {
+#pragma unroll
+          for (int g = 0; g < T2_MG; ++g) mbar_wait_cluster(BAR(C_FULL + stage + g), ph);
+          tc_fence_after();
+          uint32_t a_lo[T2_MG], b_lo[T2_MG];
+#pragma unroll
+          for (int g = 0; g < T2_MG; ++g) {
+            a_lo[g] = a_lo_const + ((s_base + L.a + (stage + g) * L.stage_bytes) >> 4);
+            b_lo[g] = b_lo_const + (uint32_t)(s + g) * b_stage;
+          }
+#pragma unroll
+          for (int g = 0; g < T2_MG; ++g)
+            umma2_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo[g], ((uint64_t)desc_hi << 32) | b_lo[g], idesc, (uint32_t)((s + g) != 0));
+#pragma unroll 1
+          for (int tap = 1; tap < ntaps; ++tap) {
+#pragma unroll
+            for (int g = 0; g < T2_MG; ++g) {
+              a_lo[g] += dil;
+              b_lo[g] += b_tap;
+              umma2_f16_elect(d_tmem, ((uint64_t)desc_hi << 32) | a_lo[g], ((uint64_t)desc_hi << 32) | b_lo[g], idesc, 1u);
+            }
+          }
+#pragma unroll
+          for (int g = 0; g < T2_MG; ++g) tc2_commit_elect(BAR(C_EMPTY + stage + g));
+          stage += T2_MG;
+          if (stage >= (uint32_t)L.n_stages) { stage = 0; ph ^= 1u; }
+        }
+        tc2_commit_elect(BAR(C_TFULL + buf));
+        if (p.trace && lane == 0 && k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 1) * T2_TRACE_N + k] = clock64();
+      }
+    }
+  } else if (warp < E) {
+    const float* ec = reinterpret_cast<const float*>(smem + L.epi);
+    const int quarter = warp & 3;
+    const int mloc = quarter * 32 + lane;
+    for (int k = 0; k < n_my; ++k) {
+      int b, tin;
+      locate(k, b, tin);
+      const int m = tin * TC_M + mloc;
+      const bool valid = m < p.rows_out;
+      const uint32_t buf = (uint32_t)k & 1u;
+      mbar_wait_cluster(BAR(C_TFULL + buf), ((uint32_t)k >> 1) & 1u);
+      tc_fence_after();
+      if (p.trace && threadIdx.x == 0 && 2 * k < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 2) * T2_TRACE_N + 2 * k] = clock64();
+      const uint32_t taddr = tmem_base + buf * (uint32_t)T2_N + ((uint32_t)(quarter * 32) << 16);
+      __half* out_h = reinterpret_cast<__half*>(p.out) + (int64_t)b * p.out_bstride;
+#pragma unroll 1
+      for (int cb = 0; cb < T2_N; cb += 32) {
+        float v[32];
+        tmem_ld32(taddr + (uint32_t)cb, v);
+        if (cb + 32 >= T2_N) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(BAR(C_TEMPTY + buf), 0u);
+        }
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bz = *reinterpret_cast<const float4*>(ec + cb + j);
+            v[j] += bz.x; v[j + 1] += bz.y; v[j + 2] += bz.z; v[j + 3] += bz.w;
+          }
+        }
+        if (valid) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const __half2 h0 = __floats2half2_rn(v[8 * q], v[8 * q + 1]), h1 = __floats2half2_rn(v[8 * q + 2], v[8 * q + 3]);
+            const __half2 h2 = __floats2half2_rn(v[8 * q + 4], v[8 * q + 5]), h3 = __floats2half2_rn(v[8 * q + 6], v[8 * q + 7]);
+            uint4 o;
+            o.x = *reinterpret_cast<const uint32_t*>(&h0); o.y = *reinterpret_cast<const uint32_t*>(&h1);
+            o.z = *reinterpret_cast<const uint32_t*>(&h2); o.w = *reinterpret_cast<const uint32_t*>(&h3);
+            const int c8 = (cb >> 3) + q;
+            *reinterpret_cast<uint4*>(out_h + (((int64_t)c8 * p.out_plane_rows + m) << 3)) = o;
+          }
+        }
+      }
+      if (p.trace && threadIdx.x == 0 && 2 * k + 1 < T2_TRACE_N) p.trace[((int64_t)blockIdx.x * 8 + 2) * T2_TRACE_N + 2 * k + 1] = clock64();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();            // neither CTA may leave (or free tensor memory) while its peer can still touch it
+  if (warp == MMA_WARP) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * T2_N) : "memory");
+  }
+}
+
+template <int XF>
+int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
+  int lo = 0, hi = 0;
+  for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
+  const int halo_lo = -lo, slab_used = TC_M + halo_lo + hi;
+  if (slab_used > 160 || p.cin_v != 128) return SPANON_ERR_UNSUPPORTED;
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used);
+  if (L.n_stages < T2_XF_WARPS || L.total > T2_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
+  auto kern = tapgemm_tc2_kernel<XF>;
+  SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+  const int tiles_per_utt = (int)ceil_div(p.rows_out, TC_M);
+  const int total = tiles_per_utt * p.B;
+  const int pairs = (total + 1) / 2;
+  const int grid = 2 * std::max(1, std::min(pairs, n_sm / 2));
+  static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
+  if (!trace_on) {
+    kern<<<grid, T2_THREADS, L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total);
+    return check_launch(p.tag ? p.tag : "tapgemm_tc2_kernel");
+  }
+  static long long* dbuf = nullptr;       // debug: clock64 stamps of cluster 0's roles
+  const size_t tbytes = (size_t)grid * 8 * T2_TRACE_N * sizeof(long long);
+  if (!dbuf) SPANON_CUDA_TRY(cudaMalloc(&dbuf, (size_t)160 * 8 * T2_TRACE_N * sizeof(long long)));
+  SPANON_CUDA_TRY(cudaMemsetAsync(dbuf, 0, tbytes, st));
+  TapGemmParams q = p;
+  q.trace = dbuf;
+  kern<<<grid, T2_THREADS, L.total, st>>>(q, halo_lo, slab_used, tiles_per_utt, total);
+  int rc = check_launch(p.tag ? p.tag : "tapgemm_tc2_kernel");
+  SPANON_CUDA_TRY(cudaStreamSynchronize(st));
+  static long long h[2 * 8 * T2_TRACE_N];
+  SPANON_CUDA_TRY(cudaMemcpy(h, dbuf, sizeof(h), cudaMemcpyDeviceToHost));
+  const long long t0 = h[0];
+  fprintf(stderr, "[trace2 %s] grid %d pairs %d n_stages %d\n", p.tag ? p.tag : "?", grid, pairs, L.n_stages);
+  for (int k : {0, 1, 2, 3, 20, 21, 22, 23}) {
+    fprintf(stderr, "  pair %2d: L0 load %lld xf %lld>%lld | issuer wait %lld go %lld end %lld | epi0 %lld..%lld | L1 load %lld xf %lld>%lld epi1 %lld..%lld\n", k,
+            h[3 * T2_TRACE_N + k] - t0, h[4 * T2_TRACE_N + k] - t0, h[5 * T2_TRACE_N + k] - t0, h[6 * T2_TRACE_N + k] - t0, h[k] - t0,
+            h[T2_TRACE_N + k] - t0, h[2 * T2_TRACE_N + 2 * k] - t0, h[2 * T2_TRACE_N + 2 * k + 1] - t0,
+            h[(8 + 3) * T2_TRACE_N + k] - t0, h[(8 + 4) * T2_TRACE_N + k] - t0, h[(8 + 5) * T2_TRACE_N + k] - t0,
+            h[(8 + 2) * T2_TRACE_N + 2 * k] - t0, h[(8 + 2) * T2_TRACE_N + 2 * k + 1] - t0);
+  }
+  return rc;
+}
+
+}  // namespace
+
+// 128 -> 128 channel layers without output statistics (tdnn.0/3/6, decoder.0): direct fp16 plane output
+bool tapgemm_tc2_supported(const TapGemmParams& p) {
+  if (!tapgemm_tc_supported(p)) return false;
+  if (p.cin_v != 128 || p.cout_v != 128 || p.cout_mod != 128 || p.stats || p.gen_feats || p.out_fold != OUT_DIRECT) return false;
+  if (p.relu || p.e_scale || p.bias_v || p.flag_in || p.flag_out) return false;
+  for (int t = 0; t < p.ntaps; ++t)
+    if (p.tap_kmax[t] != p.cin_v || p.tap_nmax[t] != p.cout_v) return false;
+  const int act = p.silu == 1 ? X2_SILU : p.silu == 2 ? X2_RELU : X2_IDENT;
+  const int xf = act | (p.t2_scale ? X2_T2 : 0);
+  return xf == X2_SILU || xf == (X2_SILU | X2_T2) || xf == (X2_RELU | X2_T2);
+}
+
+int launch_tapgemm_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
+  if (!tapgemm_tc2_supported(p) || p.B < 1 || n_sm < 2) return SPANON_ERR_UNSUPPORTED;
+  const int act = p.silu == 1 ? X2_SILU : p.silu == 2 ? X2_RELU : X2_IDENT;
+  const int xf = act | (p.t2_scale ? X2_T2 : 0);
+  if (xf == X2_SILU) return launch_tc2<X2_SILU>(p, n_sm, st);
+  if (xf == (X2_SILU | X2_T2)) return launch_tc2<X2_SILU | X2_T2>(p, n_sm, st);
+  if (xf == (X2_RELU | X2_T2)) return launch_tc2<X2_RELU | X2_T2>(p, n_sm, st);
+  return SPANON_ERR_UNSUPPORTED;
+}
+
+}  // namespace spanon

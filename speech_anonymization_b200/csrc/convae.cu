@@ -834,6 +834,10 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   const bool split_stats = on_tc && io.out_stats >= 0 && !fuse;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
+    // the 128 -> 128 layers without output statistics on CTA pairs (conv_tc2.cu); $SPANON_TC2=0: one-SM kernel
+    static const bool tc2_env = !(getenv("SPANON_TC2") && getenv("SPANON_TC2")[0] == '0');
+    if (tc2_env && tapgemm_tc2_supported(p)) SPANON_TRY(launch_tapgemm_tc2(p, c.n_sm, c.st));
+    else
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
     if (id == L_DEC45) {   // take the two rows of decoder.4 the reference does not have back out (before the statistics)
       dec45_edge_kernel<<<(unsigned)nb, 384, 0, c.st>>>((const __half*)io.in, p.t1_scale, p.t1_shift, c.ws.edge45,

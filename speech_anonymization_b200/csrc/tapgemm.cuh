@@ -97,5 +97,8 @@ int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st);
 // A chain of up to three 128 -> 128 layers (the TDNN) in one launch, see conv_tc.cu.
 int launch_tapgemm_tc_chain(const TapGemmParams* ps, int n, const int* ctas, int rr_group, cudaStream_t st);
 bool tapgemm_tc_supported(const TapGemmParams& p);
+// Two-SM (cta_group::2, cluster of 2) form for the 128 -> 128 layers (conv_tc2.cu).
+int launch_tapgemm_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st);
+bool tapgemm_tc2_supported(const TapGemmParams& p);
 
 }  // namespace spanon
