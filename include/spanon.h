@@ -334,6 +334,19 @@ SPANON_API int spanon_pool_reinterp_bwd(const float* x, const float* save, const
                              int64_t C, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * SpecAugment on features (TRAIN stage of the anonymizer)
+ * replaces  SpecAugment.time_warp / mask_along_axis   speechbrain/speechbrain/lobes/augment.py:127-200
+ *           (called at speechbrain_convae_train.py:64-67, configured by convae.yaml:273-283)
+ * The random draws are the caller's (the Python mirror makes the reference's torch.randint calls in the same order).
+ * ------------------------------------------------------------------------- */
+/* time warp: out[:, :w] = bicubic(in[:, :c] -> w rows), out[:, w:] = bicubic(in[:, c:] -> T - w rows), align_corners. */
+SPANON_API int spanon_specaug_warp(const float* in, float* out, int64_t B, int64_t T, int64_t F, int32_t c, int32_t w, void* stream);
+/* in place: x[b, idx in [pos, pos+len) of any of the n_mask masks] = 0 (replace_with_zero) or x.mean(); axis 1 = time,
+ * 2 = feature; mask_len / mask_pos int32 [B][n_mask] on the device; scratch: one double. */
+SPANON_API int spanon_specaug_mask(float* x, int64_t B, int64_t T, int64_t F, int32_t axis, int32_t n_mask, const int32_t* mask_len,
+                        const int32_t* mask_pos, int32_t replace_with_zero, double* scratch, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * Loss statistics
  * replaces  CosineSimilarityLoss.forward   utils/cosine_similarity_loss.py:53-56
  *           _pairwise_dists / ClusterMI._mutual_information  utils/ClusterMI.py:12-63,88-121

@@ -10,6 +10,7 @@ from .losses import (ClusterMI, CosineSimilarityLoss, GroupSampler, GroupSamplin
                      SimilarityMetricsStats, cosine_distance_2d, knn_mi)
 from .models import (GLU, ConvAutoencoder, ConvReconstruction, FullyConnectedAutoencoder, FullyConnSexClassifier,  # noqa: F401
                      GradReverse, StatisticsPooling, TDNNSexClassifier, Xvector, XvectorClassifier, XvectorHead)
+from .augment import SpecAugment  # noqa: F401
 from .distributed import DataParallelTrainer, FlatGradients, gather_for_mi  # noqa: F401
 from .pipeline import AnonymizerPipeline, GraphedStep, StreamPipe, shard_range  # noqa: F401
 

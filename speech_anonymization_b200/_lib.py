@@ -142,6 +142,9 @@ SIGNATURES = {
                                            C.c_int64, C.c_int64, C.c_void_p]),
     "spanon_pool_reinterp_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
                                            C.c_int64, C.c_void_p]),
+    "spanon_specaug_warp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "spanon_specaug_mask": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                      C.c_int32, C.c_void_p, C.c_void_p]),
     "spanon_cosine_loss": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_float,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "spanon_cosine_loss_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,

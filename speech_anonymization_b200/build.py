@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libspanon.so")
 SOURCES = ["api.cu", "fbank.cu", "normalize.cu", "fcae.cu", "conv_simt.cu", "conv_tc.cu", "conv_tc2.cu", "convae.cu",
-           "xvector.cu", "losses.cu", "pipeline.cu", "train.cu"]
+           "xvector.cu", "losses.cu", "pipeline.cu", "train.cu", "augment.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

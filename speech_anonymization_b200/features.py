@@ -86,6 +86,11 @@ class Fbank(torch.nn.Module):
         all_freqs = torch.linspace(0, sample_rate // 2, self.n_stft)
         self.all_freqs_mat = all_freqs.repeat(self.f_central.shape[0], 1)
         self._dev_cache = {}
+        # Opt-in (not a constructor argument: the signature is the reference's): keep the features of the last waveform
+        # tensor.  compute_objectives recomputes Fbank on the very tensor compute_forward just used
+        # (speechbrain_convae_train.py:58 and :82); with the cache the second call is a 19 MB copy instead of a pass.
+        self.cache_features = False
+        self._feat_cache = None
 
     # -- filter matrix, evaluated with the same fp32 torch ops as the reference (:586-689) so the
     #    weights are bit-identical, then compressed to the runs of non-zero taps the kernel uses
@@ -147,6 +152,7 @@ class Fbank(torch.nn.Module):
     def __getstate__(self):  # no device handles in pickles / deepcopies
         d = self.__dict__.copy()
         d["_dev_cache"] = {}
+        d["_feat_cache"] = None
         return d
 
     def num_frames(self, n_samples):
@@ -175,6 +181,12 @@ class Fbank(torch.nn.Module):
 
     def forward(self, wav):
         """Returns a set of features generated from the input waveforms (lobes/features.py:126-143)."""
+        key = None
+        if self.cache_features and not (self.training and self.param_rand_factor != 0):
+            # same storage, same in-place version, same view: the tensor has not changed since the cached call
+            key = (wav.data_ptr(), wav._version, tuple(wav.shape), tuple(wav.stride()), wav.dtype, str(wav.device))
+            if self._feat_cache is not None and self._feat_cache[0] == key:
+                return self._feat_cache[1].clone()
         multi = wav.dim() == 3
         if multi:  # STFT.forward :143-146 / Filterbank.forward :538-559: channels are folded into the batch
             B0, n0, ch = wav.shape
@@ -187,6 +199,8 @@ class Fbank(torch.nn.Module):
                                                          _lib.stream_ptr(out.device)), "fbank_clamp")
         if multi:
             out = out.reshape(B0, ch, T, F).permute(0, 2, 3, 1)
+        if key is not None:
+            self._feat_cache = (key, out.clone())
         return out
 
 

@@ -163,6 +163,41 @@ def main():
     out["sim_peek2"] = np.array(float(st.peek()))
     out["sim_summary"] = np.array(float(st.summarize()))
     out["sim_scores"] = np.concatenate([s1, s2])
+    # ---------------- SpecAugment on features (lobes/augment.py:32-200; convae.yaml:273-283) ----------------
+    sb = sys.modules["speechbrain"]
+    for name in ("speechbrain.utils.data_utils", "speechbrain.processing.speech_augmentation", "speechbrain.utils.torch_audio_backend"):
+        stub = types.ModuleType(name)      # augment.py imports these for its OTHER classes; SpecAugment uses only torch
+        for attr in ("download_file", "SpeedPerturb", "DropFreq", "DropChunk", "AddBabble", "AddNoise", "AddReverb"):
+            setattr(stub, attr, object)
+        stub.check_torchaudio_backend = lambda: None
+        sys.modules[name] = stub
+    if "torchaudio" not in sys.modules:
+        try:
+            import torchaudio  # noqa: F401
+        except Exception:
+            sys.modules["torchaudio"] = types.ModuleType("torchaudio")
+    aug_mod = importlib.import_module("speechbrain.lobes.augment")
+    real_randint = torch.randint
+    for name, (seed, B, T, kw) in {
+            "specaug_yaml": (7, 3, 108, dict(time_warp=True, time_warp_window=5, time_warp_mode="bicubic", freq_mask=True, n_freq_mask=2,
+                                             time_mask=True, n_time_mask=2, replace_with_zero=False, freq_mask_width=30, time_mask_width=40)),
+            "specaug_default": (8, 2, 1008, dict())}.items():
+        draws = []
+
+        def logged(*a, **k):
+            r = real_randint(*a, **k)
+            draws.append(r.clone().reshape(-1).to(torch.int64))
+            return r
+        torch.randint = logged
+        try:
+            torch.manual_seed(seed)
+            aug = aug_mod.SpecAugment(**kw)
+            x = t(recipe.make_feats(seed, B, T))
+            y = aug(x.clone())
+        finally:
+            torch.randint = real_randint
+        out[name + "_out"] = y.numpy()
+        out[name + "_draws"] = torch.cat(draws).numpy()        # c, w, freq len [B*n], freq pos, time len, time pos
     np.savez_compressed(os.path.join(HERE, "golden_v3.npz"), **out)
     print("wrote golden_v3.npz with %d arrays, %.1f MB" % (len(out), os.path.getsize(os.path.join(HERE, "golden_v3.npz")) / 1e6))
 

@@ -168,3 +168,51 @@ def test_input_normalization_speaker_vs_reference(golden3):
     assert [n.spk_dict_count[k] for k in (3, 5, 7, 9)] == golden3["spk_count"].tolist()
     n.eval()
     assert rel_max(n(feats.clone(), lens, spk_ids=torch.tensor([[3], [11], [9], [5]])).cpu().numpy(), golden3["spk_eval_call3"]) < 1e-5
+
+
+def test_spec_augment_vs_reference(golden3):
+    """speechbrain/lobes/augment.py:32-200 on features (convae.yaml:273-283): time warp (bicubic, align_corners) + frequency
+    and time masks filled with the tensor's mean, with the random draws the reference made (logged by make_golden_v3.py)."""
+    cases = {"specaug_yaml": (7, 3, 108, dict(time_warp=True, time_warp_window=5, time_warp_mode="bicubic", freq_mask=True, n_freq_mask=2,
+                                              time_mask=True, n_time_mask=2, replace_with_zero=False, freq_mask_width=30, time_mask_width=40)),
+             "specaug_default": (8, 2, 1008, dict())}
+    for name, (seed, B, T, kw) in cases.items():
+        aug = sab.SpecAugment(**kw)
+        d = golden3[name + "_draws"]
+        nf, nt = aug.n_freq_mask, aug.n_time_mask
+        c, w = int(d[0]), int(d[1]) + 1                           # augment.py:139-140
+        o = 2
+        fl, fp = d[o:o + B * nf].reshape(B, nf), d[o + B * nf:o + 2 * B * nf].reshape(B, nf)
+        o += 2 * B * nf
+        tl, tp = d[o:o + B * nt].reshape(B, nt), d[o + B * nt:o + 2 * B * nt].reshape(B, nt)
+        x = cu(recipe.make_feats(seed, B, T))
+        x0 = x.clone()
+        y = aug.time_warp_with(x, c, w)
+        aug.mask_with(y, 2, torch.from_numpy(fl), torch.from_numpy(fp))
+        aug.mask_with(y, 1, torch.from_numpy(tl), torch.from_numpy(tp))
+        assert torch.equal(x, x0)
+        assert rel_max(y.cpu().numpy(), golden3[name + "_out"]) < 1e-5
+    # forward(): same shapes, seeded draws are reproducible, masks are really applied
+    aug = sab.SpecAugment(replace_with_zero=True)
+    x = cu(recipe.make_feats(9, 2, 300))
+    torch.manual_seed(3)
+    y1 = aug(x)
+    torch.manual_seed(3)
+    y2 = aug(x)
+    assert y1.shape == x.shape and torch.equal(y1, y2) and int((y1 == 0).sum()) > 0
+
+
+def test_fbank_cache():
+    """Fbank.cache_features: the second call on the same waveform tensor (compute_objectives after compute_forward,
+    speechbrain_convae_train.py:58 / :82) returns the stored features; an in-place change of the waveform invalidates it."""
+    fb = sab.Fbank(n_mels=80)
+    fb.cache_features = True
+    wav = cu(recipe.make_wav(5, 2, 16000)[0])
+    L = sab.lib()
+    f1 = fb(wav)
+    n1 = L.spanon_launch_count()
+    f2 = fb(wav)
+    assert L.spanon_launch_count() == n1 and torch.equal(f1, f2) and f2.data_ptr() != f1.data_ptr()
+    wav.mul_(0.5)
+    f3 = fb(wav)
+    assert L.spanon_launch_count() > n1 and not torch.equal(f3, f1)
