@@ -88,9 +88,10 @@ def traffic(path):
     out = {"source": "ncu --set full --clock-control none (tools/ncu_round.sh), batch 60 x 10 s",
            "unit": "MB per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
            "kernels": {k: {"traffic_mb": v[0] / v[2], "time_us": v[1] / v[2], "n": v[2]} for k, v in agg.items()}}
-    conv = [(k, v) for k, v in agg.items() if k.startswith("tapgemm_tc_kernel") or k.startswith("first_layer")]
+    conv = [(k, v) for k, v in agg.items() if k.startswith("tapgemm_tc") or k.startswith("first_layer")]
     n = sum(v[2] for _, v in conv)
-    out["conv_stack"] = {"traffic_mb_per_launch": sum(v[0] for _, v in conv) / n, "launches_captured": n}
+    out["conv_stack"] = {"traffic_mb_per_launch": sum(v[0] for _, v in conv) / n, "launches_captured": n,
+                         "traffic_mb_per_step": sum(v[0] for _, v in conv)}
     print(json.dumps(out, indent=1))
 
 
