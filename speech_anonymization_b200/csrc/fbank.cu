@@ -20,6 +20,7 @@
 //     memory; the only HBM traffic is 4 B/sample in and 4 B/mel-bin out.
 #include "common.cuh"
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace spanon {
@@ -230,6 +231,198 @@ fbank400_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_strid
   }
 }
 
+// ------------------------------------------------------------------ register / warp-shuffle FFT form (the one launched)
+// 400 = 25 x 16: a HALF-WARP owns one complex 400-point transform (= two real frames: frame t -> real part, frame t+1 ->
+// imaginary part).  Lane n2 (0..15) holds the 25 samples x[16*n1 + n2] in registers:
+//   A  25-point DFT over n1 in registers (5 x 5: ten radix-5 butterflies + sixteen constant twiddles W_25^{qr}),
+//   B  twiddle W_400^{n2*k1}: 24 per-lane constants evaluated once per thread (a thread runs many transforms),
+//   C  16-point DFT over n2 ACROSS the half-warp's lanes: four radix-2 decimation-in-frequency stages of
+//      __shfl_xor exchanges (distance 8, 4, 2, 1); lane l ends with k2 = bitrev4(l), i.e. bins k = k1 + 25*k2: a CONTIGUOUS
+//      block of 25 bins per lane,
+//   D  the two real spectra: X_a[k], X_b[k] from Z[k] and conj(Z[400-k]); Z[400-k] sits in lane l^15, register 25-k1
+//      (k1 = 0: register 0 of lane bitrev((16 - k2) & 15)): two more shuffles per value; power into shared memory,
+//   E  sparse mel projection + dB from shared memory, per-utterance maximum by warp reduce + atomicMax.
+// Shared memory is touched once per sample on the way in (PCM segment) and once per bin on the way out (power); the
+// transform itself never leaves the register file (the Stockham form above moves 400 complex values through shared memory
+// four times per transform and synchronises the CTA five times).
+constexpr int FW_NT = 256;                         // 8 warps = 16 transforms = 32 frames per CTA pass
+constexpr int FW_FRAMES = 2 * (FW_NT / 16);        // 32
+constexpr int FW_SEG = (FW_FRAMES - 1) * HOP + N_FFT;   // 5360 samples
+struct FwSmem {
+  float seg[FW_SEG];
+  float win[N_FFT];
+  float P[FW_FRAMES * P_STRIDE];
+};
+
+__device__ __forceinline__ void cmul_c(float2& a, float cr, float ci) {     // a *= (cr + i ci)
+  const float x = a.x * cr - a.y * ci;
+  a.y = a.x * ci + a.y * cr;
+  a.x = x;
+}
+
+template <typename TS>
+__global__ void __launch_bounds__(FW_NT, 2)
+fbank400_warp_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T, float* __restrict__ out,
+                     int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FwSmem& S = *reinterpret_cast<FwSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n2 = lane & 15;                                  // lane inside the half-warp = input residue mod 16
+  const int k2 = ((n2 & 1) << 3) | ((n2 & 2) << 1) | ((n2 & 4) >> 1) | ((n2 & 8) >> 3);   // bitrev4: output block of this lane
+  const int b = blockIdx.y;
+  const TS* x = pcm + (int64_t)b * pcm_stride;
+  for (int i = tid; i < N_FFT; i += FW_NT) S.win[i] = cfg.window[i];
+  // per-lane constants: W_400^{n2*k1} (fp32 sincospif of the exactly reduced fraction) and the three stage twiddles
+  float twr[25], twi[25];
+#pragma unroll
+  for (int k1 = 0; k1 < 25; ++k1) sincospif(-(float)((n2 * k1) % N_FFT) / 200.f, &twi[k1], &twr[k1]);
+  float swr[3], swi[3], sgn[4];
+#pragma unroll
+  for (int st = 0; st < 4; ++st) {
+    const int h = 8 >> st;
+    const bool upper = (n2 & h) != 0;
+    sgn[st] = upper ? -1.f : 1.f;
+    if (st < 3) {
+      if (upper) sincospif(-(float)(n2 & (h - 1)) / (float)h, &swi[st], &swr[st]);     // W_{2h}^{l mod h}
+      else { swr[st] = 1.f; swi[st] = 0.f; }
+    }
+  }
+  // lane (inside the half-warp) that holds bin 25*((16 - k2) & 15): bitrev4 of that block index
+  const int kz = (16 - k2) & 15;
+  const int lz = (lane & 16) | ((kz & 1) << 3) | ((kz & 2) << 1) | ((kz & 4) >> 1) | ((kz & 8) >> 3);
+  constexpr float C25[25][2] = {
+      {1.f, 0.f}, {0.96858316112863108f, -0.24868988716485479f}, {0.87630668004386358f, -0.48175367410171532f},
+      {0.72896862742141155f, -0.68454710592868862f}, {0.53582679497899666f, -0.84432792550201508f},
+      {0.30901699437494742f, -0.95105651629515357f}, {0.062790519529313374f, -0.99802672842827156f},
+      {-0.18738131458572463f, -0.98228725072868872f}, {-0.42577929156507272f, -0.90482705246601958f},
+      {-0.63742398974868975f, -0.77051324277578925f}, {-0.80901699437494742f, -0.58778525229247313f},
+      {-0.92977648588825146f, -0.36812455268467797f}, {-0.99211470131447788f, -0.12533323356430426f},
+      {-0.99211470131447788f, 0.12533323356430426f}, {-0.92977648588825146f, 0.36812455268467797f},
+      {-0.80901699437494742f, 0.58778525229247313f}, {-0.63742398974868975f, 0.77051324277578925f},
+      {-0.42577929156507272f, 0.90482705246601958f}, {-0.18738131458572463f, 0.98228725072868872f},
+      {0.062790519529313374f, 0.99802672842827156f}, {0.30901699437494742f, 0.95105651629515357f},
+      {0.53582679497899666f, 0.84432792550201508f}, {0.72896862742141155f, 0.68454710592868862f},
+      {0.87630668004386358f, 0.48175367410171532f}, {0.96858316112863108f, 0.24868988716485479f}};   // W_25^j = exp(-2 pi i j / 25)
+
+  const int n_mels = cfg.n_mels;
+  const float db_floor = (float)((double)cfg.multiplier * log10((double)cfg.amin)) - cfg.db_offset;
+  float lmax = -INFINITY;
+  for (int t0 = blockIdx.x * FW_FRAMES; t0 < T; t0 += gridDim.x * FW_FRAMES) {
+    __syncthreads();                                         // (previous pass's mel reads of P / seg are done)
+    // PCM segment of the pass's 32 frames: padded sample p = t*HOP + n - N_FFT/2 (center=True, zero padding)
+    const int64_t base = (int64_t)t0 * HOP - N_FFT / 2;
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & (4 * sizeof(TS) - 1)) == 0) && ((base & 3) == 0);
+    for (int i4 = tid; i4 < FW_SEG / 4; i4 += FW_NT) {
+      const int64_t sidx = base + 4 * (int64_t)i4;
+      float4 v;
+      if (vec_ok && sidx >= 0 && sidx + 3 < n_samples) {
+        v = load4(x, sidx);
+      } else {
+        v.x = (sidx + 0 >= 0 && sidx + 0 < n_samples) ? load1(x, sidx + 0) : 0.f;
+        v.y = (sidx + 1 >= 0 && sidx + 1 < n_samples) ? load1(x, sidx + 1) : 0.f;
+        v.z = (sidx + 2 >= 0 && sidx + 2 < n_samples) ? load1(x, sidx + 2) : 0.f;
+        v.w = (sidx + 3 >= 0 && sidx + 3 < n_samples) ? load1(x, sidx + 3) : 0.f;
+      }
+      *reinterpret_cast<float4*>(&S.seg[4 * i4]) = v;
+    }
+    __syncthreads();
+    const int pair = warp * 2 + (lane >> 4);                 // this half-warp's transform: frames t0 + 2*pair, +1
+    {   // (frames past T are computed from the zero padding and never written out: both half-warps must take part in the
+        //  full-warp shuffles)
+      // ---- load: a[n1] = w[n] * (x_a[n] + i x_b[n]), n = 16*n1 + n2
+      float2 a[25];
+      const float* fa = S.seg + (2 * pair) * HOP + n2;
+#pragma unroll
+      for (int n1 = 0; n1 < 25; ++n1) {
+        const float wn = S.win[16 * n1 + n2];
+        a[n1] = make_float2(wn * fa[16 * n1], wn * fa[16 * n1 + HOP]);
+      }
+      // ---- A: 25-point DFT over n1 = 5p + q  ->  Y[r + 5s]
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        float2 v[5] = {a[q], a[5 + q], a[10 + q], a[15 + q], a[20 + q]};
+        dft5(v);
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+          if (r > 0 && q > 0) cmul_c(v[r], C25[(q * r) % 25][0], C25[(q * r) % 25][1]);
+          a[5 * r + q] = v[r];                                 // T[r][q]
+        }
+      }
+      float2 y[25];
+#pragma unroll
+      for (int r = 0; r < 5; ++r) {
+        float2 v[5] = {a[5 * r], a[5 * r + 1], a[5 * r + 2], a[5 * r + 3], a[5 * r + 4]};
+        dft5(v);
+#pragma unroll
+        for (int s5 = 0; s5 < 5; ++s5) y[r + 5 * s5] = v[s5];
+      }
+      // ---- B: twiddle W_400^{n2*k1}
+#pragma unroll
+      for (int k1 = 1; k1 < 25; ++k1) cmul_c(y[k1], twr[k1], twi[k1]);
+      // ---- C: 16-point DFT across the half-warp (radix-2 DIF, distances 8, 4, 2, 1)
+#pragma unroll
+      for (int st = 0; st < 4; ++st) {
+        const int h = 8 >> st;
+#pragma unroll
+        for (int k1 = 0; k1 < 25; ++k1) {
+          const float pr = __shfl_xor_sync(0xffffffffu, y[k1].x, h), pi = __shfl_xor_sync(0xffffffffu, y[k1].y, h);
+          float2 tq = make_float2(fmaf(sgn[st], y[k1].x, pr), fmaf(sgn[st], y[k1].y, pi));
+          if (st < 3) cmul_c(tq, swr[st], swi[st]);
+          y[k1] = tq;
+        }
+      }
+      // ---- D: separate the two real transforms, power spectrum of bins k <= 200 into shared memory
+      float* Pa = S.P + (2 * pair) * P_STRIDE;
+      float* Pb = Pa + P_STRIDE;
+      {   // k1 = 0: bin 25*k2, partner bin 25*((16-k2)&15) in register 0 of lane lz
+        const float zr = __shfl_sync(0xffffffffu, y[0].x, lz), zi = __shfl_sync(0xffffffffu, y[0].y, lz);
+        const int k = 25 * k2;
+        if (k <= 200) {
+          const float ar = y[0].x + zr, ai = y[0].y - zi, br = y[0].y + zi, bi = y[0].x - zr;
+          Pa[k] = 0.25f * (ar * ar + ai * ai);
+          Pb[k] = 0.25f * (br * br + bi * bi);
+        }
+      }
+#pragma unroll
+      for (int k1 = 1; k1 <= 12; ++k1) {
+        // partner lane l^15 holds block 15-k2: its y[25-k1] = Z[400 - kA], its y[k1] = Z[400 - kB]
+        const float nAr = __shfl_xor_sync(0xffffffffu, y[25 - k1].x, 15), nAi = __shfl_xor_sync(0xffffffffu, y[25 - k1].y, 15);
+        const float nBr = __shfl_xor_sync(0xffffffffu, y[k1].x, 15), nBi = __shfl_xor_sync(0xffffffffu, y[k1].y, 15);
+        const int kA = k1 + 25 * k2, kB = (25 - k1) + 25 * k2;
+        if (kA <= 200) {
+          const float ar = y[k1].x + nAr, ai = y[k1].y - nAi, br = y[k1].y + nAi, bi = y[k1].x - nAr;
+          Pa[kA] = 0.25f * (ar * ar + ai * ai);
+          Pb[kA] = 0.25f * (br * br + bi * bi);
+        }
+        if (kB <= 200) {
+          const float ar = y[25 - k1].x + nBr, ai = y[25 - k1].y - nBi, br = y[25 - k1].y + nBi, bi = y[25 - k1].x - nBr;
+          Pa[kB] = 0.25f * (ar * ar + ai * ai);
+          Pb[kB] = 0.25f * (br * br + bi * bi);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- E: mel projection + dB (fp32 like the reference, processing/features.py:701-710)
+    for (int w = tid; w < FW_FRAMES * n_mels; w += FW_NT) {
+      const int fr = w / n_mels;
+      const int m = w - fr * n_mels;
+      const int t = t0 + fr;
+      if (t >= T) continue;
+      const int st = __ldg(cfg.mel_start + m);
+      const int ln = __ldg(cfg.mel_len + m);
+      const float* wv = cfg.mel_w + __ldg(cfg.mel_off + m);
+      const float* pp = S.P + fr * P_STRIDE + st;
+      float acc = 0.f;
+      for (int i = 0; i < ln; ++i) acc = fmaf(pp[i], __ldg(wv + i), acc);
+      const float db = acc <= cfg.amin ? db_floor : cfg.multiplier * log10f(acc) - cfg.db_offset;
+      out[((int64_t)b * T + t) * n_mels + m] = db;
+      lmax = fmaxf(lmax, db);
+    }
+  }
+  lmax = warp_max(lmax);
+  if (lane == 0 && lmax > -INFINITY) atomicMax(utt_max + b, float_to_key(lmax));
+}
+
 // Generic (any n_fft <= 4096, win_length <= n_fft) direct-DFT path: one CTA per frame.
 // O(n_fft^2) per frame -- correctness path for non-reference configurations only.
 template <typename TS>
@@ -343,9 +536,19 @@ int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride
     static std::atomic<unsigned long long> attr_done{0};   // per device: the attribute belongs to the device's context
     int dev = 0;
     SPANON_CUDA_TRY(cudaGetDevice(&dev));
-    if (first_use_on_device(attr_done, dev))
+    if (first_use_on_device(attr_done, dev)) {
       SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(FbankSmem)));
+      SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_warp_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(FwSmem)));
+    }
+    // register / warp-shuffle FFT (default); $SPANON_FBANK_SMEM=1: the shared-memory Stockham form (A/B switch)
+    static const bool smem_form = getenv("SPANON_FBANK_SMEM") && getenv("SPANON_FBANK_SMEM")[0] == '1';
+    if (!smem_form) {
+      dim3 grid((unsigned)ceil_div(T, FW_FRAMES), (unsigned)B);
+      fbank400_warp_kernel<TS><<<grid, FW_NT, sizeof(FwSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+      return check_launch("fbank400_kernel");
+    }
     dim3 grid((unsigned)ceil_div(T, FRAMES_PER_CTA), (unsigned)B);
     fbank400_kernel<TS><<<grid, NT, sizeof(FbankSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
     return check_launch("fbank400_kernel");
