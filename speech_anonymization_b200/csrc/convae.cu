@@ -682,10 +682,9 @@ const int kInC[6] = {64, 64, 128, 128, 64, 32};        // ConvAutoencoder: chann
 const int kInC_recon[6] = {32, 64, 64, 32, 8, 8};      // ConvReconstruction: encoder.{1,4,7,10} (two unused slots)
 
 int default_chunk(int64_t L, size_t esize) {
-  // Utterances per pass over the layer list.  Measured on B200 (bench.py --chunk, 60 x 10 s): 6 utterances (planes of
-  // a layer pair resident in the 126 MB L2) 7.1 ms/step, 20 -> 5.4, 60 -> 4.8: the kernels are latency- not
-  // bandwidth-bound, so fewer, longer launches (better tile balance over 148 SMs) win over L2 residency.  Cap the
-  // workspace at ~2 GB of activation planes.
+  // Utterances per pass over the layer list.  Fewer, longer launches (better tile balance of the persistent kernels
+  // over 148 SMs) beat keeping a layer pair's planes in the 126 MB L2 (bench.py --chunk on 60 x 10 s: a chunk of 6 is
+  // ~1.5x slower per step than the whole batch); the only cap is ~2 GB of activation planes per workspace.
   const double per = (double)L * 32.0 * (double)esize;      // one plane of one utterance
   int c = (int)(2.0e9 / (6.0 * per));
   return std::max(1, std::min(c, 64));
