@@ -158,6 +158,12 @@ SPANON_API int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
                     float top_db, float* recon, float* logp, void* workspace,
                     size_t workspace_bytes, int64_t B, int64_t T, void* stream);
 
+/* FullyConnSexClassifier.forward on its own (models/FullyConnected.py:88-104, eval-mode BatchNorm):
+ * z [B,T,20] (the bottleneck) -> logp [B,2].  Reads only the classifier fields of `w` (clf_norm, init_*, cls_*).
+ * workspace: spanon_fcae_workspace_bytes(B, T). */
+SPANON_API int spanon_fcae_classify(const float* z, const SpanonFcaeWeights* w, const float* pool_noise, float* logp,
+                         void* workspace, size_t workspace_bytes, int64_t B, int64_t T, void* stream);
+
 /* spanon_fcae_fwd for callers that must not allocate and have no workspace to pass (code under CUDA-graph capture,
  * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same arguments and results as spanon_fcae_fwd minus the workspace: the pooling accumulators
@@ -267,7 +273,8 @@ typedef struct SpanonXvectorWeights {
 SPANON_API size_t spanon_xvector_workspace_bytes(int64_t B, int64_t T);
 /* feats [B,T,80] fp32 (already normalised, like classify_batch_feats expects), rel_len [B] relative lengths (NULL = 1.0):
  * pooling runs over round(rel_len * T) frames.  pool_noise [B,1500] is the tensor StatisticsPooling adds to the mean
- * (NULL = none).  emb_out [B,128] (NULL to skip) = the x-vector; logp [B,2] = log posteriors.  weights_prepared = 1: the
+ * (NULL = none).  emb_out [B,128] (NULL to skip) = the x-vector; logp [B,2] = log posteriors (NULL with emb_out given:
+ * Xvector.forward alone, Xvector.py:95-108 -- the classifier fields of `w` are then not read).  weights_prepared = 1: the
  * workspace still holds the packed weights of an earlier call with the same weights. */
 SPANON_API int spanon_xvector_classify(const float* feats, const float* rel_len, const SpanonXvectorWeights* w,
                             const float* pool_noise, float* emb_out, float* logp, void* workspace,

@@ -106,6 +106,8 @@ SIGNATURES = {
     "spanon_fcae_fwd": (C.c_int, [C.c_void_p, C.POINTER(FcaeWeights), C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                   C.c_int64, C.c_int64, C.c_void_p]),
+    "spanon_fcae_classify": (C.c_int, [C.c_void_p, C.POINTER(FcaeWeights), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                       C.c_int64, C.c_int64, C.c_void_p]),
     "spanon_fcae_static_max_batch": (C.c_int64, []),
     "spanon_fcae_fwd_static": (C.c_int, [C.c_void_p, C.POINTER(FcaeWeights), C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,

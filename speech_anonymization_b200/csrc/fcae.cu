@@ -82,6 +82,37 @@ __device__ __forceinline__ void dense(const float* __restrict__ xin, float* __re
   }
 }
 
+// FullyConnSexClassifier up to the pooled sums (FullyConnected.py:93-99) for the 256 frames of one tile: bottleneck z in
+// S.Y[0..20), scratch S.X; `frame`, `b`, `valid` describe this thread's frame.
+__device__ __forceinline__ void fc_clf_tile(FcSmem& S, int tid, int64_t frame, int b, bool valid, int T, double* __restrict__ pool) {
+    // FullyConnected.py:93-95: BatchNorm1d(20) on the [B,20,T] REINTERPRETATION of z
+    const int t = valid ? (int)(frame - (int64_t)b * T) : 0;
+#pragma unroll
+    for (int d = 0; d < 20; ++d) {
+      const int ch = (int)(((int64_t)t * 20 + d) / T);
+      S.X[(60 + d) * LDA + tid] = fmaf(S.Y[d * LDA + tid], S.bn_s[ch], S.bn_t[ch]);
+    }
+    dense<20, 40, true>(S.X + 60 * LDA, S.X, S.W + W_C0, S.Bv + B_C0, tid);
+    dense<40, 40, true>(S.X, S.X + 40 * LDA, S.W + W_C1, S.Bv + B_C1, tid);
+    // StatisticsPooling sums over frames: warp reduce when the whole warp is in one utterance
+    const int b0 = __shfl_sync(0xffffffffu, b, 0);
+    const bool uniform = __all_sync(0xffffffffu, b == b0) && b0 >= 0;
+#pragma unroll 1
+    for (int c = 0; c < 40; ++c) {
+      const float h = valid ? S.X[(40 + c) * LDA + tid] : 0.f;
+      if (uniform) {
+        const float s = warp_sum(h), q = warp_sum(h * h);
+        if ((tid & 31) == 0) {
+          atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 0, (double)s);
+          atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 1, (double)q);
+        }
+      } else if (valid) {
+        atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 0, (double)h);
+        atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 1, (double)h * (double)h);
+      }
+    }
+}
+
 __global__ void __launch_bounds__(NTHR, 1)
 fcae_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* __restrict__ norm_mean,
             const float* __restrict__ norm_std, const int32_t* __restrict__ utt_max, float top_db,
@@ -143,34 +174,7 @@ fcae_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* _
     const int64_t frame = f0 + tid;
     const bool valid = tid < nf;
     const int b = valid ? (int)(frame / T) : -1;
-    if (run_clf) {
-      // FullyConnected.py:93-95: BatchNorm1d(20) on the [B,20,T] REINTERPRETATION of z
-      const int t = valid ? (int)(frame - (int64_t)b * T) : 0;
-#pragma unroll
-      for (int d = 0; d < 20; ++d) {
-        const int ch = (int)(((int64_t)t * 20 + d) / T);
-        S.X[(60 + d) * LDA + tid] = fmaf(S.Y[d * LDA + tid], S.bn_s[ch], S.bn_t[ch]);
-      }
-      dense<20, 40, true>(S.X + 60 * LDA, S.X, S.W + W_C0, S.Bv + B_C0, tid);
-      dense<40, 40, true>(S.X, S.X + 40 * LDA, S.W + W_C1, S.Bv + B_C1, tid);
-      // StatisticsPooling sums over frames: warp reduce when the whole warp is in one utterance
-      const int b0 = __shfl_sync(0xffffffffu, b, 0);
-      const bool uniform = __all_sync(0xffffffffu, b == b0) && b0 >= 0;
-#pragma unroll 1
-      for (int c = 0; c < 40; ++c) {
-        const float h = valid ? S.X[(40 + c) * LDA + tid] : 0.f;
-        if (uniform) {
-          const float s = warp_sum(h), q = warp_sum(h * h);
-          if ((tid & 31) == 0) {
-            atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 0, (double)s);
-            atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 1, (double)q);
-          }
-        } else if (valid) {
-          atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 0, (double)h);
-          atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 1, (double)h * (double)h);
-        }
-      }
-    }
+    if (run_clf) fc_clf_tile(S, tid, frame, b, valid, T, pool);
     dense<20, 40, true>(S.Y, S.X, S.W + W_D0, S.Bv + B_D0, tid);
     dense<40, 60, true>(S.X, S.Y, S.W + W_D1, S.Bv + B_D1, tid);
     dense<60, 80, false>(S.Y, S.X, S.W + W_D2, S.Bv + B_D2, tid);
@@ -180,6 +184,38 @@ fcae_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* _
       const int fr = e / D_IN, d = e - fr * D_IN;
       dst[e] = S.X[d * LDA + fr];
     }
+    __syncthreads();
+  }
+}
+
+// FullyConnSexClassifier.forward on its own (FullyConnected.py:88-104): the bottleneck z [B, T, 20] comes from the caller.
+__global__ void __launch_bounds__(NTHR, 1)
+fc_clf_kernel(const float* __restrict__ z, SpanonFcaeWeights w, double* __restrict__ pool, int64_t n_frames, int T) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FcSmem& S = *reinterpret_cast<FcSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  load_wt(S.W + W_C0, w.init_w[0], 40, 20, tid);
+  load_wt(S.W + W_C1, w.init_w[1], 40, 40, tid);
+  for (int i = tid; i < 40; i += NTHR) { S.Bv[B_C0 + i] = w.init_b[0][i]; S.Bv[B_C1 + i] = w.init_b[1][i]; }
+  if (tid < 20) {
+    const float s = w.clf_norm.weight[tid] / sqrtf(w.clf_norm.running_var[tid] + 1e-5f);
+    S.bn_s[tid] = s;
+    S.bn_t[tid] = w.clf_norm.bias[tid] - w.clf_norm.running_mean[tid] * s;
+  }
+  __syncthreads();
+  const int64_t n_tiles = (n_frames + NTHR - 1) / NTHR;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t f0 = tile * NTHR;
+    const int nf = (int)min((int64_t)NTHR, n_frames - f0);
+    for (int e = tid; e < NTHR * 20; e += NTHR) {
+      const int fr = e / 20, d = e - fr * 20;
+      S.Y[d * LDA + fr] = fr < nf ? __ldg(z + f0 * 20 + e) : 0.f;
+    }
+    __syncthreads();
+    const int64_t frame = f0 + tid;
+    const bool valid = tid < nf;
+    const int b = valid ? (int)(frame / T) : -1;
+    fc_clf_tile(S, tid, frame, b, valid, T, pool);
     __syncthreads();
   }
 }
@@ -278,6 +314,35 @@ extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
     SPANON_TRY(check_launch("fcae_head_kernel"));
   }
   return SPANON_OK;
+}
+
+
+// FullyConnSexClassifier.forward alone (models/FullyConnected.py:88-104, eval-mode BatchNorm): z [B, T, 20] -> log-probs [B, 2].
+// Only the classifier fields of `w` are read (clf_norm, init_*, cls_*).  workspace: spanon_fcae_workspace_bytes(B, T).
+extern "C" int spanon_fcae_classify(const float* z, const SpanonFcaeWeights* w, const float* pool_noise, float* logp,
+                                    void* workspace, size_t workspace_bytes, int64_t B, int64_t T, void* stream) {
+  if (!w) return SPANON_ERR_NULL_POINTER;
+  if (B < 0 || T < 0) return SPANON_ERR_BAD_SHAPE;
+  if (B == 0) return SPANON_OK;
+  if (T == 0) return SPANON_ERR_BAD_SHAPE;
+  if (!z || !logp || !workspace) return SPANON_ERR_NULL_POINTER;
+  if (workspace_bytes < spanon_fcae_workspace_bytes(B, T)) return SPANON_ERR_WORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 7) return SPANON_ERR_MISALIGNED;
+  cudaStream_t st = as_stream(stream);
+  static std::atomic<unsigned long long> attr_done{0};
+  int dev = 0;
+  const int n_sm = current_device_sms(&dev);
+  if (n_sm <= 0) return SPANON_ERR_CUDA;
+  if (first_use_on_device(attr_done, dev))
+    SPANON_CUDA_TRY(cudaFuncSetAttribute(fc_clf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FcSmem)));
+  double* pool = reinterpret_cast<double*>(workspace);
+  SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
+  const int64_t n_frames = B * T;
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n_frames, NTHR), n_sm);
+  fc_clf_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(z, *w, pool, n_frames, (int)T);
+  SPANON_TRY(check_launch("fc_clf_kernel"));
+  fcae_head_kernel<<<(unsigned)B, 64, 0, st>>>(pool, pool_noise, *w, (int)T, logp);
+  return check_launch("fcae_head_kernel");
 }
 
 

@@ -320,6 +320,7 @@ xv_head_kernel(const float* __restrict__ pooled, SpanonXvectorWeights w, int n_c
   }
   __syncthreads();
   if (emb_out) emb_out[(int64_t)b * XV_EMB + tid] = e[tid];
+  if (!logp) return;                                                // Xvector.forward alone: the embedding is the result
   const float x0 = xv_bn(xv_leaky(e[tid]), w.clf_norm, tid);      // Classifier: act -> norm
   __syncthreads();
   e[tid] = x0;
@@ -395,7 +396,7 @@ extern "C" int spanon_xvector_classify(const float* feats, const float* rel_len,
   if (B < 0 || T <= 0 || F != XV_CIN[0]) return SPANON_ERR_BAD_SHAPE;
   if (T < 4) return SPANON_ERR_BAD_SHAPE;     // reflect padding of 3 frames needs T > 3 (torch raises as well)
   if (B == 0) return SPANON_OK;
-  if (!feats || !logp || !workspace) return SPANON_ERR_NULL_POINTER;
+  if (!feats || (!logp && !emb_out) || !workspace) return SPANON_ERR_NULL_POINTER;
   if (B > 65535) return SPANON_ERR_BAD_SHAPE;
   if (workspace_bytes < spanon_xvector_workspace_bytes(B, T)) return SPANON_ERR_WORKSPACE;
   cudaStream_t st = as_stream(stream);

@@ -98,7 +98,9 @@ def _precision_from_env():
 
 
 class TDNNSexClassifier(nn.Module):
-    """models/ConvAutoEncoder.py:30-69 (parameter container; computed inside spanon_convae_fwd)."""
+    """models/ConvAutoEncoder.py:30-69.  Inside ConvAutoencoder.forward the classifier runs fused in spanon_convae_fwd;
+    called on its own (forward(input [B, 128, L']) -> log-probs [B, 2], :57-69) it runs on the fp32 training kernels
+    (train.tdnn_classifier_forward): batch statistics + autograd in train mode, running statistics under no_grad in eval."""
 
     def __init__(self, num_classes):
         super().__init__()
@@ -115,8 +117,15 @@ class TDNNSexClassifier(nn.Module):
             nn.Linear(64, num_classes),
         )
 
-    def forward(self, input):
-        raise NotImplementedError("TDNNSexClassifier runs fused inside ConvAutoencoder.forward")
+    def forward(self, input, pool_noise=None):
+        _lib.require_cuda(input, "input")
+        if input.dim() != 3 or input.shape[1] != 128:
+            raise RuntimeError("TDNNSexClassifier expects [batch, 128, time] (channels first), got %s" % (tuple(input.shape),))
+        if input.shape[2] < 15:
+            raise RuntimeError("TDNNSexClassifier: the three TDNN layers need at least 15 time steps")
+        from . import train
+        return train.tdnn_classifier_forward(self, input.float().transpose(1, 2).contiguous(), pool_noise,
+                                             getattr(self, "sync_bn_group", None))
 
 
 class ConvAutoencoder(nn.Module):
@@ -376,7 +385,7 @@ class _SbLinear(nn.Module):
 class Xvector(nn.Module):
     """Parameter container for speechbrain.lobes.models.Xvector.Xvector (Xvector.py:45-93) in the configuration of
     evaluator_inference.yaml:34-41; `state_dict()` keys = the reference's embedding_model.ckpt (`blocks.{0,3,6,9,12}.conv.*`,
-    `blocks.{2,5,8,11,14}.norm.*`, `blocks.16.w.*`).  Computed inside XvectorClassifier."""
+    `blocks.{2,5,8,11,14}.norm.*`, `blocks.16.w.*`).  forward() = the embedding part of spanon_xvector_classify."""
 
     def __init__(self, device="cpu", activation=nn.LeakyReLU, tdnn_blocks=5, tdnn_channels=[512, 512, 512, 512, 1500],
                  tdnn_kernel_sizes=[5, 3, 3, 1, 1], tdnn_dilations=[1, 2, 3, 1, 1], lin_neurons=512, in_channels=40):
@@ -397,8 +406,15 @@ class Xvector(nn.Module):
         self.blocks.append(StatisticsPooling())
         self.blocks.append(_SbLinear(2 * cin, lin_neurons))
 
-    def forward(self, x, lens=None):
-        raise NotImplementedError("Xvector runs fused inside XvectorClassifier.classify_batch_feats")
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d.pop("_ws_cache", None)
+        return d
+
+    @torch.no_grad()
+    def forward(self, x, lens=None, pool_noise=None):
+        """Xvector.py:95-108: features [B, T, 80] (+ relative lengths) -> x-vectors [B, 1, lin_neurons]."""
+        return _xvector_run(self, self, None, x, lens, pool_noise)[0]
 
 
 class _SbDNNBlock(nn.Module):
@@ -431,6 +447,60 @@ class XvectorHead(nn.Module):
         self.out = _SbLinear(128, out_neurons)
 
 
+def _xvector_weight_struct(e, c):
+    """SpanonXvectorWeights of an Xvector `e` and (optionally) its Classifier head `c`."""
+    w = _lib.XvectorWeights()
+    for i in range(5):
+        w.tdnn_w[i], w.tdnn_b[i] = _p(e.blocks[3 * i].conv.weight), _p(e.blocks[3 * i].conv.bias)
+        w.tdnn_bn[i] = _bn(e.blocks[3 * i + 2].norm)
+    w.emb_w, w.emb_b = _p(e.blocks[16].w.weight), _p(e.blocks[16].w.bias)
+    if c is not None:
+        w.clf_norm = _bn(c.norm.norm)
+        w.dnn_w, w.dnn_b = _p(c.DNN.block_0.linear.w.weight), _p(c.DNN.block_0.linear.w.bias)
+        w.dnn_bn = _bn(c.DNN.block_0.norm.norm)
+        w.out_w, w.out_b = _p(c.out.w.weight), _p(c.out.w.bias)
+    return w
+
+
+def _xvector_run(owner, emb_model, classifier, feats, wav_lens, pool_noise):
+    """spanon_xvector_classify for `owner` (the module that keeps the workspace / packed-weight cache): returns
+    (embeddings [B,1,128], log-probs [B,2] or None when `classifier` is None)."""
+    _lib.require_cuda(feats, "feats")
+    _forward_only_guard(owner, feats)
+    if feats.dim() != 3 or feats.shape[2] != 80:
+        raise ValueError("%s expects [batch, time, 80] features" % type(owner).__name__)
+    if emb_model.lin_neurons != 128 or emb_model.in_channels != 80:
+        raise NotImplementedError("the CUDA x-vector path computes evaluator_inference.yaml's model "
+                                  "(in_channels=80, lin_neurons=128)")
+    x = feats.contiguous()
+    B, T, F = x.shape
+    dev = x.device
+    emb = torch.empty((B, 1, 128), dtype=torch.float32, device=dev)
+    logp = torch.empty((B, 2), dtype=torch.float32, device=dev) if classifier is not None else None
+    if B == 0:
+        return emb, logp
+    if wav_lens is not None:
+        wav_lens = wav_lens.to(device=dev, dtype=torch.float32).contiguous()
+    if pool_noise is None:
+        pool_noise = emb_model.blocks[15]._get_gauss_noise((B, 1500), device=dev)
+    pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
+    w = _xvector_weight_struct(emb_model, classifier)
+    L = _lib.lib()
+    ws_bytes = L.spanon_xvector_workspace_bytes(B, T)
+    key = (B, T, str(dev), tuple((t.data_ptr(), t._version) for t in list(owner.parameters()) + list(owner.buffers())))
+    cache = owner.__dict__.get("_ws_cache")
+    if cache is None or cache[0].numel() != ws_bytes or cache[0].device != dev:
+        cache = [torch.empty((ws_bytes,), dtype=torch.uint8, device=dev), None]
+        owner.__dict__["_ws_cache"] = cache
+    prepared = 1 if cache[1] == key else 0
+    cache[1] = key
+    with torch.cuda.device(dev):
+        _lib.check(L.spanon_xvector_classify(_lib.ptr(x), _lib.ptr(wav_lens), C.byref(w), _lib.ptr(pool_noise),
+                                             _lib.ptr(emb), _lib.ptr(logp), _lib.ptr(cache[0]), ws_bytes, B, T, F,
+                                             prepared, _lib.stream_ptr(dev)), "xvector_classify")
+    return emb, logp
+
+
 class XvectorClassifier(nn.Module):
     """The external gender classifier of the evaluation configs: drop-in for the parts of
     speechbrain.pretrained.EncoderClassifier the reference uses on FEATURES (interfaces.py:762-776, 825-829) with
@@ -447,17 +517,7 @@ class XvectorClassifier(nn.Module):
         self.classifier = classifier if classifier is not None else XvectorHead()
 
     def weight_struct(self):
-        e, c = self.embedding_model, self.classifier
-        w = _lib.XvectorWeights()
-        for i in range(5):
-            w.tdnn_w[i], w.tdnn_b[i] = _p(e.blocks[3 * i].conv.weight), _p(e.blocks[3 * i].conv.bias)
-            w.tdnn_bn[i] = _bn(e.blocks[3 * i + 2].norm)
-        w.emb_w, w.emb_b = _p(e.blocks[16].w.weight), _p(e.blocks[16].w.bias)
-        w.clf_norm = _bn(c.norm.norm)
-        w.dnn_w, w.dnn_b = _p(c.DNN.block_0.linear.w.weight), _p(c.DNN.block_0.linear.w.bias)
-        w.dnn_bn = _bn(c.DNN.block_0.norm.norm)
-        w.out_w, w.out_b = _p(c.out.w.weight), _p(c.out.w.bias)
-        return w
+        return _xvector_weight_struct(self.embedding_model, self.classifier)
 
     def __getstate__(self):
         d = dict(self.__dict__)
@@ -465,40 +525,7 @@ class XvectorClassifier(nn.Module):
         return d
 
     def _run(self, feats, wav_lens, pool_noise):
-        _lib.require_cuda(feats, "feats")
-        _forward_only_guard(self, feats)
-        if feats.dim() != 3 or feats.shape[2] != 80:
-            raise ValueError("XvectorClassifier expects [batch, time, 80] features")
-        if self.embedding_model.lin_neurons != 128 or self.embedding_model.in_channels != 80:
-            raise NotImplementedError("the CUDA x-vector path computes evaluator_inference.yaml's model "
-                                      "(in_channels=80, lin_neurons=128)")
-        x = feats.contiguous()
-        B, T, F = x.shape
-        dev = x.device
-        emb = torch.empty((B, 1, 128), dtype=torch.float32, device=dev)
-        logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
-        if B == 0:
-            return emb, logp
-        if wav_lens is not None:
-            wav_lens = wav_lens.to(device=dev, dtype=torch.float32).contiguous()
-        if pool_noise is None:
-            pool_noise = self.embedding_model.blocks[15]._get_gauss_noise((B, 1500), device=dev)
-        pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
-        w = self.weight_struct()
-        L = _lib.lib()
-        ws_bytes = L.spanon_xvector_workspace_bytes(B, T)
-        key = (B, T, str(dev), tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers())))
-        cache = self.__dict__.get("_ws_cache")
-        if cache is None or cache[0].numel() != ws_bytes or cache[0].device != dev:
-            cache = [torch.empty((ws_bytes,), dtype=torch.uint8, device=dev), None]
-            self.__dict__["_ws_cache"] = cache
-        prepared = 1 if cache[1] == key else 0
-        cache[1] = key
-        with torch.cuda.device(dev):
-            _lib.check(L.spanon_xvector_classify(_lib.ptr(x), _lib.ptr(wav_lens), C.byref(w), _lib.ptr(pool_noise),
-                                                 _lib.ptr(emb), _lib.ptr(logp), _lib.ptr(cache[0]), ws_bytes, B, T, F,
-                                                 prepared, _lib.stream_ptr(dev)), "xvector_classify")
-        return emb, logp
+        return _xvector_run(self, self.embedding_model, self.classifier, feats, wav_lens, pool_noise)
 
     @torch.no_grad()
     def encode_batch_feat(self, feats, wav_lens=None, normalize=False, pool_noise=None):
@@ -519,7 +546,8 @@ class XvectorClassifier(nn.Module):
 
 
 class FullyConnSexClassifier(nn.Module):
-    """models/FullyConnected.py:65-104 (parameter container; computed inside spanon_fcae_fwd)."""
+    """models/FullyConnected.py:65-104.  Inside FullyConnectedAutoencoder.forward the classifier runs fused in spanon_fcae_fwd;
+    called on its own, forward(z [B, T, 20]) -> log-probs [B, 2] runs spanon_fcae_classify (eval-mode BatchNorm, forward only)."""
 
     def __init__(self, num_classes):
         super().__init__()
@@ -533,8 +561,44 @@ class FullyConnSexClassifier(nn.Module):
         )
         self.stats_pooling = StatisticsPooling()
 
-    def forward(self, input):
-        raise NotImplementedError("FullyConnSexClassifier runs fused inside FullyConnectedAutoencoder.forward")
+    def fill_weight_struct(self, w):
+        s = self
+        w.clf_norm = _bn(s.norm)
+        for i, k in enumerate((0, 2)):
+            w.init_w[i], w.init_b[i] = _p(s.initial[k].weight), _p(s.initial[k].bias)
+        for i, k in enumerate((0, 3, 5, 7)):
+            w.cls_w[i], w.cls_b[i] = _p(s.classify[k].weight), _p(s.classify[k].bias)
+        w.cls_bn1, w.cls_bn6 = _bn(s.classify[1]), _bn(s.classify[6])
+        return w
+
+    def forward(self, input, pool_noise=None):
+        _lib.require_cuda(input, "input")
+        _forward_only_guard(self, input)
+        if input.dim() != 3 or input.shape[2] != 20:
+            raise RuntimeError("FullyConnSexClassifier expects [batch, time, 20], got %s" % (tuple(input.shape),))
+        if self.training:
+            raise NotImplementedError("FullyConnSexClassifier: the CUDA path is the eval-mode forward (running statistics)")
+        z = input.float().contiguous()
+        B, T, _ = z.shape
+        dev = z.device
+        logp = torch.empty((B, 2), dtype=torch.float32, device=dev)
+        if B == 0:
+            return logp
+        if T == 0:
+            raise RuntimeError("FullyConnSexClassifier: empty time axis")
+        if pool_noise is None:
+            pool_noise = self.stats_pooling._get_gauss_noise((B, 40), device=dev)
+        pool_noise = pool_noise.to(device=dev, dtype=torch.float32).contiguous()
+        w = _lib.FcaeWeights()
+        w.in_dim = 80
+        self.fill_weight_struct(w)
+        L = _lib.lib()
+        ws_bytes = L.spanon_fcae_workspace_bytes(B, T)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(L.spanon_fcae_classify(_lib.ptr(z), C.byref(w), _lib.ptr(pool_noise), _lib.ptr(logp), _lib.ptr(ws),
+                                              ws_bytes, B, T, _lib.stream_ptr(dev)), "fcae_classify")
+        return logp
 
 
 class FullyConnectedAutoencoder(nn.Module):
@@ -566,13 +630,7 @@ class FullyConnectedAutoencoder(nn.Module):
         for i, k in enumerate((0, 2, 4)):
             w.enc_w[i], w.enc_b[i] = _p(e[k].weight), _p(e[k].bias)
             w.dec_w[i], w.dec_b[i] = _p(d[k].weight), _p(d[k].bias)
-        w.clf_norm = _bn(s.norm)
-        for i, k in enumerate((0, 2)):
-            w.init_w[i], w.init_b[i] = _p(s.initial[k].weight), _p(s.initial[k].bias)
-        for i, k in enumerate((0, 3, 5, 7)):
-            w.cls_w[i], w.cls_b[i] = _p(s.classify[k].weight), _p(s.classify[k].bias)
-        w.cls_bn1, w.cls_bn6 = _bn(s.classify[1]), _bn(s.classify[6])
-        return w
+        return s.fill_weight_struct(w)
 
     def forward(self, input, pool_noise=None, fused_norm=None):
         """`fused_norm` = (mean [F], std [F], utt_max [B], top_db): input is RAW Fbank dB."""

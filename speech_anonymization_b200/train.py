@@ -285,10 +285,52 @@ def _sync_bn_rows(x, m, group):
     return (x - mean) * torch.rsqrt(var + m.eps) * m.weight + m.bias
 
 
+def _bnorm_frozen(z, m):
+    """eval-mode BatchNorm1d on a channels-last tensor: the running statistics enter spanon_norm_act_fwd as the sums of ONE
+    pseudo-sample per channel (sum = mean, sum of squares = var + mean^2, count 1), so the same kernels normalise with them."""
+    rm, rv = m.running_mean.double(), m.running_var.double()
+    stats = torch.stack((rm, rv + rm * rm), dim=1).reshape(1, -1, 2).contiguous()
+    B, rows, Cc = z.shape
+    out = torch.empty_like(z)
+    mean = torch.empty((Cc,), dtype=torch.float32, device=z.device)
+    rstd = torch.empty((Cc,), dtype=torch.float32, device=z.device)
+    with torch.cuda.device(z.device):
+        _call(_lib.lib().spanon_norm_act_fwd, _lib.ptr(z), _lib.ptr(stats), _lib.ptr(m.weight), _lib.ptr(m.bias), 1, 0, float(m.eps),
+              None, None, 0.0, _lib.ptr(out), _lib.ptr(mean), _lib.ptr(rstd), B, rows, Cc, 1, 1.0, _lib.stream_ptr(z.device),
+              what="norm_act_fwd")
+    return out
+
+
+def tdnn_classifier_forward(s, enc, pool_noise=None, group=None, _taps=None):
+    """TDNNSexClassifier.forward (models/ConvAutoEncoder.py:57-69) on a CHANNELS-LAST bottleneck `enc` [B, L', 128]:
+    GradReverse -> BatchNorm -> 3 x (conv, ReLU, BatchNorm) -> reshape + StatisticsPooling -> MLP -> log_softmax.
+    Train mode: batch statistics, attached to the autograd graph.  Eval mode: running statistics, forward only."""
+    from .models import GradReverse
+    B = enc.shape[0]
+    if s.training:
+        c = GradReverse.apply(enc)
+        c = _bnorm(c, colstats(c.detach()), s.norm, 0, group)
+    else:
+        if torch.is_grad_enabled() and (enc.requires_grad or any(p.requires_grad for p in s.parameters())):
+            raise NotImplementedError("TDNNSexClassifier: a backward pass through eval-mode BatchNorm is not built; call "
+                                      ".train() for a training step or run under torch.no_grad()")
+        c = _bnorm_frozen(enc.contiguous(), s.norm)
+    if _taps is not None:      # (debugging aid: intermediate tensors, channels-last)
+        _taps["enc"], _taps["norm"] = enc, c
+    for i in (0, 3, 6):
+        r, st = _conv(c, s.tdnn[i], 0, relu=1, want_stats=s.training)
+        c = _bnorm(r, st, s.tdnn[i + 2], 1, group) if s.training else _bnorm_frozen(r, s.tdnn[i + 2])
+        if _taps is not None:
+            _taps["relu%d" % i], _taps["bn%d" % (i + 2)] = r, c
+    if pool_noise is None:
+        pool_noise = s.stats_pooling._get_gauss_noise((B, 128), device=enc.device)
+    pooled = _PoolReinterp.apply(c, pool_noise.to(device=enc.device, dtype=torch.float32).contiguous())
+    return F.log_softmax(_classify_head(s.classify, pooled, group if s.training else None), 1)
+
+
 def convae_train_forward(model, feats, pool_noise=None, _taps=None, on_encoder_grad=None):
     """ConvAutoencoder.forward in TRAIN mode (batch-statistics BatchNorm in the sex classifier) with a backward pass.
     feats [B, T, F] fp32 CUDA -> (reconstruction [B, T, F], sex log-probs [B, 2]), both attached to the autograd graph."""
-    from .models import GradReverse
     B, T, Fd = feats.shape
     Lf = T * Fd
     e, d, s = model.encoder, model.decoder, model.sex_classifier
@@ -309,19 +351,7 @@ def convae_train_forward(model, feats, pool_noise=None, _taps=None, on_encoder_g
     if on_encoder_grad is not None and enc.requires_grad:
         # fires when both branches' gradients have reached the bottleneck: every decoder / classifier gradient is final
         enc.register_hook(lambda g: (on_encoder_grad(), g)[1])
-    c = GradReverse.apply(enc)
-    c = _bnorm(c, colstats(c.detach()), s.norm, 0, group)
-    if _taps is not None:      # (debugging aid: intermediate tensors, channels-last)
-        _taps["enc"], _taps["norm"] = enc, c
-    for i in (0, 3, 6):
-        r, st = _conv(c, s.tdnn[i], 0, relu=1, want_stats=True)
-        c = _bnorm(r, st, s.tdnn[i + 2], 1, group)
-        if _taps is not None:
-            _taps["relu%d" % i], _taps["bn%d" % (i + 2)] = r, c
-    if pool_noise is None:
-        pool_noise = s.stats_pooling._get_gauss_noise((B, 128), device=feats.device)
-    pooled = _PoolReinterp.apply(c, pool_noise.to(device=feats.device, dtype=torch.float32).contiguous())
-    logp = F.log_softmax(_classify_head(s.classify, pooled, group), 1)
+    logp = tdnn_classifier_forward(s, enc, pool_noise, group, _taps)
     # ---- decoder (:160-172)
     z, _ = _conv(enc, d[0], 0)
     z, st = _conv(z, d[1], 2, want_stats=True)
