@@ -1,5 +1,6 @@
 // Shared helpers for libspanon (sm_100a only).
 #pragma once
+#include <stdlib.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -101,6 +102,31 @@ template <> __device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(f
 }
 
 template <> __device__ __forceinline__ __half from_float<__half>(float v) { return __float2half_rn(v); }
+
+// ---- programmatic dependent launch (PDL).  A kernel launched through launch_pdl() may begin while its predecessor on the
+// stream is still running: its CTAs become resident as the predecessor's CTAs exit, run their prologue (barrier init, tensor
+// memory allocation, weight copies -- nothing the predecessor produces) and then block in pdl_wait() until the predecessor
+// grid has COMPLETED and its memory is visible.  Every kernel launched this way must call pdl_wait() before its first read or
+// write of anything an earlier kernel touches; completion is transitive along the chain.  $SPANON_PDL=0: plain launches.
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("SPANON_PDL") && getenv("SPANON_PDL")[0] == '0');
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#ifdef __CUDACC__
+// (both are no-ops in a kernel launched without the attribute)
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 
 // Per-device one-time setup (cudaFuncSetAttribute is a per-device setting, and one process may drive several GPUs):
 // returns true the first time it is called with `mask` while device `dev` is current.  Thread-safe.

@@ -169,6 +169,7 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
     else if (k_next < n_my_tiles) locate(k_next, b, tin);
   };
 
+  pdl_launch_dependents();      // the next kernel's CTAs may take this SM as soon as this CTA exits (common.cuh)
   if (warp == TC_MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < L.n_stages; ++i) {
@@ -206,6 +207,7 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                   // everything above touched only constants (weights, biases); the planes come from the predecessor
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int planes_in = p.cin_v / 8;
 
@@ -808,7 +810,8 @@ int launch_tc_mg(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int grid = std::min(total, n_sm);
   static const bool trace_on = getenv("SPANON_TC_TRACE") && getenv("SPANON_TC_TRACE")[0] == '1';
   if (!trace_on) {
-    kern<<<grid, tc_threads(XF), L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total, tile_step, mma_group);
+    SPANON_CUDA_TRY(launch_pdl(kern, dim3((unsigned)grid), dim3((unsigned)tc_threads(XF)), L.total, st, p.pdl != 0, p, halo_lo, slab_used,
+                               tiles_per_utt, total, tile_step, mma_group));
     return check_launch(p.tag ? p.tag : "tapgemm_tc_kernel");
   }
   // debug: clock64 stamps of CTA 0's three roles, printed after a synchronising launch

@@ -15,6 +15,7 @@
 //               tcgen05.mma.cta_group::2 (M = 256: rows 0..127 from its own shared memory / TMEM, 128..255 from the
 //               peer's at the same offsets), and commits with .multicast::cluster so that `empty` / `tmem_full` fire in
 //               both CTAs.  The epilogue warps of both CTAs hand the accumulator back on the leader's `tmem_empty`.
+#include <type_traits>
 #include "tapgemm.cuh"
 #include "tc_prims.cuh"
 #include <cuda_fp16.h>
@@ -28,20 +29,20 @@ using namespace tc;
 constexpr int T2_N = 128;                   // output columns of the layer (both CTAs together)
 constexpr int T2_NH = T2_N / 2;             // weight columns resident per CTA
 constexpr int T2_XF_WARPS = 8, T2_LOAD_WARPS = 2, T2_STAGE_CH = 16, T2_MAX_STAGES = 16;
-__host__ __device__ constexpr int t2_epi_warps(int xf) { return (xf & 8) ? 8 : 4; }      // 8 = X2_STATS
+__host__ __device__ constexpr int t2_epi_warps(int xf) { return (xf & 24) ? 8 : 4; }     // 8 = X2_STATS, 16 = X2_POOL
 __host__ __device__ constexpr int t2_threads(int xf) { return (t2_epi_warps(xf) + 12) * 32; }
 #ifndef T2_MG_VALUE
 #define T2_MG_VALUE 2
 #endif
 constexpr int T2_MG = T2_MG_VALUE;            // stages per MMA issue round (divides the 8 stages of a tile)
 constexpr size_t T2_SMEM_LIMIT = 232448;
-enum { X2_IDENT = 0, X2_SILU = 1, X2_RELU = 2, X2_T2 = 4, X2_STATS = 8 };
+enum { X2_IDENT = 0, X2_SILU = 1, X2_RELU = 2, X2_T2 = 4, X2_STATS = 8, X2_POOL = 16 };
 constexpr int T2_ST_PITCH = 17;
 enum { C_RAW = 0, C_FULL = 16, C_EMPTY = 32, C_TFULL = 48, C_TEMPTY = 50, C_W = 52, C_TPTR = 54 };
 
 struct T2Layout { uint32_t w, epi, red, bars, a, total, w_bytes, stage_bytes, lbo_a; int n_stages, slab; };
 
-__host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_used, bool stats) {
+__host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_used, bool stats, bool pool = false) {
   T2Layout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;
   L.lbo_a = (uint32_t)L.slab * 16u;
@@ -49,8 +50,9 @@ __host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_use
   L.w_bytes = (uint32_t)ntaps * cin_v * T2_NH * 2u;
   L.w = 0;
   L.epi = L.w + L.w_bytes;                               // bias [128] fp32
-  L.red = L.epi + T2_N * 4u;                             // statistics: one [32][17] transpose buffer per epilogue warp
-  L.bars = L.red + (stats ? 8u * 32u * T2_ST_PITCH * 4u : 0u);
+  L.red = (L.epi + T2_N * 4u * (pool ? 3u : 1u) + 7u) / 8u * 8u;          // (pooling: bias, scale, shift)
+  // statistics: one [32][17] transpose buffer per epilogue warp; pooling: the CTA's [128 bins][sum, sum of squares]
+  L.bars = L.red + (stats ? 8u * 32u * T2_ST_PITCH * 4u : pool ? 2u * T2_N * 8u : 0u);
   L.a = (L.bars + 512u + 127u) / 128u * 128u;
   const size_t avail = T2_SMEM_LIMIT > L.a ? T2_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
@@ -115,9 +117,11 @@ template <int XF>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(t2_threads(XF), 1)
 tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0);
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int E = t2_epi_warps(XF), MMA_WARP = E + 11;
+  // tensor memory: two accumulator buffers
+  constexpr int T2_TMEM_COLS = (XF & X2_POOL) ? 4 * T2_N : 2 * T2_N;      // (a power of two; the pooling sums use 128 more)
   const int wd = warp - E;
   const bool is_loader = wd == 3 || wd == 7, is_xform = wd >= 0 && wd < 10 && !is_loader;
   const uint32_t rank = cluster_rank();
@@ -140,6 +144,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
     else { b = t / tiles_per_utt; tin = t - b * tiles_per_utt; }
   };
 
+  pdl_launch_dependents();      // (common.cuh: programmatic dependent launch)
   if (warp == MMA_WARP) {
     if (lane == 0) {
       for (int i = 0; i < L.n_stages; ++i) {
@@ -159,19 +164,23 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
     }
     __syncwarp();
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_ptr_smem)),
-                 "r"(2 * T2_N)
+                 "r"(T2_TMEM_COLS)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     mbar_wait(BAR(C_W), 0);                   // (before the cluster barrier below: the peer's half is then in place too)
   }
   if (warp < E) {
     float* ec = reinterpret_cast<float*>(smem + L.epi);
-    for (int c = threadIdx.x; c < T2_N; c += E * 32) ec[c] = p.bias ? p.bias[c % p.cout_mod] : 0.f;
+    for (int c = threadIdx.x; c < T2_N; c += E * 32) {
+      ec[c] = p.bias ? p.bias[c % p.cout_mod] : 0.f;
+      if constexpr ((XF & X2_POOL) != 0) { ec[T2_N + c] = p.e_scale[c]; ec[2 * T2_N + c] = p.e_shift[c]; }
+    }
   }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                         // both CTAs' barriers initialised and weights landed before any remote access
   tc_fence_after();
+  pdl_wait();                                 // only constants were touched so far; the planes come from the predecessor
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int planes_in = p.cin_v / 8;
 
@@ -335,6 +344,125 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
     const float* ec = reinterpret_cast<const float*>(smem + L.epi);
     const int quarter = warp & 3, chalf = warp >> 2;      // E = 8: two warps per TMEM lane quarter, half of the columns each
     const int mloc = quarter * 32 + lane;
+    if constexpr ((XF & X2_POOL) != 0) {
+      // ---- tdnn.6 + ReLU + BatchNorm + reshape + StatisticsPooling sums (ConvAutoEncoder.py:60-64): nothing is stored.
+      // The reference pools the [128][rows_out] channels-first image REINTERPRETED as [rows_out][128]: value (row m,
+      // channel c) lands in bin (c * rows_out + m) mod 128 = (m mod 128 + c * (rows_out mod 128)) mod 128, and m mod 128
+      // is this thread's TMEM lane for every tile.  So running sums (value, square) per (lane, channel) over all tiles of one
+      // utterance live in the tensor-memory columns the accumulators do not use, and only when the utterance changes are
+      // they rotated into the CTA's 128 bins (shared-memory fp64 atomics), then one fp64 atomic per bin and CTA.
+      // Channels c and c + 64 of one row fall into the SAME bin when rows_out is even (64 * rot = 0 mod 128), so one pair of
+      // sums serves both: 2 x 64 tensor-memory columns.  The epilogue is paced by tcgen05.ld (~64 B/clk per SM): per tile it
+      // reads the accumulator (64 KB) plus the sums (64 KB) -- sums per single channel (128 KB) ran at 158 us against 123 us
+      // for the plain store epilogue, register-resident sums did not fit beside the transform warps' 96 registers.
+      double* red = reinterpret_cast<double*>(smem + L.red);
+      const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+      const int c_lo = chalf * 32;                          // eight warps: two per lane quarter, channels [c_lo, +32) and +64
+      const uint32_t t_s = tmem_base + 2u * T2_N + lane_off, t_q = t_s + (uint32_t)(T2_N / 2);
+      const int rot = p.rows_out & 127;
+      auto pool_bar = [] { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+      {
+        float z[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) { tmem_st8(t_s + (uint32_t)(c_lo + i), z); tmem_st8(t_q + (uint32_t)(c_lo + i), z); }
+        tmem_st_wait();
+        red[threadIdx.x] = 0.0;
+        pool_bar();
+      }
+      auto flush = [&](int bb) {
+        float z[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = 0.f;
+#pragma unroll 1
+        for (int i = 0; i < 32; i += 8) {
+          float s_[8], q[8];
+          tmem_ld8_nowait(t_s + (uint32_t)(c_lo + i), s_);
+          tmem_ld8_nowait(t_q + (uint32_t)(c_lo + i), q);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int bin = (mloc + (c_lo + i + j) * rot) & 127;
+            atomicAdd(red + 2 * bin, (double)s_[j]);
+            atomicAdd(red + 2 * bin + 1, (double)q[j]);
+          }
+          tmem_st8(t_s + (uint32_t)(c_lo + i), z);
+          tmem_st8(t_q + (uint32_t)(c_lo + i), z);
+        }
+        tmem_st_wait();
+        pool_bar();
+        const int t = (int)threadIdx.x;
+        atomicAdd(p.pool + (int64_t)bb * 256 + t, red[t]);
+        red[t] = 0.0;
+        pool_bar();
+      };
+      int b_prev = -1;
+      for (int k = 0; k < n_my; ++k) {
+        int b, tin;
+        locate(k, b, tin);
+        if (b_prev >= 0 && b != b_prev) flush(b_prev);
+        b_prev = b;
+        const float vmask = tin * TC_M + mloc < p.rows_out ? 1.f : 0.f;
+        const uint32_t buf = (uint32_t)k & 1u;
+        mbar_wait_cluster(BAR(C_TFULL + buf), ((uint32_t)k >> 1) & 1u);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + buf * (uint32_t)T2_N + lane_off;
+        // four blocks of 8 channel pairs, software-pipelined over two register sets (tcgen05.wait::ld waits for ALL
+        // outstanding loads, so the next block's loads are issued right after the wait for the current one)
+        auto LD = [&](int c, float* va, float* vb, float* s_, float* q) {
+          tmem_ld8_nowait(taddr + (uint32_t)c, va);
+          tmem_ld8_nowait(taddr + (uint32_t)(c + 64), vb);
+          tmem_ld8_nowait(t_s + (uint32_t)c, s_);
+          tmem_ld8_nowait(t_q + (uint32_t)c, q);
+        };
+        auto tile = [&](auto masked_c) {
+          constexpr bool masked = decltype(masked_c)::value;    // last tile of an utterance: rows past its end are masked out
+          auto CP = [&](int c, float* va, float* vb, float* s_, float* q) {
+#pragma unroll
+            for (int j = 0; j < 8; j += 4) {
+              // (the same constants through the read-only global path, __ldg, were measured 4 us slower)
+              const float4 ba = *reinterpret_cast<const float4*>(ec + c + j), bb4 = *reinterpret_cast<const float4*>(ec + c + j + 64);
+              const float4 sa = *reinterpret_cast<const float4*>(ec + T2_N + c + j), sb = *reinterpret_cast<const float4*>(ec + T2_N + c + j + 64);
+              const float4 ha = *reinterpret_cast<const float4*>(ec + 2 * T2_N + c + j), hb = *reinterpret_cast<const float4*>(ec + 2 * T2_N + c + j + 64);
+              const float bav[4] = {ba.x, ba.y, ba.z, ba.w}, bbv[4] = {bb4.x, bb4.y, bb4.z, bb4.w};
+              const float sav[4] = {sa.x, sa.y, sa.z, sa.w}, sbv[4] = {sb.x, sb.y, sb.z, sb.w};
+              const float hav[4] = {ha.x, ha.y, ha.z, ha.w}, hbv[4] = {hb.x, hb.y, hb.z, hb.w};
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                float xa = fmaf(fmaxf(va[j + u] + bav[u], 0.f), sav[u], hav[u]);
+                float xb = fmaf(fmaxf(vb[j + u] + bbv[u], 0.f), sbv[u], hbv[u]);
+                if constexpr (masked) { xa *= vmask; xb *= vmask; }
+                s_[j + u] += xa + xb;
+                q[j + u] = fmaf(xa, xa, fmaf(xb, xb, q[j + u]));
+              }
+            }
+            tmem_st8(t_s + (uint32_t)c, s_);
+            tmem_st8(t_q + (uint32_t)c, q);
+          };
+          float a0[8], b0[8], s0[8], q0[8], a1[8], b1[8], s1[8], q1[8];
+          LD(c_lo, a0, b0, s0, q0);
+#pragma unroll
+          for (int i = 0; i < 4; i += 2) {
+            tmem_ld_wait();
+            LD(c_lo + 8 * (i + 1), a1, b1, s1, q1);
+            CP(c_lo + 8 * i, a0, b0, s0, q0);
+            tmem_ld_wait();
+            if (i + 2 < 4) LD(c_lo + 8 * (i + 2), a0, b0, s0, q0);
+            else {                                              // every accumulator column of this warp has been read
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(BAR(C_TEMPTY + buf), 0u);
+            }
+            CP(c_lo + 8 * (i + 1), a1, b1, s1, q1);
+          }
+        };
+        if ((tin + 1) * TC_M > p.rows_out) tile(std::true_type{});
+        else tile(std::false_type{});
+        tmem_st_wait();
+      }
+      if (b_prev >= 0) flush(b_prev);
+    } else {
     constexpr bool e_stats = (XF & X2_STATS) != 0;
     constexpr int NCH = T2_N / 8, CPW = T2_N / (E / 4);
     // InstanceNorm statistics of the output (X2_STATS), as in conv_tc.cu: column sums over the warp's 32 rows of the values
@@ -423,6 +551,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
       }
     }
     if constexpr (e_stats) { if (b_prev >= 0) e_flush(b_prev); }
+    }   // !X2_POOL
   }
 
   tc_fence_before();
@@ -430,7 +559,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
   cluster_sync_all();            // neither CTA may leave (or free tensor memory) while its peer can still touch it
   if (warp == MMA_WARP) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * T2_N) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(T2_TMEM_COLS) : "memory");
   }
 }
 
@@ -440,7 +569,7 @@ int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
   const int halo_lo = -lo, slab_used = TC_M + halo_lo + hi;
   if (slab_used > 160 || p.cin_v != 128) return SPANON_ERR_UNSUPPORTED;
-  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0);
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0);
   if (L.n_stages < T2_XF_WARPS || L.total > T2_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc2_kernel<XF>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
@@ -448,7 +577,7 @@ int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int total = tiles_per_utt * p.B;
   const int pairs = (total + 1) / 2;
   const int grid = 2 * std::max(1, std::min(pairs, n_sm / 2));
-  kern<<<grid, t2_threads(XF), L.total, st>>>(p, halo_lo, slab_used, tiles_per_utt, total);
+  SPANON_CUDA_TRY(launch_pdl(kern, dim3((unsigned)grid), dim3((unsigned)t2_threads(XF)), L.total, st, p.pdl != 0, p, halo_lo, slab_used, tiles_per_utt, total));
   return check_launch(p.tag ? p.tag : "tapgemm_tc2_kernel");
 }
 
@@ -458,13 +587,16 @@ int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
 // encoder.8 (stride 2: pair view), encoder.11, decoder.1 (transposed: [even | odd] phase columns)
 static int tc2_xf(const TapGemmParams& p) {
   const int act = p.silu == 1 ? X2_SILU : p.silu == 2 ? X2_RELU : X2_IDENT;
-  return act | (p.t2_scale ? X2_T2 : 0) | (p.stats ? X2_STATS : 0);
+  return act | (p.t2_scale ? X2_T2 : 0) | (p.stats ? X2_STATS : 0) | (p.pool ? X2_POOL : 0);
 }
 
 bool tapgemm_tc2_supported(const TapGemmParams& p) {
   if (!tapgemm_tc_supported(p)) return false;
   if (p.cin_v != 128 || p.cout_v != 128 || p.gen_feats) return false;
-  if (p.relu || p.e_scale || p.bias_v || p.flag_in || p.flag_out) return false;
+  if (p.bias_v || p.flag_in || p.flag_out) return false;
+  if (p.pool) {         // tdnn.6 with the pooling sums in its epilogue: ReLU -> BatchNorm affine, no stored output
+    if (!p.relu || !p.e_scale || !p.e_shift || p.stats || p.cout_mod != 128 || (p.rows_out & 1)) return false;
+  } else if (p.relu || p.e_scale) return false;
   if (p.stats && p.cout_mod != 128 && p.cout_mod != 64) return false;
   if (!p.stats && (p.cout_mod != 128 || p.out_fold != OUT_DIRECT)) return false;
   // measured per layer (same-box A/B): the pair kernel wins on the k5 layers (tdnn.0 -21, decoder.0 -20, encoder.11 -14 us)
@@ -478,7 +610,7 @@ bool tapgemm_tc2_supported(const TapGemmParams& p) {
   //  columns hold zero weights)
   const int xf = tc2_xf(p);
   return xf == X2_SILU || xf == (X2_SILU | X2_T2) || xf == (X2_RELU | X2_T2) || xf == (X2_SILU | X2_STATS) ||
-         xf == (X2_IDENT | X2_STATS);
+         xf == (X2_IDENT | X2_STATS) || xf == (X2_RELU | X2_T2 | X2_POOL);
 }
 
 int launch_tapgemm_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
@@ -489,6 +621,7 @@ int launch_tapgemm_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (xf == (X2_RELU | X2_T2)) return launch_tc2<X2_RELU | X2_T2>(p, n_sm, st);
   if (xf == (X2_SILU | X2_STATS)) return launch_tc2<X2_SILU | X2_STATS>(p, n_sm, st);
   if (xf == (X2_IDENT | X2_STATS)) return launch_tc2<X2_IDENT | X2_STATS>(p, n_sm, st);
+  if (xf == (X2_RELU | X2_T2 | X2_POOL)) return launch_tc2<X2_RELU | X2_T2 | X2_POOL>(p, n_sm, st);
   return SPANON_ERR_UNSUPPORTED;
 }
 

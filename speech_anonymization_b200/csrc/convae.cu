@@ -189,6 +189,8 @@ __device__ __forceinline__ void mma16816(float* d, uint32_t a0, uint32_t a1, uin
 __global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
                                          const float* __restrict__ beta, int B, int C, double count,
                                          float* __restrict__ scale, float* __restrict__ shift) {
+  pdl_launch_dependents();      // (launched as a programmatic dependent of the producer: common.cuh)
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B * C) {
     const int c = i % C;
@@ -833,6 +835,9 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   const bool split_stats = on_tc && io.out_stats >= 0 && !fuse;
   if (split_stats) p.stats = nullptr;
   if (on_tc) {
+    // programmatic dependent launch for every tcgen05 layer but the first of a forward (its predecessor may be a weight
+    // preparation kernel, whose output the prologue reads)
+    p.pdl = id != L_ENC2;
     // the 128 -> 128 layers without output statistics on CTA pairs (conv_tc2.cu); $SPANON_TC2=0: one-SM kernel
     static const bool tc2_env = !(getenv("SPANON_TC2") && getenv("SPANON_TC2")[0] == '0');
     if (tc2_env && tapgemm_tc2_supported(p)) SPANON_TRY(launch_tapgemm_tc2(p, c.n_sm, c.st));
@@ -856,9 +861,9 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
       return check_launch("instnorm_finalize_kernel");
     }
     if (fuse) {
-      instnorm_finalize_kernel<<<(unsigned)ceil_div((int64_t)nb * s.cout, 128), 128, 0, c.st>>>(
-          c.ws.stats[io.out_stats], io.fin_gamma, io.fin_beta, nb, s.cout, io.fin_count, c.ws.in_scale[io.out_stats],
-          c.ws.in_shift[io.out_stats]);
+      SPANON_CUDA_TRY(launch_pdl(instnorm_finalize_kernel, dim3((unsigned)ceil_div((int64_t)nb * s.cout, 128)), dim3(128), 0, c.st,
+                                 id != L_DEC45, (const double*)c.ws.stats[io.out_stats], io.fin_gamma, io.fin_beta, nb, s.cout,
+                                 io.fin_count, c.ws.in_scale[io.out_stats], c.ws.in_shift[io.out_stats]));
       return check_launch("instnorm_finalize_kernel");
     }
     return SPANON_OK;
@@ -1025,6 +1030,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     // X[0] = raw encoder.11 output; the bottleneck is SiLU(IN(X[0])), applied by both consumers on load
     if (run_clf) {
       const int64_t L3 = L4 - 14;
+      bool pooled = false;
       if (c.tc) {
         LayerIO t0{X[0], X[1], 3, 0, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
         LayerIO t3{X[1], X[2], -1, 1, nullptr, 0, -1, -1, OUT_CHANNELS_LAST};
@@ -1060,14 +1066,32 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         } else {
         SPANON_TRY(run_layer(c, L_TD0, t0, nb));
         SPANON_TRY(run_layer(c, L_TD3, t3, nb));
-        SPANON_TRY(run_layer(c, L_TD6, t6, nb));
+        // tdnn.6 on the CTA-pair kernel keeps ReLU -> BatchNorm 3 -> reshape -> pooling sums in its epilogue (running sums per
+        // row residue and channel in tensor memory, conv_tc2.cu X2_POOL): its output plane is never written and
+        // pool_planar_kernel's pass over it disappears.  $SPANON_POOL_FUSE=0: store the plane, pool in a second pass.
+        static const bool pool_fuse = !(getenv("SPANON_POOL_FUSE") && getenv("SPANON_POOL_FUSE")[0] == '0') &&
+                                      !(getenv("SPANON_TC2") && getenv("SPANON_TC2")[0] == '0');
+        if (pool_fuse) {
+          LayerIO t6p = t6;
+          t6p.bias = w->tdnn_b[2]; t6p.relu = 1; t6p.e_bn = 3;
+          TapGemmParams pp = make_params(c, L_TD6, t6p, nb);
+          pp.pool = c.ws.pool;
+          pp.pdl = 1;
+          if (tapgemm_tc2_supported(pp)) {
+            SPANON_TRY(launch_tapgemm_tc2(pp, c.n_sm, c.st));
+            pooled = true;
+          }
+        }
+        if (!pooled) SPANON_TRY(run_layer(c, L_TD6, t6, nb));
         }
         // (pooling in tdnn.6's epilogue instead -- a lane rotation per column hands each value to the lane owning its bin
         // -- was measured at +140 us on that launch against 85 us for this pass: ~20 dependent instructions per column on
         // two warps per TMEM lane quarter run at ~3 cycles each)
+        if (!pooled) {
         dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);   // ReLU(x + b2) -> BatchNorm 3 -> pooling
         pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, w->tdnn_b[2], c.ws.bn_scale[3],
                                                    c.ws.bn_shift[3], c.ws.pool);
+        }
       } else {
         SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
         SPANON_TRY(run_layer(c, L_TD3, {X[1], X[2], -1, -1, w->tdnn_b[1], 1, 2, -1, OUT_CHANNELS_LAST}, nb));

@@ -423,6 +423,201 @@ fbank400_warp_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_
   if (lane == 0 && lmax > -INFINITY) atomicMax(utt_max + b, float_to_key(lmax));
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// fbank400_rr_kernel: the 400-point transform as TWO register passes, 400 = 16 x 25 (n = 16 n1 + n2, k = k1 + 25 k2):
+//   pass A  thread (transform, n2): 25-point DFT over n1 in registers (5 x 5), twiddle W_400^{n2 k1}, one store of 25 values
+//   pass B  thread (transform, k1 <= 12): the 16-point DFTs (4 x 4, registers) of rows k1 AND 25 - k1 -- between them they
+//           hold every pair Z[k], Z[400 - k], so the two real spectra of the frame pair separate without another exchange
+// One trip through shared memory instead of the Stockham kernel's four, all butterfly indices compile-time constants
+// (the Stockham form spends more issue slots on index arithmetic than on butterflies: ncu, 47 % ALU vs 28 % FMA pipe).
+constexpr int FBANK_DEFAULT_FORM = 1;               // 0 rr, 1 stockham, 2 warp (see fbank_launch)
+constexpr int FR_NT = 256;                          // 16 transforms x 16 residues
+constexpr int FR_TR = FR_NT / 16;                   // transforms (frame pairs) per CTA pass
+constexpr int FR_FRAMES = 2 * FR_TR;                // 32
+constexpr int FR_SEG = (FR_FRAMES - 1) * HOP + N_FFT;   // 5360 samples
+constexpr int FR_ZR = 18;                           // float2 per k1 row (16 + 2: the 128-bit row reads of pass B are conflict-free)
+constexpr int FR_ZS = 25 * FR_ZR;                   // float2 per transform
+struct FrSmem {
+  float seg[FR_SEG];
+  float win[N_FFT];
+  float2 tw[25 * 16];                               // W_400^{n2 k1} at [k1][n2]
+  float2 Z[FR_TR * FR_ZS];                          // pass A -> pass B: [transform][k1][n2]
+  float P[FR_FRAMES * P_STRIDE];
+};
+
+// 16-point forward DFT, natural order in and out (radix 4 x 4: n = 4a + b, k = c + 4d)
+__device__ __forceinline__ void dft16(float2* v) {
+  constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R2 = 0.70710678118654752f;
+  float2 t[4][4];
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    float2 u[4] = {v[b], v[4 + b], v[8 + b], v[12 + b]};
+    dft4(u);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) t[b][c] = u[c];
+  }
+  // W_16^{b c}
+  cmul_c(t[1][1], C1, -S1); cmul_c(t[1][2], R2, -R2); cmul_c(t[1][3], S1, -C1);
+  cmul_c(t[2][1], R2, -R2); t[2][2] = make_float2(t[2][2].y, -t[2][2].x); cmul_c(t[2][3], -R2, -R2);
+  cmul_c(t[3][1], S1, -C1); cmul_c(t[3][2], -R2, -R2); cmul_c(t[3][3], -C1, S1);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float2 u[4] = {t[0][c], t[1][c], t[2][c], t[3][c]};
+    dft4(u);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) v[c + 4 * d] = u[d];
+  }
+}
+
+template <typename TS>
+__global__ void __launch_bounds__(FR_NT, 2)
+fbank400_rr_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T, float* __restrict__ out,
+                   int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FrSmem& S = *reinterpret_cast<FrSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int b = blockIdx.y;
+  const TS* x = pcm + (int64_t)b * pcm_stride;
+  for (int i = tid; i < N_FFT; i += FR_NT) {
+    S.win[i] = cfg.window[i];
+    const int k1 = i >> 4, n2 = i & 15;
+    float sn, cs;
+    sincospif(-(float)(n2 * k1) / 200.f, &sn, &cs);          // n2 * k1 <= 360 < 400: already reduced
+    S.tw[i] = make_float2(cs, sn);
+  }
+  constexpr float C25[25][2] = {
+      {1.f, 0.f}, {0.96858316112863108f, -0.24868988716485479f}, {0.87630668004386358f, -0.48175367410171532f},
+      {0.72896862742141155f, -0.68454710592868862f}, {0.53582679497899666f, -0.84432792550201508f},
+      {0.30901699437494742f, -0.95105651629515357f}, {0.062790519529313374f, -0.99802672842827156f},
+      {-0.18738131458572463f, -0.98228725072868872f}, {-0.42577929156507272f, -0.90482705246601958f},
+      {-0.63742398974868975f, -0.77051324277578925f}, {-0.80901699437494742f, -0.58778525229247313f},
+      {-0.92977648588825146f, -0.36812455268467797f}, {-0.99211470131447788f, -0.12533323356430426f},
+      {-0.99211470131447788f, 0.12533323356430426f}, {-0.92977648588825146f, 0.36812455268467797f},
+      {-0.80901699437494742f, 0.58778525229247313f}, {-0.63742398974868975f, 0.77051324277578925f},
+      {-0.42577929156507272f, 0.90482705246601958f}, {-0.18738131458572463f, 0.98228725072868872f},
+      {0.062790519529313374f, 0.99802672842827156f}, {0.30901699437494742f, 0.95105651629515357f},
+      {0.53582679497899666f, 0.84432792550201508f}, {0.72896862742141155f, 0.68454710592868862f},
+      {0.87630668004386358f, 0.48175367410171532f}, {0.96858316112863108f, 0.24868988716485479f}};   // W_25^j
+  const int n_mels = cfg.n_mels;
+  const float db_floor = (float)((double)cfg.multiplier * log10((double)cfg.amin)) - cfg.db_offset;
+  float lmax = -INFINITY;
+  for (int t0 = blockIdx.x * FR_FRAMES; t0 < T; t0 += gridDim.x * FR_FRAMES) {
+    __syncthreads();                                         // (previous pass's mel reads of P are done; tables are written)
+    // PCM segment of the pass's 32 frames: padded sample p = t*HOP + n - N_FFT/2 (center=True, zero padding)
+    const int64_t base = (int64_t)t0 * HOP - N_FFT / 2;
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & (4 * sizeof(TS) - 1)) == 0) && ((base & 3) == 0);
+    for (int i4 = tid; i4 < FR_SEG / 4; i4 += FR_NT) {
+      const int64_t sidx = base + 4 * (int64_t)i4;
+      float4 v;
+      if (vec_ok && sidx >= 0 && sidx + 3 < n_samples) {
+        v = load4(x, sidx);
+      } else {
+        v.x = (sidx + 0 >= 0 && sidx + 0 < n_samples) ? load1(x, sidx + 0) : 0.f;
+        v.y = (sidx + 1 >= 0 && sidx + 1 < n_samples) ? load1(x, sidx + 1) : 0.f;
+        v.z = (sidx + 2 >= 0 && sidx + 2 < n_samples) ? load1(x, sidx + 2) : 0.f;
+        v.w = (sidx + 3 >= 0 && sidx + 3 < n_samples) ? load1(x, sidx + 3) : 0.f;
+      }
+      *reinterpret_cast<float4*>(&S.seg[4 * i4]) = v;
+    }
+    __syncthreads();
+    {   // ---- pass A: transform tr = frames t0 + 2 tr (real part) and + 1 (imaginary part), residue n2
+      const int tr = tid >> 4, n2 = tid & 15;
+      float2 a[25];
+      const float* fa = S.seg + (2 * tr) * HOP + n2;
+#pragma unroll
+      for (int n1 = 0; n1 < 25; ++n1) {
+        const float wn = S.win[16 * n1 + n2];
+        a[n1] = make_float2(wn * fa[16 * n1], wn * fa[16 * n1 + HOP]);
+      }
+      // 25-point DFT over n1 = 5p + q -> y[r + 5s]
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        float2 v[5] = {a[q], a[5 + q], a[10 + q], a[15 + q], a[20 + q]};
+        dft5(v);
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+          if (r > 0 && q > 0) cmul_c(v[r], C25[(q * r) % 25][0], C25[(q * r) % 25][1]);
+          a[5 * r + q] = v[r];
+        }
+      }
+      float2* zrow = S.Z + tr * FR_ZS + n2;
+#pragma unroll
+      for (int r = 0; r < 5; ++r) {
+        float2 v[5] = {a[5 * r], a[5 * r + 1], a[5 * r + 2], a[5 * r + 3], a[5 * r + 4]};
+        dft5(v);
+#pragma unroll
+        for (int s5 = 0; s5 < 5; ++s5) {
+          const int k1 = r + 5 * s5;
+          if (k1 > 0) { const float2 w = S.tw[k1 * 16 + n2]; cmul_c(v[s5], w.x, w.y); }
+          zrow[k1 * FR_ZR] = v[s5];
+        }
+      }
+    }
+    __syncthreads();
+    if (tid < FR_TR * 13) {   // ---- pass B: item (transform, k1 in 0..12) -> bins k1 + 25 k2 and (25 - k1) + 25 k2, k <= 200
+      const int tr = tid / 13, k1 = tid - tr * 13;
+      float* Pa = S.P + (2 * tr) * P_STRIDE;
+      float* Pb = Pa + P_STRIDE;
+      float2 A[16];
+      {
+        const float4* src = reinterpret_cast<const float4*>(S.Z + tr * FR_ZS + k1 * FR_ZR);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const float4 u = src[i]; A[2 * i] = make_float2(u.x, u.y); A[2 * i + 1] = make_float2(u.z, u.w); }
+      }
+      dft16(A);
+      if (k1 == 0) {          // bins 25 k2: Z[400 - 25 k2] = A[(16 - k2) & 15]
+#pragma unroll
+        for (int k2 = 0; k2 <= 8; ++k2) {
+          const float2 y = A[k2], z = A[(16 - k2) & 15];
+          const float ar = y.x + z.x, ai = y.y - z.y, br = y.y + z.y, bi = y.x - z.x;
+          Pa[25 * k2] = 0.25f * (ar * ar + ai * ai);
+          Pb[25 * k2] = 0.25f * (br * br + bi * bi);
+        }
+      } else {
+        float2 Bq[16];
+        const float4* src = reinterpret_cast<const float4*>(S.Z + tr * FR_ZS + (25 - k1) * FR_ZR);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const float4 u = src[i]; Bq[2 * i] = make_float2(u.x, u.y); Bq[2 * i + 1] = make_float2(u.z, u.w); }
+        dft16(Bq);
+#pragma unroll
+        for (int k2 = 0; k2 < 8; ++k2) {
+          {   // kA = k1 + 25 k2, 400 - kA = (25 - k1) + 25 (15 - k2)
+            const float2 y = A[k2], z = Bq[15 - k2];
+            const float ar = y.x + z.x, ai = y.y - z.y, br = y.y + z.y, bi = y.x - z.x;
+            Pa[k1 + 25 * k2] = 0.25f * (ar * ar + ai * ai);
+            Pb[k1 + 25 * k2] = 0.25f * (br * br + bi * bi);
+          }
+          {   // kB = (25 - k1) + 25 k2, 400 - kB = k1 + 25 (15 - k2)
+            const float2 y = Bq[k2], z = A[15 - k2];
+            const float ar = y.x + z.x, ai = y.y - z.y, br = y.y + z.y, bi = y.x - z.x;
+            Pa[(25 - k1) + 25 * k2] = 0.25f * (ar * ar + ai * ai);
+            Pb[(25 - k1) + 25 * k2] = 0.25f * (br * br + bi * bi);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- mel projection + dB (fp32 like the reference, processing/features.py:701-710)
+    for (int w = tid; w < FR_FRAMES * n_mels; w += FR_NT) {
+      const int fr = w / n_mels;
+      const int m = w - fr * n_mels;
+      const int t = t0 + fr;
+      if (t >= T) continue;
+      const int st = __ldg(cfg.mel_start + m);
+      const int ln = __ldg(cfg.mel_len + m);
+      const float* wv = cfg.mel_w + __ldg(cfg.mel_off + m);
+      const float* pp = S.P + fr * P_STRIDE + st;
+      float acc = 0.f;
+      for (int i = 0; i < ln; ++i) acc = fmaf(pp[i], __ldg(wv + i), acc);
+      const float db = acc <= cfg.amin ? db_floor : cfg.multiplier * log10f(acc) - cfg.db_offset;
+      out[((int64_t)b * T + t) * n_mels + m] = db;
+      lmax = fmaxf(lmax, db);
+    }
+  }
+  lmax = warp_max(lmax);
+  if (lane == 0 && lmax > -INFINITY) atomicMax(utt_max + b, float_to_key(lmax));
+}
+
 // Generic (any n_fft <= 4096, win_length <= n_fft) direct-DFT path: one CTA per frame.
 // O(n_fft^2) per frame -- correctness path for non-reference configurations only.
 template <typename TS>
@@ -541,10 +736,19 @@ int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride
                                            (int)sizeof(FbankSmem)));
       SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_warp_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(FwSmem)));
+      SPANON_CUDA_TRY(cudaFuncSetAttribute(fbank400_rr_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(FrSmem)));
     }
-    // register / warp-shuffle FFT (default); $SPANON_FBANK_SMEM=1: the shared-memory Stockham form (A/B switch)
-    static const bool smem_form = getenv("SPANON_FBANK_SMEM") && getenv("SPANON_FBANK_SMEM")[0] == '1';
-    if (!smem_form) {
+    // $SPANON_FBANK = rr (two register passes, default) | stockham (shared-memory Stockham, round 1) | warp (register /
+    // warp-shuffle FFT, measured slower: DESIGN.md 3.5)
+    static const char* form_env = getenv("SPANON_FBANK");
+    static const int form = !form_env ? FBANK_DEFAULT_FORM : form_env[0] == 's' ? 1 : form_env[0] == 'w' ? 2 : 0;
+    if (form == 0) {
+      dim3 grid((unsigned)ceil_div(T, FR_FRAMES), (unsigned)B);
+      fbank400_rr_kernel<TS><<<grid, FR_NT, sizeof(FrSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+      return check_launch("fbank400_kernel");
+    }
+    if (form == 2) {
       dim3 grid((unsigned)ceil_div(T, FW_FRAMES), (unsigned)B);
       fbank400_warp_kernel<TS><<<grid, FW_NT, sizeof(FwSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
       return check_launch("fbank400_kernel");

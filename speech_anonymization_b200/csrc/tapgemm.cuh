@@ -82,6 +82,10 @@ struct TapGemmParams {
   unsigned* flag_out; const unsigned* flag_in; int flag_in_tpu; unsigned flag_target;
   int out_half;        // tcgen05 kernel, OUT_CH0_F32: store fp16 instead of fp32 (recon_fp16)
   int mma_group;       // tcgen05 kernel: stages per MMA issue round the caller asks for (0/1 = one; 4 where it pays)
+  // pair kernel (conv_tc2.cu), tdnn.6: instead of storing the output, ReLU(acc + bias) * e_scale + e_shift is summed (value and
+  // square) into the StatisticsPooling bins of the [B][cout][rows_out] -> [B][rows_out][cout] REINTERPRETATION: pool [B][128][2]
+  double* pool;
+  int pdl;             // tcgen05 kernels: launch as a programmatic dependent of the previous kernel (common.cuh launch_pdl)
   unsigned* err_flag;  // set to 1 if a dataflow wait timed out (results are then invalid; the consumer kernels report it)
   long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]
   const char* tag;     // profile name of this launch ("tapgemm:<layer>")
