@@ -430,19 +430,26 @@ fbank400_warp_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_
 //           hold every pair Z[k], Z[400 - k], so the two real spectra of the frame pair separate without another exchange
 // One trip through shared memory instead of the Stockham kernel's four, all butterfly indices compile-time constants
 // (the Stockham form spends more issue slots on index arithmetic than on butterflies: ncu, 47 % ALU vs 28 % FMA pipe).
-constexpr int FBANK_DEFAULT_FORM = 1;               // 0 rr, 1 stockham, 2 warp (see fbank_launch)
+constexpr int FBANK_DEFAULT_FORM = 0;               // 0 rr, 1 stockham, 2 warp (see fbank_launch)
 constexpr int FR_NT = 256;                          // 16 transforms x 16 residues
 constexpr int FR_TR = FR_NT / 16;                   // transforms (frame pairs) per CTA pass
 constexpr int FR_FRAMES = 2 * FR_TR;                // 32
 constexpr int FR_SEG = (FR_FRAMES - 1) * HOP + N_FFT;   // 5360 samples
 constexpr int FR_ZR = 18;                           // float2 per k1 row (16 + 2: the 128-bit row reads of pass B are conflict-free)
 constexpr int FR_ZS = 25 * FR_ZR;                   // float2 per transform
+constexpr int FR_PS = 205;                          // power-spectrum row (odd: lanes = frames read it conflict-free)
+constexpr int FR_MAXMEL = 128, FR_MAXTAPS = 512;    // filterbanks staged in shared memory (larger ones: Stockham kernel)
 struct FrSmem {
   float seg[FR_SEG];
   float win[N_FFT];
   float2 tw[25 * 16];                               // W_400^{n2 k1} at [k1][n2]
-  float2 Z[FR_TR * FR_ZS];                          // pass A -> pass B: [transform][k1][n2]
-  float P[FR_FRAMES * P_STRIDE];
+  union {
+    float2 Z[FR_TR * FR_ZS];                        // pass A -> pass B: [transform][k1][n2]
+    float O[FR_FRAMES * (FR_MAXMEL + 1)];           // mel stage -> coalesced store: [frame][mel] (row n_mels + 1)
+  };
+  float P[FR_FRAMES * FR_PS];
+  float melw[FR_MAXTAPS];
+  int mst[FR_MAXMEL], mln[FR_MAXMEL], moff[FR_MAXMEL];
 };
 
 // 16-point forward DFT, natural order in and out (radix 4 x 4: n = 4a + b, k = c + 4d)
@@ -472,19 +479,35 @@ __device__ __forceinline__ void dft16(float2* v) {
 template <typename TS>
 __global__ void __launch_bounds__(FR_NT, 2)
 fbank400_rr_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_stride, int T, float* __restrict__ out,
-                   int32_t* __restrict__ utt_max, SpanonFbankCfg cfg) {
+                   int32_t* __restrict__ utt_max, SpanonFbankCfg cfg, int passes_per_utt, int total_passes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FrSmem& S = *reinterpret_cast<FrSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
-  const int b = blockIdx.y;
-  const TS* x = pcm + (int64_t)b * pcm_stride;
-  for (int i = tid; i < N_FFT; i += FR_NT) {
-    S.win[i] = cfg.window[i];
-    const int k1 = i >> 4, n2 = i & 15;
-    float sn, cs;
-    sincospif(-(float)(n2 * k1) / 200.f, &sn, &cs);          // n2 * k1 <= 360 < 400: already reduced
-    S.tw[i] = make_float2(cs, sn);
-  }
+  __shared__ int s_ntaps;
+  if (tid == 0) s_ntaps = 0;
+  const float* melw = S.melw;    // (a filterbank with more than FR_MAXTAPS weights is read from global memory instead)
+  auto stage_tables = [&] {      // window, inter-pass twiddles, the sparse mel filterbank
+    for (int i = tid; i < N_FFT; i += FR_NT) {
+      S.win[i] = cfg.window[i];
+      const int k1 = i >> 4, n2 = i & 15;
+      float sn, cs;
+      sincospif(-(float)(n2 * k1) / 200.f, &sn, &cs);          // n2 * k1 <= 360 < 400: already reduced
+      S.tw[i] = make_float2(cs, sn);
+    }
+    __syncthreads();
+    for (int m = tid; m < cfg.n_mels; m += FR_NT) {
+      const int st = cfg.mel_start[m], ln = cfg.mel_len[m], off = cfg.mel_off[m];
+      S.mst[m] = st; S.mln[m] = ln; S.moff[m] = off;
+      atomicMax(&s_ntaps, off + ln);
+    }
+    __syncthreads();
+    const int n_taps = s_ntaps;
+    if (n_taps <= FR_MAXTAPS) {
+      for (int i = tid; i < n_taps; i += FR_NT) S.melw[i] = cfg.mel_w[i];
+    } else {
+      melw = cfg.mel_w;
+    }
+  };
   constexpr float C25[25][2] = {
       {1.f, 0.f}, {0.96858316112863108f, -0.24868988716485479f}, {0.87630668004386358f, -0.48175367410171532f},
       {0.72896862742141155f, -0.68454710592868862f}, {0.53582679497899666f, -0.84432792550201508f},
@@ -500,24 +523,43 @@ fbank400_rr_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_st
       {0.87630668004386358f, 0.48175367410171532f}, {0.96858316112863108f, 0.24868988716485479f}};   // W_25^j
   const int n_mels = cfg.n_mels;
   const float db_floor = (float)((double)cfg.multiplier * log10((double)cfg.amin)) - cfg.db_offset;
-  float lmax = -INFINITY;
-  for (int t0 = blockIdx.x * FR_FRAMES; t0 < T; t0 += gridDim.x * FR_FRAMES) {
-    __syncthreads();                                         // (previous pass's mel reads of P are done; tables are written)
-    // PCM segment of the pass's 32 frames: padded sample p = t*HOP + n - N_FFT/2 (center=True, zero padding)
+  const float l2_mult = cfg.multiplier * 0.30102999566398120f;      // multiplier * log10(x) = l2_mult * log2(x)
+  bool first = true;
+  // persistent CTAs (two per SM) over the flattened (utterance, 32-frame pass) list: the tables are staged once per CTA
+  for (int item = blockIdx.x; item < total_passes; item += gridDim.x) {
+    const int b = item / passes_per_utt;
+    const int t0 = (item - b * passes_per_utt) * FR_FRAMES;
+    const TS* x = pcm + (int64_t)b * pcm_stride;
+    float lmax = -INFINITY;
+    // PCM segment of the pass's 32 frames: padded sample p = t*HOP + n - N_FFT/2 (center=True, zero padding).  The
+    // global loads are issued first and land while the tables are staged (first pass) / behind the barrier.
     const int64_t base = (int64_t)t0 * HOP - N_FFT / 2;
     const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & (4 * sizeof(TS) - 1)) == 0) && ((base & 3) == 0);
-    for (int i4 = tid; i4 < FR_SEG / 4; i4 += FR_NT) {
+    constexpr int NLD = (FR_SEG / 4 + FR_NT - 1) / FR_NT;      // 6
+    float4 pre[NLD];
+#pragma unroll
+    for (int r = 0; r < NLD; ++r) {
+      const int i4 = tid + r * FR_NT;
       const int64_t sidx = base + 4 * (int64_t)i4;
-      float4 v;
-      if (vec_ok && sidx >= 0 && sidx + 3 < n_samples) {
-        v = load4(x, sidx);
-      } else {
-        v.x = (sidx + 0 >= 0 && sidx + 0 < n_samples) ? load1(x, sidx + 0) : 0.f;
-        v.y = (sidx + 1 >= 0 && sidx + 1 < n_samples) ? load1(x, sidx + 1) : 0.f;
-        v.z = (sidx + 2 >= 0 && sidx + 2 < n_samples) ? load1(x, sidx + 2) : 0.f;
-        v.w = (sidx + 3 >= 0 && sidx + 3 < n_samples) ? load1(x, sidx + 3) : 0.f;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i4 < FR_SEG / 4) {
+        if (vec_ok && sidx >= 0 && sidx + 3 < n_samples) {
+          v = load4(x, sidx);
+        } else {
+          v.x = (sidx + 0 >= 0 && sidx + 0 < n_samples) ? load1(x, sidx + 0) : 0.f;
+          v.y = (sidx + 1 >= 0 && sidx + 1 < n_samples) ? load1(x, sidx + 1) : 0.f;
+          v.z = (sidx + 2 >= 0 && sidx + 2 < n_samples) ? load1(x, sidx + 2) : 0.f;
+          v.w = (sidx + 3 >= 0 && sidx + 3 < n_samples) ? load1(x, sidx + 3) : 0.f;
+        }
       }
-      *reinterpret_cast<float4*>(&S.seg[4 * i4]) = v;
+      pre[r] = v;
+    }
+    if (first) { stage_tables(); first = false; }
+    __syncthreads();                                         // (previous pass's reads of O / seg are done)
+#pragma unroll
+    for (int r = 0; r < NLD; ++r) {
+      const int i4 = tid + r * FR_NT;
+      if (i4 < FR_SEG / 4) *reinterpret_cast<float4*>(&S.seg[4 * i4]) = pre[r];
     }
     __syncthreads();
     {   // ---- pass A: transform tr = frames t0 + 2 tr (real part) and + 1 (imaginary part), residue n2
@@ -556,8 +598,8 @@ fbank400_rr_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_st
     __syncthreads();
     if (tid < FR_TR * 13) {   // ---- pass B: item (transform, k1 in 0..12) -> bins k1 + 25 k2 and (25 - k1) + 25 k2, k <= 200
       const int tr = tid / 13, k1 = tid - tr * 13;
-      float* Pa = S.P + (2 * tr) * P_STRIDE;
-      float* Pb = Pa + P_STRIDE;
+      float* Pa = S.P + (2 * tr) * FR_PS;
+      float* Pb = Pa + FR_PS;
       float2 A[16];
       {
         const float4* src = reinterpret_cast<const float4*>(S.Z + tr * FR_ZS + k1 * FR_ZR);
@@ -597,25 +639,42 @@ fbank400_rr_kernel(const TS* __restrict__ pcm, int64_t n_samples, int64_t pcm_st
       }
     }
     __syncthreads();
-    // ---- mel projection + dB (fp32 like the reference, processing/features.py:701-710)
-    for (int w = tid; w < FR_FRAMES * n_mels; w += FR_NT) {
-      const int fr = w / n_mels;
-      const int m = w - fr * n_mels;
-      const int t = t0 + fr;
-      if (t >= T) continue;
-      const int st = __ldg(cfg.mel_start + m);
-      const int ln = __ldg(cfg.mel_len + m);
-      const float* wv = cfg.mel_w + __ldg(cfg.mel_off + m);
-      const float* pp = S.P + fr * P_STRIDE + st;
-      float acc = 0.f;
-      for (int i = 0; i < ln; ++i) acc = fmaf(pp[i], __ldg(wv + i), acc);
-      const float db = acc <= cfg.amin ? db_floor : cfg.multiplier * log10f(acc) - cfg.db_offset;
-      out[((int64_t)b * T + t) * n_mels + m] = db;
-      lmax = fmaxf(lmax, db);
+    // ---- mel projection + dB (fp32 like the reference, processing/features.py:701-710).  Lanes = the 32 frames, a warp
+    // walks mel filters m = warp, warp + 8, ...: the filter (start, length, weights) is uniform over the warp -- no
+    // divergence on the filter length, weights broadcast from shared memory -- and the results go through shared memory so
+    // that the pass's 32 x n_mels outputs (contiguous in the output) leave as coalesced stores.
+    {
+      const int fr = lane, wq = tid >> 5;
+      const float* prow = S.P + fr * FR_PS;
+      for (int m = wq; m < n_mels; m += FR_NT / 32) {
+        const int st = S.mst[m], ln = S.mln[m];
+        const float* wv = melw + S.moff[m];
+        const float* pp = prow + st;
+        float acc = 0.f;
+#pragma unroll 1
+        for (int i = 0; i + 1 < ln; i += 2) acc = fmaf(pp[i + 1], wv[i + 1], fmaf(pp[i], wv[i], acc));
+        if (ln & 1) acc = fmaf(pp[ln - 1], wv[ln - 1], acc);
+        float l2;
+        asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(fmaxf(acc, cfg.amin)));     // (acc >= amin: never denormal)
+        S.O[fr * (n_mels + 1) + m] = acc <= cfg.amin ? db_floor : l2_mult * l2 - cfg.db_offset;
+      }
     }
+    __syncthreads();
+    {   // rows of the staged block -> the pass's contiguous [frames][n_mels] output range, coalesced
+      const int nvalid = min(FR_FRAMES, T - t0);
+      float* dst = out + ((int64_t)b * T + t0) * n_mels;
+      for (int fr = tid >> 5; fr < nvalid; fr += FR_NT / 32) {
+        const float* srow = S.O + fr * (n_mels + 1);
+        for (int m = lane; m < n_mels; m += 32) {
+          const float db = srow[m];
+          dst[fr * n_mels + m] = db;
+          lmax = fmaxf(lmax, db);
+        }
+      }
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0 && lmax > -INFINITY) atomicMax(utt_max + b, float_to_key(lmax));
   }
-  lmax = warp_max(lmax);
-  if (lane == 0 && lmax > -INFINITY) atomicMax(utt_max + b, float_to_key(lmax));
 }
 
 // Generic (any n_fft <= 4096, win_length <= n_fft) direct-DFT path: one CTA per frame.
@@ -743,9 +802,14 @@ int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride
     // warp-shuffle FFT, measured slower: DESIGN.md 3.5)
     static const char* form_env = getenv("SPANON_FBANK");
     static const int form = !form_env ? FBANK_DEFAULT_FORM : form_env[0] == 's' ? 1 : form_env[0] == 'w' ? 2 : 0;
-    if (form == 0) {
-      dim3 grid((unsigned)ceil_div(T, FR_FRAMES), (unsigned)B);
-      fbank400_rr_kernel<TS><<<grid, FR_NT, sizeof(FrSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg);
+    if (form == 0 && cfg->n_mels <= FR_MAXMEL) {
+      const int ppu = (int)ceil_div(T, FR_FRAMES);
+      const int64_t total = (int64_t)ppu * B;
+      const int n_sm = current_device_sms();
+      if (n_sm <= 0 || total > INT32_MAX) return SPANON_ERR_CUDA;
+      const unsigned grid = (unsigned)std::min<int64_t>(total, 2 * (int64_t)n_sm);
+      fbank400_rr_kernel<TS><<<grid, FR_NT, sizeof(FrSmem), st>>>(pcm, n_samples, pcm_stride, (int)T, out, utt_max, *cfg, ppu,
+                                                                  (int)total);
       return check_launch("fbank400_kernel");
     }
     if (form == 2) {
