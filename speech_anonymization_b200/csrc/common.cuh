@@ -126,6 +126,15 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 // (both are no-ops in a kernel launched without the attribute)
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Loads through `const T* __restrict__` (ld.global.nc) are "invariant" to the compiler, and it hoists them ABOVE the wait --
+// asm memory clobber or not (seen in clf_head_kernel's SASS: the pooled sums were read before ACQBULK, i.e. before the
+// producer had written them).  A pointer to data the predecessor produces must therefore be re-derived AFTER pdl_wait():
+//   pdl_wait(); p = pdl_acquire(p);
+template <typename T>
+__device__ __forceinline__ T* pdl_acquire(T* p) {
+  asm volatile("" : "+l"(p)::"memory");
+  return p;
+}
 #endif
 
 // Per-device one-time setup (cudaFuncSetAttribute is a per-device setting, and one process may drive several GPUs):

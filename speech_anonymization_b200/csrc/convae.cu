@@ -186,11 +186,12 @@ __device__ __forceinline__ void mma16816(float* d, uint32_t a0, uint32_t a1, uin
 }
 
 // nn.InstanceNorm1d(affine=True): biased variance over the sequence, eps 1e-5
-__global__ void instnorm_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
+__global__ void instnorm_finalize_kernel(const double* stats, const float* __restrict__ gamma,
                                          const float* __restrict__ beta, int B, int C, double count,
                                          float* __restrict__ scale, float* __restrict__ shift) {
   pdl_launch_dependents();      // (launched as a programmatic dependent of the producer: common.cuh)
   pdl_wait();
+  stats = pdl_acquire(stats);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B * C) {
     const int c = i % C;
@@ -507,10 +508,20 @@ __device__ __forceinline__ float bn_eval(float x, const SpanonBatchNorm& bn, int
 
 // classify: Linear(256,128) ReLU BN | Linear(128,64) ReLU BN | Linear(64,2) | log_softmax.  grid = B, block = 128
 __global__ void __launch_bounds__(128)
-clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise, int64_t n /*L3*/,
-                SpanonConvAEWeights w, float* __restrict__ logp, const unsigned* __restrict__ err_flag) {
+clf_head_kernel(const double* pool, const float* __restrict__ noise, int64_t n /*L3*/,
+                SpanonConvAEWeights w, float* __restrict__ logp, const unsigned* err_flag) {
   __shared__ float s0[256], s1[128], s2[64], s3[2];
   const int b = blockIdx.x, tid = threadIdx.x;
+  pdl_launch_dependents();      // (common.cuh: launched as a programmatic dependent of tdnn.6 / the pooling pass)
+  // (bias / BatchNorm parameters of row tid are fetched up front, before the wait for the producer)
+  const float b0 = w.cls_b[0][tid], g0 = w.cls_bn[0].weight[tid], be0 = w.cls_bn[0].bias[tid], m0 = w.cls_bn[0].running_mean[tid],
+              v0 = w.cls_bn[0].running_var[tid];
+  const int t64 = tid & 63;
+  const float b1 = w.cls_b[1][t64], g1 = w.cls_bn[1].weight[t64], be1 = w.cls_bn[1].bias[t64], m1 = w.cls_bn[1].running_mean[t64],
+              v1 = w.cls_bn[1].running_var[t64];
+  pdl_wait();
+  pool = pdl_acquire(pool);     // (produced by the predecessor: see common.cuh)
+  err_flag = pdl_acquire(err_flag);
   {
     const double s = pool[((int64_t)b * 128 + tid) * 2 + 0], q = pool[((int64_t)b * 128 + tid) * 2 + 1];
     const double mean = s / (double)n;
@@ -520,19 +531,32 @@ clf_head_kernel(const double* __restrict__ pool, const float* __restrict__ noise
     s0[128 + tid] = (float)sqrt(var) + 1e-5f;
   }
   __syncthreads();
-  {
-    float a = w.cls_b[0][tid];
-    const float* wr = w.cls_w[0] + tid * 256;
-    for (int i = 0; i < 256; ++i) a = fmaf(s0[i], __ldg(wr + i), a);
-    s1[tid] = bn_eval(fmaxf(a, 0.f), w.cls_bn[0], tid);
+  // a warp per output row: the lanes read 128 contiguous bytes of the weight row per step (a thread per row read its own
+  // 1 KB row sequentially -- 128 uncoalesced streams and one 256-long dependent chain: 36 us for this 60-CTA launch)
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll 4
+  for (int j = warp; j < 128; j += 4) {
+    const float* wr = w.cls_w[0] + j * 256 + lane;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a = fmaf(s0[lane + 32 * k], __ldg(wr + 32 * k), a);
+    a = warp_sum(a);
+    if (lane == 0) s1[j] = a;
   }
   __syncthreads();
-  if (tid < 64) {
-    float a = w.cls_b[1][tid];
-    const float* wr = w.cls_w[1] + tid * 128;
-    for (int i = 0; i < 128; ++i) a = fmaf(s1[i], __ldg(wr + i), a);
-    s2[tid] = bn_eval(fmaxf(a, 0.f), w.cls_bn[1], tid);
+  s1[tid] = (fmaxf(s1[tid] + b0, 0.f) - m0) / sqrtf(v0 + 1e-5f) * g0 + be0;
+  __syncthreads();
+#pragma unroll 4
+  for (int j = warp; j < 64; j += 4) {
+    const float* wr = w.cls_w[1] + j * 128 + lane;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a = fmaf(s1[lane + 32 * k], __ldg(wr + 32 * k), a);
+    a = warp_sum(a);
+    if (lane == 0) s2[j] = a;
   }
+  __syncthreads();
+  if (tid < 64) s2[tid] = (fmaxf(s2[tid] + b1, 0.f) - m1) / sqrtf(v1 + 1e-5f) * g1 + be1;
   __syncthreads();
   if (tid < 2) {
     float a = w.cls_b[2][tid];
@@ -1101,8 +1125,9 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
       }
       SPANON_TRY(check_launch("pool_kernel"));
-      clf_head_kernel<<<(unsigned)nb, 128, 0, c.st>>>(c.ws.pool, pool_noise ? pool_noise + b0 * 128 : nullptr, L3, *w,
-                                                      logp + b0 * 2, c.ws.counter + 1);
+      SPANON_CUDA_TRY(launch_pdl(clf_head_kernel, dim3((unsigned)nb), dim3(128), 0, c.st, true, (const double*)c.ws.pool,
+                                 pool_noise ? pool_noise + b0 * 128 : (const float*)nullptr, L3, *w, logp + b0 * 2,
+                                 (const unsigned*)(c.ws.counter + 1)));
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));

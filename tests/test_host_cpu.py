@@ -265,3 +265,38 @@ def test_data_parallel_trainer_gloo_world2():
         assert err < 1e-6, err
         assert fired == [0, 1, 2] and frozen_none and dec_has and flat_max == 0.0
         assert Xcol == [0.0, 0.0, 1.0, 1.0] and y == [0, 0, 1, 1]
+
+
+def test_pdl_kernels_keep_invariant_loads_behind_the_wait():
+    """Programmatic dependent launch (csrc/common.cuh): a kernel launched that way may start before its predecessor has
+    finished and blocks in griddepcontrol.wait (ACQBULK in the SASS).  nvcc hoists `const __restrict__` / __ldg loads
+    (LDG...CONSTANT, "invariant" to it) above that wait, memory clobber or not -- which once made clf_head_kernel read the
+    pooled sums before tdnn.6 had written them.  Guard: in every kernel of the library that waits, no invariant load sits
+    ahead of the wait (constants fetched early on purpose use plain LDG)."""
+    import shutil
+    import subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    so = os.path.join(os.path.dirname(sab.__file__), "libspanon.so")
+    sass = subprocess.run([cuobjdump, "-sass", so], capture_output=True, text=True, check=True).stdout
+    name, early, seen, waits, bad = None, [], False, 0, []
+    def close():
+        nonlocal waits
+        if name and seen:
+            waits += 1
+            if early:
+                bad.append((name, early[:4]))
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            close()
+            name, early, seen = m.group(1), [], False
+            continue
+        if "ACQBULK" in line:
+            seen = True
+        elif not seen and re.search(r"\bLDG\S*\.CONSTANT\b", line):
+            early.append(line.strip()[:80])
+    close()
+    assert waits >= 10, "expected the tcgen05 tap-GEMM kernels, the finalize and the classifier head to wait (found %d)" % waits
+    assert not bad, "invariant loads ahead of griddepcontrol.wait: %r" % bad
