@@ -752,6 +752,7 @@ struct Ctx {
   int n_sm;
   int64_t L;
   cudaStream_t st;
+  bool prepared = false;   // weights_prepared call: no weight-preparation kernel runs ahead of the first layer
 };
 
 bool layer_on_tc(const Ctx& c, int id) { return c.tc; (void)id; }
@@ -861,7 +862,7 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
   if (on_tc) {
     // programmatic dependent launch for every tcgen05 layer but the first of a forward (its predecessor may be a weight
     // preparation kernel, whose output the prologue reads)
-    p.pdl = id != L_ENC2;
+    p.pdl = id != L_ENC2 || c.prepared;
     // the 128 -> 128 layers without output statistics on CTA pairs (conv_tc2.cu); $SPANON_TC2=0: one-SM kernel
     static const bool tc2_env = !(getenv("SPANON_TC2") && getenv("SPANON_TC2")[0] == '0');
     if (tc2_env && tapgemm_tc2_supported(p)) SPANON_TRY(launch_tapgemm_tc2(p, c.n_sm, c.st));
@@ -964,7 +965,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
   }
   // ---- per-call weight preparation (weights may have changed since the last call) ----
-  if (!(opts && opts->weights_prepared)) {
+  c.prepared = opts && opts->weights_prepared;
+  if (!c.prepared) {
   SPANON_TRY(pack_layer(c, L_ENC2, w->enc_w[1]));
   SPANON_TRY(pack_layer(c, L_ENC5, w->enc_w[2]));
   SPANON_TRY(pack_layer(c, L_ENC8, w->enc_w[3]));
@@ -1115,6 +1117,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         dim3 pg((unsigned)ceil_div(L3, PL_NT * PL_ROWS), 16u, (unsigned)nb);   // ReLU(x + b2) -> BatchNorm 3 -> pooling
         pool_planar_kernel<<<pg, PL_NT, 0, c.st>>>((const __half*)X[3], 16, (int)L3, w->tdnn_b[2], c.ws.bn_scale[3],
                                                    c.ws.bn_shift[3], c.ws.pool);
+        SPANON_TRY(check_launch("pool_kernel"));
         }
       } else {
         SPANON_TRY(run_layer(c, L_TD0, {X[0], X[1], 3, 0, w->tdnn_b[0], 1, 1, -1, OUT_CHANNELS_LAST}, nb));
@@ -1123,8 +1126,8 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         const int64_t n_el = 128 * L3;
         dim3 pg((unsigned)std::min<int64_t>(ceil_div(n_el, 256 * 16), 256), (unsigned)nb);
         pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
+        SPANON_TRY(check_launch("pool_kernel"));
       }
-      SPANON_TRY(check_launch("pool_kernel"));
       SPANON_CUDA_TRY(launch_pdl(clf_head_kernel, dim3((unsigned)nb), dim3(128), 0, c.st, true, (const double*)c.ws.pool,
                                  pool_noise ? pool_noise + b0 * 128 : (const float*)nullptr, L3, *w, logp + b0 * 2,
                                  (const unsigned*)(c.ws.counter + 1)));
@@ -1199,7 +1202,8 @@ extern "C" int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWei
     SPANON_CUDA_TRY(cudaGetDevice(&dev));
     SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
   }
-  if (!(opts && opts->weights_prepared)) {
+  c.prepared = opts && opts->weights_prepared;
+  if (!c.prepared) {
     SPANON_TRY(pack_layer(c, L_ENC2, w->conv_w[1]));
     SPANON_TRY(pack_layer(c, L_ENC5, w->conv_w[2]));
     SPANON_TRY(pack_layer(c, L_DEC5, w->conv_w[3]));
