@@ -204,12 +204,14 @@ def profile_begin(device=None):
 
 
 def profile_end(max_entries=64):
-    """-> {kernel name: (launches, total ms)} since profile_begin (synchronises the stream)."""
+    """-> {kernel name: (launches, total ms)} since profile_begin (synchronises the stream).  Host latency ahead of an entry
+    point's first launch is booked by the library under "(host)" and left out here."""
     arr = (KernelTime * max_entries)()
     n = lib().spanon_profile_end(arr, max_entries)
     if n < 0:
         check(n, "profile_end")
-    return {arr[i].name.decode(): (int(arr[i].launches), float(arr[i].ms_total)) for i in range(n)}
+    return {arr[i].name.decode(): (int(arr[i].launches), float(arr[i].ms_total)) for i in range(n)
+            if not arr[i].name.decode().startswith("(")}
 
 
 def ptr(t):

@@ -18,6 +18,12 @@ void set_last_cuda_error(const char* what, cudaError_t e);
 // Kernel-time profile (spanon_profile_begin/_end): an event after every launch on the profiled stream.
 void profile_mark(const char* what);
 
+// First statement of an entry point that launches kernels: while a profile is on, the time from the previous mark to this
+// call (Python / host latency on an idle stream) is booked under "(host)" instead of inflating the first kernel's time.
+inline void profile_entry() {
+  if (g_profile_on.load(std::memory_order_relaxed)) profile_mark("(host)");
+}
+
 inline int check_launch(const char* what) {
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   if (g_profile_on.load(std::memory_order_relaxed)) profile_mark(what);

@@ -957,6 +957,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
   const size_t esize = c.tc ? 2 : 4;
   carve(c.ws, base, chunk, L, c.tc, esize);
+  profile_entry();
   c.w = w; c.L = L; c.st = as_stream(stream);
 
   {
@@ -1196,6 +1197,7 @@ extern "C" int spanon_convrecon_fwd(const float* feats, const SpanonConvReconWei
   char* base = reinterpret_cast<char*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
   const size_t esize = c.tc ? 2 : 4;
   carve(c.ws, base, chunk, L, c.tc, esize, kInC_recon, false);
+  profile_entry();
   c.w = nullptr; c.L = L; c.st = as_stream(stream);
   {
     int dev = 0;

@@ -783,6 +783,7 @@ int fbank_launch(const TS* pcm, int64_t B, int64_t n_samples, int64_t pcm_stride
       !cfg->mel_w)
     return SPANON_ERR_NULL_POINTER;
   if (B > 65535) return SPANON_ERR_BAD_SHAPE;
+  profile_entry();
   cudaStream_t st = as_stream(stream);
   const int64_t T = 1 + n_samples / cfg->hop_length;
   SPANON_TRY(fill_i32(utt_max, B, INT32_MIN, st));

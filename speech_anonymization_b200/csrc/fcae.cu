@@ -293,6 +293,7 @@ extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
   const int run_clf = logp != nullptr;
   if (run_clf && (!workspace || workspace_bytes < spanon_fcae_workspace_bytes(B, T))) return SPANON_ERR_WORKSPACE;
   if (run_clf && (reinterpret_cast<uintptr_t>(workspace) & 7)) return SPANON_ERR_MISALIGNED;
+  profile_entry();
   cudaStream_t st = as_stream(stream);
   static std::atomic<unsigned long long> attr_done{0};     // per device (one process may drive several GPUs)
   int dev = 0;
@@ -328,6 +329,7 @@ extern "C" int spanon_fcae_classify(const float* z, const SpanonFcaeWeights* w, 
   if (!z || !logp || !workspace) return SPANON_ERR_NULL_POINTER;
   if (workspace_bytes < spanon_fcae_workspace_bytes(B, T)) return SPANON_ERR_WORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 7) return SPANON_ERR_MISALIGNED;
+  profile_entry();
   cudaStream_t st = as_stream(stream);
   static std::atomic<unsigned long long> attr_done{0};
   int dev = 0;
@@ -384,6 +386,7 @@ extern "C" int spanon_fcae_fwd_static(const float* feats, const SpanonFcaeWeight
   if (!feats || !recon) return SPANON_ERR_NULL_POINTER;
   if ((norm_mean == nullptr) != (norm_std == nullptr)) return SPANON_ERR_NULL_POINTER;
   const int run_clf = logp != nullptr;
+  profile_entry();
   cudaStream_t st = as_stream(stream);
   int dev = 0;
   const int n_sm = current_device_sms(&dev);

@@ -201,24 +201,23 @@ __global__ void __launch_bounds__(XV_THREADS, 1) xv_gemm_kernel(XvGemmParams p) 
 
 // feats [B][T][80] fp32 -> planes [B][10][Rp][8] fp16 with reflected halo rows
 __global__ void xv_input_kernel(const float* __restrict__ feats, __half* __restrict__ out, int T, int Rp, int F) {
-  const int b = blockIdx.y;
-  const int planes = F / 8;
-  const int64_t n = (int64_t)(T + 2 * XV_H) * planes;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int pl = (int)(i % planes), r = (int)(i / planes);
-    int m = r - XV_H;
-    if (m < 0) m = -m;
-    if (m >= T) m = 2 * (T - 1) - m;
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
-    if (m >= 0 && m < T) {
-      const float4* src = reinterpret_cast<const float4*>(feats + ((int64_t)b * T + m) * F + pl * 8);
-      const float4 x0 = __ldg(src), x1 = __ldg(src + 1);
-      __half2* oh = reinterpret_cast<__half2*>(&o);
-      oh[0] = __floats2half2_rn(x0.x, x0.y); oh[1] = __floats2half2_rn(x0.z, x0.w);
-      oh[2] = __floats2half2_rn(x1.x, x1.y); oh[3] = __floats2half2_rn(x1.z, x1.w);
-    }
-    *reinterpret_cast<uint4*>(out + (((int64_t)b * planes + pl) * Rp + r) * 8) = o;
+  // grid = (row blocks, planes, B): consecutive lanes = consecutive rows of ONE plane, so a warp writes 512 contiguous
+  // bytes (the first version walked (row, plane) pairs: 16-byte pieces scattered over ten planes, 0.2 ms for 29 MB)
+  const int b = blockIdx.z, pl = blockIdx.y, planes = F / 8;
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= T + 2 * XV_H) return;
+  int m = r - XV_H;
+  if (m < 0) m = -m;
+  if (m >= T) m = 2 * (T - 1) - m;
+  uint4 o = make_uint4(0u, 0u, 0u, 0u);
+  if (m >= 0 && m < T) {
+    const float4* src = reinterpret_cast<const float4*>(feats + ((int64_t)b * T + m) * F + pl * 8);
+    const float4 x0 = __ldg(src), x1 = __ldg(src + 1);
+    __half2* oh = reinterpret_cast<__half2*>(&o);
+    oh[0] = __floats2half2_rn(x0.x, x0.y); oh[1] = __floats2half2_rn(x0.z, x0.w);
+    oh[2] = __floats2half2_rn(x1.x, x1.y); oh[3] = __floats2half2_rn(x1.z, x1.w);
   }
+  *reinterpret_cast<uint4*>(out + (((int64_t)b * planes + pl) * Rp + r) * 8) = o;
 }
 
 // Conv1d weight [Cout][Cin][k] fp32 -> [n_tile][k_stage][tap][2 chunks][256 cols][8] fp16 (UMMA K-major B operand, LBO = 4 KB)
@@ -278,8 +277,8 @@ xv_pool_kernel(const __half* __restrict__ x, const float* __restrict__ rel_len, 
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const double a = warp_sum((double)s[j]), c = warp_sum((double)q[j]);
-    if (lane == 0) { red[0][warp][j] = a; red[1][warp][j] = c; }
+    const float a = warp_sum(s[j]), c = warp_sum(q[j]);        // (<= 4 rows per lane: fp32 is exact enough here;
+    if (lane == 0) { red[0][warp][j] = (double)a; red[1][warp][j] = (double)c; }   //  the cross-warp sums are fp64)
   }
   __syncthreads();
   if (tid < 8) {
@@ -302,34 +301,42 @@ __device__ __forceinline__ float xv_bn(float x, const SpanonBatchNorm& bn, int c
   return (x - bn.running_mean[c]) * rsqrtf(bn.running_var[c] + 1e-5f) * bn.weight[c] + bn.bias[c];
 }
 
-// Linear(3000 -> 128) embedding + the Classifier MLP + log-softmax: one block (128 threads) per utterance
-__global__ void __launch_bounds__(128)
+// Linear(3000 -> 128) embedding + the Classifier MLP + log-softmax: one block per utterance.  XV_HEAD_NT threads: sixteen
+// warps share the 128 embedding rows (a warp per row, coalesced weight reads) -- with four warps the 1.5 MB weight matrix was
+// streamed by 240 warps on the whole GPU, latency-bound at 0.19 ms.
+constexpr int XV_HEAD_NT = 512;
+__global__ void __launch_bounds__(XV_HEAD_NT)
 xv_head_kernel(const float* __restrict__ pooled, SpanonXvectorWeights w, int n_classes, float* __restrict__ emb_out,
                float* __restrict__ logp) {
   __shared__ float sp[2 * XV_POOLC];
   __shared__ float e[XV_EMB], h[XV_EMB], o[8];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < 2 * XV_POOLC; i += 128) sp[i] = pooled[(int64_t)b * 2 * XV_POOLC + i];
+  for (int i = tid; i < 2 * XV_POOLC; i += XV_HEAD_NT) sp[i] = pooled[(int64_t)b * 2 * XV_POOLC + i];
   __syncthreads();
-  for (int j = warp; j < XV_EMB; j += 4) {        // a warp per output: coalesced reads of the weight row
+  for (int j = warp; j < XV_EMB; j += XV_HEAD_NT / 32) {        // a warp per output: coalesced reads of the weight row
     const float* wr = w.emb_w + (int64_t)j * 2 * XV_POOLC;
-    float a = 0.f;
-    for (int i = lane; i < 2 * XV_POOLC; i += 32) a = fmaf(__ldg(wr + i), sp[i], a);
-    a = warp_sum(a);
+    float a0 = 0.f, a1 = 0.f;
+    int i = lane;
+    for (; i + 32 < 2 * XV_POOLC; i += 64) { a0 = fmaf(__ldg(wr + i), sp[i], a0); a1 = fmaf(__ldg(wr + i + 32), sp[i + 32], a1); }
+    if (i < 2 * XV_POOLC) a0 = fmaf(__ldg(wr + i), sp[i], a0);
+    const float a = warp_sum(a0 + a1);
     if (lane == 0) e[j] = a + w.emb_b[j];
   }
   __syncthreads();
-  if (emb_out) emb_out[(int64_t)b * XV_EMB + tid] = e[tid];
-  if (!logp) return;                                                // Xvector.forward alone: the embedding is the result
-  const float x0 = xv_bn(xv_leaky(e[tid]), w.clf_norm, tid);      // Classifier: act -> norm
+  if (emb_out && tid < XV_EMB) emb_out[(int64_t)b * XV_EMB + tid] = e[tid];
+  if (!logp) return;                                              // Xvector.forward alone: the embedding is the result
+  float x0 = 0.f;
+  if (tid < XV_EMB) x0 = xv_bn(xv_leaky(e[tid]), w.clf_norm, tid);  // Classifier: act -> norm
   __syncthreads();
-  e[tid] = x0;
+  if (tid < XV_EMB) e[tid] = x0;
   __syncthreads();
-  {
-    const float* wr = w.dnn_w + (int64_t)tid * XV_EMB;            // DNN.block_0: linear -> act -> norm
-    float a = w.dnn_b[tid];
-    for (int i = 0; i < XV_EMB; ++i) a = fmaf(__ldg(wr + i), e[i], a);
-    h[tid] = xv_bn(xv_leaky(a), w.dnn_bn, tid);
+  for (int j = warp; j < XV_EMB; j += XV_HEAD_NT / 32) {        // DNN.block_0: linear -> act -> norm
+    const float* wr = w.dnn_w + (int64_t)j * XV_EMB;
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < XV_EMB / 32; ++k) a = fmaf(__ldg(wr + lane + 32 * k), e[lane + 32 * k], a);
+    a = warp_sum(a);
+    if (lane == 0) h[j] = xv_bn(xv_leaky(a + w.dnn_b[j]), w.dnn_bn, j);
   }
   __syncthreads();
   if (warp == 0) {
@@ -399,6 +406,7 @@ extern "C" int spanon_xvector_classify(const float* feats, const float* rel_len,
   if (!feats || (!logp && !emb_out) || !workspace) return SPANON_ERR_NULL_POINTER;
   if (B > 65535) return SPANON_ERR_BAD_SHAPE;
   if (workspace_bytes < spanon_xvector_workspace_bytes(B, T)) return SPANON_ERR_WORKSPACE;
+  profile_entry();
   cudaStream_t st = as_stream(stream);
   const int Rp = xv_rows(T);
   XvWs ws;
@@ -422,7 +430,7 @@ extern "C" int spanon_xvector_classify(const float* feats, const float* rel_len,
     }
   }
   {
-    dim3 grid((unsigned)std::min<int64_t>(ceil_div((T + 2 * XV_H) * (F / 8), 256), 64), (unsigned)B);
+    dim3 grid((unsigned)ceil_div(T + 2 * XV_H, 256), (unsigned)(F / 8), (unsigned)B);
     xv_input_kernel<<<grid, 256, 0, st>>>(feats, ws.in, (int)T, Rp, (int)F);
     SPANON_TRY(check_launch("xv_input_kernel"));
   }
@@ -461,6 +469,6 @@ extern "C" int spanon_xvector_classify(const float* feats, const float* rel_len,
     xv_pool_kernel<<<grid, 256, 0, st>>>(ws.last, rel_len, pool_noise, (int)T, Rp, P, XV_POOLC, ws.pooled);
     SPANON_TRY(check_launch("xv_pool_kernel"));
   }
-  xv_head_kernel<<<(unsigned)B, 128, 0, st>>>(ws.pooled, *w, 2, emb_out, logp);
+  xv_head_kernel<<<(unsigned)B, XV_HEAD_NT, 0, st>>>(ws.pooled, *w, 2, emb_out, logp);
   return check_launch("xv_head_kernel");
 }
