@@ -60,7 +60,7 @@ __host__ __device__ constexpr int tc_epi_warps(int xf);
 __host__ __device__ constexpr int tc_threads(int xf) { return (tc_epi_warps(xf) + 12) * 32; }
 constexpr int TC_EPI_THREADS = 128;       // Toeplitz epilogue (always four warps)
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
-constexpr int TC_MAX_STAGES = 16;
+constexpr int TC_MAX_STAGES = 32;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
 enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16, XF_DYN = 32, XF_FLOW = 64 };
 constexpr int TC_GEN_SIG = 320;           // fp16 samples of one tile's signal window (XF_GEN)
@@ -92,7 +92,8 @@ struct TcLayout {        // byte offsets inside dynamic shared memory
 };
 
 constexpr int TC_ST_PITCH = 17;              // fp32 row pitch of the statistics transpose buffer ([32 rows][16 columns] per warp)
-__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, bool stats, bool gen = false) {
+__host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, int slab_used, bool stats, bool gen = false,
+                                              int ring_cap = 0) {
   TcLayout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;              // == 1 (mod 8): chunks start 16 B apart modulo 128 B
   L.lbo_a = (uint32_t)L.slab * 16u;
@@ -106,10 +107,11 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   // XF_GEN: ring of TC_GEN_SLOTS signal windows (two fp16 copies each, the second shifted by one sample) + one
   // (mean, 1/std) table per loader warp
   L.bars = L.sig + (gen ? (uint32_t)TC_GEN_SLOTS * 2u * TC_GEN_SIG * 2u + (uint32_t)TC_LOAD_WARPS * 2u * TC_GEN_MAXF * 4u : 0u);
-  L.a = (L.bars + 512u + 127u) / 128u * 128u;
+  L.a = (L.bars + 1024u + 127u) / 128u * 128u;
   const size_t avail = TC_SMEM_LIMIT > L.a ? TC_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
-  L.n_stages = ns > TC_MAX_STAGES ? TC_MAX_STAGES : ns;
+  const int cap = ring_cap >= TC_XF_WARPS && ring_cap < TC_MAX_STAGES ? ring_cap : TC_MAX_STAGES;
+  L.n_stages = ns > cap ? cap : ns;
   // a multiple of the number of transform warps: every ring slot then belongs to ONE warp, so each slot's mbarriers
   // are waited on in order by a single consumer (a waiter two phases behind would alias the parity)
   L.n_stages = L.n_stages / TC_XF_WARPS * TC_XF_WARPS;
@@ -117,9 +119,9 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   return L;
 }
 
-// barrier slots (8 B each): [0,16) raw (bulk copy landed), [16,32) full (transformed), [32,48) empty (MMAs read it),
-// [48,50) tmem_full, [50,52) tmem_empty, 52 weights; 54 = TMEM base pointer
-enum { B_RAW = 0, B_FULL = 16, B_EMPTY = 32, B_TFULL = 48, B_TEMPTY = 50, B_W = 52, B_TPTR = 54, B_SFULL = 56, B_SEMPTY = 60 };
+// barrier slots (8 B each): [0,32) raw (bulk copy landed), [32,64) full (transformed), [64,96) empty (MMAs read it),
+// [96,98) tmem_full, [98,100) tmem_empty, 100 weights; 102 = TMEM base pointer; 104.. XF_GEN signal ring
+enum { B_RAW = 0, B_FULL = 32, B_EMPTY = 64, B_TFULL = 96, B_TEMPTY = 98, B_W = 100, B_TPTR = 102, B_SFULL = 104, B_SEMPTY = 108 };
 
 // One CTA's work on one layer.  cta_idx / n_cta: this CTA's index among the CTAs working on the layer.  rr_group == 0: the
 // CTA walks a CONTIGUOUS run of tiles; rr_group = G > 0: groups of G consecutive tiles are dealt round-robin to the
@@ -128,7 +130,7 @@ template <int COUT_V, int XF, int MG>
 __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles,
                                         int tile_step, int cta_idx, int n_cta, int rr_group, int mma_group) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0, p.ring_cap);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int E = tc_epi_warps(XF), TC_MMA_WARP = E + 11;
   const int wd = warp - E;                                   // role index among the non-epilogue warps
@@ -796,7 +798,7 @@ int launch_tc_mg(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   if (slab_used > 160) return SPANON_ERR_UNSUPPORTED;
   const int nst = p.cin_v / TC_STAGE_CH;
   if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
-  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
+  const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, slab_used, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0, p.ring_cap);
   if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   if ((XF & XF_GEN) && (slab_used > 144 || 2 * 143 + 17 > TC_GEN_SIG || p.gen_F > TC_GEN_MAXF || p.gen_F < 32 || p.cin_mod != 32 || p.cin_v != 64 || !p.gen_feats ||
                         !p.gen_w || !p.gen_b || (p.gen_mean == nullptr) != (p.gen_std == nullptr)))
@@ -851,7 +853,7 @@ int launch_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   else {
     int lo = 0, hi = 0;
     for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
-    const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, TC_M - lo + hi, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0);
+    const TcLayout L = tc_layout(p.ntaps, p.cin_v, COUT_V, TC_M - lo + hi, (XF & XF_STATS) != 0, (XF & XF_GEN) != 0, p.ring_cap);
     // measured per layer on B200 (same-box A/B): rounds of 4 stages pay on decoder.4 o 5 (7 taps) and tdnn.3 / tdnn.6
     // (-5 .. -12 us), and cost 3 .. 10 us on the layers whose epilogue reduces statistics or whose ring holds one tile
     if (p.mma_group >= 4 && L.n_stages >= 16) {
@@ -892,7 +894,7 @@ int launch_tapgemm_tc_chain(const TapGemmParams* ps, int n, const int* ctas, int
     SPANON_TRY(tc_geometry(p, &g.halo_lo, &g.slab_used));
     const int nst = p.cin_v / TC_STAGE_CH;
     if (nst != 2 && nst != 4 && nst != 8) return SPANON_ERR_UNSUPPORTED;
-    const TcLayout L = tc_layout(p.ntaps, p.cin_v, 128, g.slab_used, false, false);
+    const TcLayout L = tc_layout(p.ntaps, p.cin_v, 128, g.slab_used, false, false, p.ring_cap);
     if (L.n_stages < TC_XF_WARPS || L.total > TC_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
     smem_max = std::max(smem_max, L.total);
     g.tile_step = TC_M;

@@ -28,7 +28,7 @@ namespace {
 using namespace tc;
 constexpr int T2_N = 128;                   // output columns of the layer (both CTAs together)
 constexpr int T2_NH = T2_N / 2;             // weight columns resident per CTA
-constexpr int T2_XF_WARPS = 8, T2_LOAD_WARPS = 2, T2_STAGE_CH = 16, T2_MAX_STAGES = 16;
+constexpr int T2_XF_WARPS = 8, T2_LOAD_WARPS = 2, T2_STAGE_CH = 16, T2_MAX_STAGES = 32;
 __host__ __device__ constexpr int t2_epi_warps(int xf) { return (xf & 24) ? 8 : 4; }     // 8 = X2_STATS, 16 = X2_POOL
 __host__ __device__ constexpr int t2_threads(int xf) { return (t2_epi_warps(xf) + 12) * 32; }
 #ifndef T2_MG_VALUE
@@ -38,11 +38,11 @@ constexpr int T2_MG = T2_MG_VALUE;            // stages per MMA issue round (div
 constexpr size_t T2_SMEM_LIMIT = 232448;
 enum { X2_IDENT = 0, X2_SILU = 1, X2_RELU = 2, X2_T2 = 4, X2_STATS = 8, X2_POOL = 16 };
 constexpr int T2_ST_PITCH = 17;
-enum { C_RAW = 0, C_FULL = 16, C_EMPTY = 32, C_TFULL = 48, C_TEMPTY = 50, C_W = 52, C_TPTR = 54 };
+enum { C_RAW = 0, C_FULL = 32, C_EMPTY = 64, C_TFULL = 96, C_TEMPTY = 98, C_W = 100, C_TPTR = 102 };     // (up to 32 stages)
 
 struct T2Layout { uint32_t w, epi, red, bars, a, total, w_bytes, stage_bytes, lbo_a; int n_stages, slab; };
 
-__host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_used, bool stats, bool pool = false) {
+__host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_used, bool stats, bool pool, int max_stages) {
   T2Layout L;
   L.slab = (slab_used + 7) / 8 * 8 + 1;
   L.lbo_a = (uint32_t)L.slab * 16u;
@@ -53,10 +53,10 @@ __host__ __device__ inline T2Layout t2_layout(int ntaps, int cin_v, int slab_use
   L.red = (L.epi + T2_N * 4u * (pool ? 3u : 1u) + 7u) / 8u * 8u;          // (pooling: bias, scale, shift)
   // statistics: one [32][17] transpose buffer per epilogue warp; pooling: the CTA's [128 bins][sum, sum of squares]
   L.bars = L.red + (stats ? 8u * 32u * T2_ST_PITCH * 4u : pool ? 2u * T2_N * 8u : 0u);
-  L.a = (L.bars + 512u + 127u) / 128u * 128u;
+  L.a = (L.bars + 1024u + 127u) / 128u * 128u;
   const size_t avail = T2_SMEM_LIMIT > L.a ? T2_SMEM_LIMIT - L.a : 0;
   int ns = (int)(avail / L.stage_bytes);
-  L.n_stages = (ns > T2_MAX_STAGES ? T2_MAX_STAGES : ns) / T2_XF_WARPS * T2_XF_WARPS;
+  L.n_stages = (ns > max_stages ? max_stages : ns) / T2_XF_WARPS * T2_XF_WARPS;
   L.total = L.a + (uint32_t)L.n_stages * L.stage_bytes;
   return L;
 }
@@ -115,9 +115,9 @@ __device__ __forceinline__ __half2 silu_from_half2(__half2 hh) {
 
 template <int XF>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(t2_threads(XF), 1)
-tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles) {
+tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int slab_used, int tiles_per_utt, int total_tiles, int max_stages) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0);
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0, max_stages);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int E = t2_epi_warps(XF), MMA_WARP = E + 11;
   // tensor memory: two accumulator buffers
@@ -576,7 +576,9 @@ int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   for (int t = 0; t < p.ntaps; ++t) { lo = std::min(lo, p.shift[t]); hi = std::max(hi, p.shift[t]); }
   const int halo_lo = -lo, slab_used = TC_M + halo_lo + hi;
   if (slab_used > 160 || p.cin_v != 128) return SPANON_ERR_UNSUPPORTED;
-  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0);
+  // ring depth: up to T2_MAX_STAGES 16-channel stages (8 per tile); $SPANON_T2_STAGES caps it (A/B: 16 = two tiles)
+  static const int max_stages = [] { const char* e = getenv("SPANON_T2_STAGES"); const int v = e ? atoi(e) : T2_MAX_STAGES; return v >= 8 && v <= T2_MAX_STAGES ? v : T2_MAX_STAGES; }();
+  const T2Layout L = t2_layout(p.ntaps, p.cin_v, slab_used, (XF & X2_STATS) != 0, (XF & X2_POOL) != 0, max_stages);
   if (L.n_stages < T2_XF_WARPS || L.total > T2_SMEM_LIMIT) return SPANON_ERR_UNSUPPORTED;
   auto kern = tapgemm_tc2_kernel<XF>;
   SPANON_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
@@ -584,7 +586,7 @@ int launch_tc2(const TapGemmParams& p, int n_sm, cudaStream_t st) {
   const int total = tiles_per_utt * p.B;
   const int pairs = (total + 1) / 2;
   const int grid = 2 * std::max(1, std::min(pairs, n_sm / 2));
-  SPANON_CUDA_TRY(launch_pdl(kern, dim3((unsigned)grid), dim3((unsigned)t2_threads(XF)), L.total, st, p.pdl != 0, p, halo_lo, slab_used, tiles_per_utt, total));
+  SPANON_CUDA_TRY(launch_pdl(kern, dim3((unsigned)grid), dim3((unsigned)t2_threads(XF)), L.total, st, p.pdl != 0, p, halo_lo, slab_used, tiles_per_utt, total, max_stages));
   return check_launch(p.tag ? p.tag : "tapgemm_tc2_kernel");
 }
 

@@ -863,6 +863,11 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
     // programmatic dependent launch for every tcgen05 layer but the first of a forward (its predecessor may be a weight
     // preparation kernel, whose output the prologue reads)
     p.pdl = id != L_ENC2 || c.prepared;
+    // $SPANON_TC_STAGES: cap on the one-SM kernel's operand ring, 8 .. 32 stages of 16 channels.  Default 16: a deeper ring
+    // measured no gain there (encoder.5 178 vs 180 us, decoder.4o5 210 vs 211), unlike on the CTA-pair kernel, whose ring
+    // holds 8 stages per tile (32 stages: tdnn.3 122 -> 114, decoder.0 153 -> 146, tdnn.6 157 -> 152 us).
+    static const int ring_cap_env = getenv("SPANON_TC_STAGES") ? atoi(getenv("SPANON_TC_STAGES")) : 16;
+    p.ring_cap = ring_cap_env;
     // the 128 -> 128 layers without output statistics on CTA pairs (conv_tc2.cu); $SPANON_TC2=0: one-SM kernel
     static const bool tc2_env = !(getenv("SPANON_TC2") && getenv("SPANON_TC2")[0] == '0');
     if (tc2_env && tapgemm_tc2_supported(p)) SPANON_TRY(launch_tapgemm_tc2(p, c.n_sm, c.st));

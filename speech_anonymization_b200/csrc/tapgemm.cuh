@@ -85,6 +85,7 @@ struct TapGemmParams {
   // pair kernel (conv_tc2.cu), tdnn.6: instead of storing the output, ReLU(acc + bias) * e_scale + e_shift is summed (value and
   // square) into the StatisticsPooling bins of the [B][cout][rows_out] -> [B][rows_out][cout] REINTERPRETATION: pool [B][128][2]
   double* pool;
+  int ring_cap;        // one-SM tcgen05 kernel: cap on the operand ring's 16-channel stages (0 = TC_MAX_STAGES)
   int pdl;             // tcgen05 kernels: launch as a programmatic dependent of the previous kernel (common.cuh launch_pdl)
   unsigned* err_flag;  // set to 1 if a dataflow wait timed out (results are then invalid; the consumer kernels report it)
   long long* trace;    // debug ($SPANON_TC_TRACE=1): per-CTA clock64 stamps [grid][3 roles][TRACE_N]
