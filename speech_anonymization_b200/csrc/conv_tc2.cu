@@ -611,7 +611,8 @@ bool tapgemm_tc2_supported(const TapGemmParams& p) {
   // measured per layer (same-box A/B): the pair kernel wins on the k5 layers (tdnn.0 -21, decoder.0 -20, encoder.11 -14 us)
   // and on tdnn.3 / tdnn.6 (-5 us); the 3-tap layers that also reduce statistics (encoder.8, decoder.1) are HBM- and
   // epilogue-paced and lose 12 .. 20 us to the pair's lock-step, so they stay on the one-SM kernel
-  if (p.stats && p.ntaps < 5) return false;
+  static const bool stats3_env = getenv("SPANON_TC2_STATS3") && getenv("SPANON_TC2_STATS3")[0] == '1';
+  if (p.stats && p.ntaps < 5 && !stats3_env) return false;
   for (int t = 0; t + 1 < p.ntaps; ++t)
     if (p.tap_kmax[t] != p.cin_v) return false;
   if (p.tap_kmax[p.ntaps - 1] % (T2_STAGE_CH * T2_MG) != 0) return false;
