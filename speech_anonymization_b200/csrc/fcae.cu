@@ -6,15 +6,17 @@
 //                                               StatisticsPooling over T, MLP 80-40-40-20-2, log_softmax
 //   StatisticsPooling                 speechbrain/speechbrain/nnet/pooling.py:263-312
 //
-// Kernel design: one thread = one frame; the six autoencoder layers and the two per-frame
-// classifier layers run back to back with activations in shared memory ([dim][frame],
-// conflict free) and all 18.4 k weights resident in shared memory (transposed so that one
-// broadcast 128-bit load feeds four FMAs).  HBM traffic is the algorithmic minimum: 320 B in
-// and 320 B out per frame; the pooled classifier statistics leave the kernel as fp64 atomics.
-// BatchNorm layers use running statistics (eval mode).
+// Kernel design: the six autoencoder layers and the two per-frame classifier layers run back to back on a 256-frame tile
+// with activations in shared memory ([dim][frame]) and all 18.4 k weights resident in shared memory (transposed: [in][out]).
+// fcae4_kernel (default): a thread owns 4 consecutive frames x a quarter of the layer's outputs as a register tile -- one
+// 128-bit load of activations and one broadcast 128-bit load of weights per sixteen FMAs.  fcae_kernel (round 1,
+// $SPANON_FCAE=1): one thread = one frame, one broadcast 128-bit weight load per four FMAs -- bound by the shared-memory
+// pipe.  HBM traffic is the algorithmic minimum: 320 B in and 320 B out per frame; the pooled classifier statistics leave
+// the kernel as fp64 atomics.  BatchNorm layers use running statistics (eval mode).
 #include "common.cuh"
 #include <algorithm>
 #include <math.h>
+#include <stdlib.h>
 
 namespace spanon {
 namespace {
@@ -48,6 +50,7 @@ struct FcSmem {
 
 __device__ __forceinline__ void load_wt(float* dst, const float* __restrict__ w, int out, int in, int tid) {
   // PyTorch Linear weight [out][in] -> smem [in][out]
+#pragma unroll 4
   for (int e = tid; e < out * in; e += NTHR) {
     const int o = e / in, i = e - o * in;
     dst[i * out + o] = __ldg(w + e);
@@ -188,6 +191,229 @@ fcae_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* _
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// fcae4_kernel: the same forward with a REGISTER TILE of 4 frames x up to 20 outputs per thread.  fcae_kernel (one thread =
+// one frame) needs one broadcast LDS.128 of weights per four FMAs and is bound by the shared-memory pipe (0.27 ms for
+// 64 x 10 s = 3 % of the HBM roofline).  Here a thread owns four consecutive frames of the 256-frame tile and a quarter of
+// the layer's outputs (warps 2g, 2g + 1 take output group g): per input channel one LDS.128 brings its four frames' values
+// and one LDS.128 per output chunk brings four weights for sixteen FMAs -- 3.6 x fewer shared-memory instructions per FMA.
+// Layers are separated by a CTA barrier (a thread no longer owns whole frames).
+constexpr int LDA4 = 260;                   // activation row stride (floats): a multiple of 4 (aligned float4 over frames)
+struct Fc4Smem {
+  float X[80 * LDA4];
+  float Y[60 * LDA4];
+  float W[W_END];
+  float Bv[B_END];
+  float bn_s[20], bn_t[20];
+  float nmean[D_IN], nstd[D_IN];
+  int fb[NTHR], ft[NTHR];                    // utterance / frame-in-utterance of the tile's frames (-1 past the end)
+};
+
+// xin [IN][LDA4] -> xout [OUT][LDA4] for this thread's 4 frames (fg) and its output chunks (group og of 4)
+template <int IN, int OUT, bool RELU, int NC>
+__device__ __forceinline__ void dense4_body(const float* __restrict__ xp, float* __restrict__ op, const float* __restrict__ wp,
+                                            const float* __restrict__ bp) {
+  float acc[NC][4][4];                               // [chunk][output in chunk][frame]
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const float4 b4 = *reinterpret_cast<const float4*>(bp + 4 * c);
+#pragma unroll
+    for (int f = 0; f < 4; ++f) { acc[c][0][f] = b4.x; acc[c][1][f] = b4.y; acc[c][2][f] = b4.z; acc[c][3][f] = b4.w; }
+  }
+#pragma unroll 4
+  for (int i = 0; i < IN; ++i) {
+    const float4 x4 = *reinterpret_cast<const float4*>(xp + i * LDA4);
+    const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const float4 w4 = *reinterpret_cast<const float4*>(wp + i * OUT + 4 * c);
+      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int f = 0; f < 4; ++f) acc[c][k][f] = fmaf(xv[f], wv[k], acc[c][k][f]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float4 o = make_float4(acc[c][k][0], acc[c][k][1], acc[c][k][2], acc[c][k][3]);
+      if (RELU) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+      *reinterpret_cast<float4*>(op + (4 * c + k) * LDA4) = o;
+    }
+}
+
+// xin [IN][LDA4] -> xout [OUT][LDA4] for this thread's 4 frames (fg) and its output chunks (group og of 4).  The OUT / 4
+// chunks of four outputs are dealt to the four groups as evenly as they go; a group's chunk count is uniform over its two
+// warps, so the choice between the two instantiations is a warp-uniform branch outside the loops.
+template <int IN, int OUT, bool RELU>
+__device__ __forceinline__ void dense4(const float* __restrict__ xin, float* __restrict__ xout, const float* __restrict__ Wt,
+                                       const float* __restrict__ bias, int fg, int og) {
+  constexpr int NCH = OUT / 4;                       // float4 chunks of outputs
+  constexpr int MAXC = (NCH + 3) / 4;                // chunks per thread: MAXC, or MAXC - 1 when NCH is not a multiple of 4
+  static_assert(OUT % 4 == 0, "OUT must be a multiple of 4");
+  const int cb = og * NCH / 4, nch = (og + 1) * NCH / 4 - cb;
+  const float* xp = xin + 4 * fg;
+  float* op = xout + 4 * cb * LDA4 + 4 * fg;
+  if (nch == MAXC) dense4_body<IN, OUT, RELU, MAXC>(xp, op, Wt + 4 * cb, bias + 4 * cb);
+  else if constexpr (MAXC > 1) dense4_body<IN, OUT, RELU, MAXC - 1>(xp, op, Wt + 4 * cb, bias + 4 * cb);
+}
+
+__global__ void __launch_bounds__(NTHR, 1)
+fcae4_kernel(const float* __restrict__ feats, SpanonFcaeWeights w, const float* __restrict__ norm_mean,
+             const float* __restrict__ norm_std, const int32_t* __restrict__ utt_max, float top_db,
+             float* __restrict__ recon, double* __restrict__ pool /*[B][40][2]*/, int64_t n_frames, int T, int run_clf) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Fc4Smem& S = *reinterpret_cast<Fc4Smem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int og = warp >> 1, fg = (warp & 1) * 32 + lane;          // output group, frame group (frames 4 fg .. 4 fg + 3)
+  load_wt(S.W + W_E0, w.enc_w[0], 60, 80, tid);
+  load_wt(S.W + W_E1, w.enc_w[1], 40, 60, tid);
+  load_wt(S.W + W_E2, w.enc_w[2], 20, 40, tid);
+  load_wt(S.W + W_C0, w.init_w[0], 40, 20, tid);
+  load_wt(S.W + W_C1, w.init_w[1], 40, 40, tid);
+  load_wt(S.W + W_D0, w.dec_w[0], 40, 20, tid);
+  load_wt(S.W + W_D1, w.dec_w[1], 60, 40, tid);
+  load_wt(S.W + W_D2, w.dec_w[2], 80, 60, tid);
+  for (int i = tid; i < 60; i += NTHR) S.Bv[B_E0 + i] = w.enc_b[0][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_E1 + i] = w.enc_b[1][i];
+  for (int i = tid; i < 20; i += NTHR) S.Bv[B_E2 + i] = w.enc_b[2][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_C0 + i] = w.init_b[0][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_C1 + i] = w.init_b[1][i];
+  for (int i = tid; i < 40; i += NTHR) S.Bv[B_D0 + i] = w.dec_b[0][i];
+  for (int i = tid; i < 60; i += NTHR) S.Bv[B_D1 + i] = w.dec_b[1][i];
+  for (int i = tid; i < 80; i += NTHR) S.Bv[B_D2 + i] = w.dec_b[2][i];
+  if (tid < 20) {
+    const float s = w.clf_norm.weight[tid] / sqrtf(w.clf_norm.running_var[tid] + 1e-5f);
+    S.bn_s[tid] = s;
+    S.bn_t[tid] = w.clf_norm.bias[tid] - w.clf_norm.running_mean[tid] * s;
+  }
+  if (tid < D_IN) {
+    S.nmean[tid] = norm_mean ? norm_mean[tid] : 0.f;
+    S.nstd[tid] = norm_std ? norm_std[tid] : 1.f;
+  }
+  __syncthreads();
+
+  // every CTA takes one contiguous, equal share of the frames (tiles of up to 256 inside it): 251 whole tiles over 148 CTAs
+  // would leave the second round 70 % full
+  const int64_t per = (n_frames + gridDim.x - 1) / gridDim.x;
+  const int64_t beg = blockIdx.x * per, end = min(n_frames, beg + per);
+  for (int64_t f0 = beg; f0 < end; f0 += NTHR) {
+    const int nf = (int)min((int64_t)NTHR, end - f0);
+    {   // this thread's frame of the tile: utterance and position (one 64-bit division per frame and tile)
+      const int64_t frame = f0 + tid;
+      const int b = tid < nf ? (int)(frame / T) : -1;
+      S.fb[tid] = b;
+      S.ft[tid] = tid < nf ? (int)(frame - (int64_t)b * T) : 0;
+    }
+    // the tile's nf * 80 contiguous floats as 128-bit loads, all in flight before the first use, transposed into X[d][frame]
+    const float4* src4 = reinterpret_cast<const float4*>(feats + f0 * D_IN);      // (f0 * 80 floats: 16-byte aligned)
+    constexpr int NV = D_IN / 4;                       // 20 float4 per frame; 20 per thread as well
+    float4 v4[NV];
+#pragma unroll
+    for (int r = 0; r < NV; ++r) {
+      const int e4 = tid + r * NTHR;
+      v4[r] = (e4 / NV) < nf ? __ldg(src4 + e4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();                                   // fb / ft visible (and the previous tile's readers are done)
+#pragma unroll
+    for (int r = 0; r < NV; ++r) {
+      const int e4 = tid + r * NTHR;
+      const int fr = e4 / NV, d = (e4 - fr * NV) * 4;
+      float vv[4] = {v4[r].x, v4[r].y, v4[r].z, v4[r].w};
+      if (norm_mean && fr < nf) {
+        const float floor_db = utt_max ? key_to_float(utt_max[S.fb[fr]]) - top_db : -INFINITY;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) vv[q] = (fmaxf(vv[q], floor_db) - S.nmean[d + q]) / S.nstd[d + q];
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) S.X[(d + q) * LDA4 + fr] = vv[q];
+    }
+    __syncthreads();
+    dense4<80, 60, true>(S.X, S.Y, S.W + W_E0, S.Bv + B_E0, fg, og);
+    __syncthreads();
+    dense4<60, 40, true>(S.Y, S.X, S.W + W_E1, S.Bv + B_E1, fg, og);
+    __syncthreads();
+    dense4<40, 20, false>(S.X, S.Y, S.W + W_E2, S.Bv + B_E2, fg, og);  // bottleneck z in Y[0..20)
+    __syncthreads();
+    if (run_clf) {
+      // FullyConnected.py:93-95: BatchNorm1d(20) on the [B,20,T] REINTERPRETATION of z -> X rows 60..79
+      {
+        const int t20 = S.ft[tid] * 20;                  // thread = frame: its 20 bottleneck values
+        const bool valid = tid < nf;
+#pragma unroll
+        for (int d = 0; d < 20; ++d) {
+          const int ch = (t20 + d) / T;
+          S.X[(60 + d) * LDA4 + tid] = valid ? fmaf(S.Y[d * LDA4 + tid], S.bn_s[ch], S.bn_t[ch]) : 0.f;
+        }
+      }
+      __syncthreads();
+      dense4<20, 40, true>(S.X + 60 * LDA4, S.X, S.W + W_C0, S.Bv + B_C0, fg, og);
+      __syncthreads();
+      dense4<40, 40, true>(S.X, S.X + 40 * LDA4, S.W + W_C1, S.Bv + B_C1, fg, og);
+      __syncthreads();
+      // StatisticsPooling sums over frames: warp w takes channels 5w .. 5w + 4, lanes walk the tile's frames 32 at a time
+      // (a group of 32 consecutive frames is reduced in the warp when it lies inside one utterance)
+      const int b_first = S.fb[0], b_last = S.fb[nf - 1];
+      if (b_first == b_last) {          // the whole tile lies in one utterance (the usual case: T >> 256): one reduction per channel
+#pragma unroll 1
+        for (int c = warp * 5; c < warp * 5 + 5; ++c) {
+          const float* hrow = S.X + (40 + c) * LDA4;
+          float s1 = 0.f, q1 = 0.f;
+#pragma unroll
+          for (int g = 0; g < NTHR; g += 32) {
+            const float h = g + lane < nf ? hrow[g + lane] : 0.f;
+            s1 += h; q1 = fmaf(h, h, q1);
+          }
+          s1 = warp_sum(s1); q1 = warp_sum(q1);
+          if (lane == 0) {
+            atomicAdd(pool + ((int64_t)b_first * 40 + c) * 2 + 0, (double)s1);
+            atomicAdd(pool + ((int64_t)b_first * 40 + c) * 2 + 1, (double)q1);
+          }
+        }
+      } else {
+#pragma unroll 1
+      for (int c = warp * 5; c < warp * 5 + 5; ++c) {
+        const float* hrow = S.X + (40 + c) * LDA4;
+#pragma unroll 1
+        for (int g = 0; g < NTHR; g += 32) {
+          const int fr = g + lane;
+          const int b = S.fb[fr];
+          const bool valid = b >= 0;
+          const float h = valid ? hrow[fr] : 0.f;
+          const int b0 = __shfl_sync(0xffffffffu, b, 0);
+          const bool uniform = __all_sync(0xffffffffu, b == b0) && b0 >= 0;
+          if (uniform) {
+            const float s = warp_sum(h), q = warp_sum(h * h);
+            if (lane == 0) {
+              atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 0, (double)s);
+              atomicAdd(pool + ((int64_t)b0 * 40 + c) * 2 + 1, (double)q);
+            }
+          } else if (valid) {
+            atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 0, (double)h);
+            atomicAdd(pool + ((int64_t)b * 40 + c) * 2 + 1, (double)h * (double)h);
+          }
+        }
+      }
+      }
+      __syncthreads();
+    }
+    dense4<20, 40, true>(S.Y, S.X, S.W + W_D0, S.Bv + B_D0, fg, og);
+    __syncthreads();
+    dense4<40, 60, true>(S.X, S.Y, S.W + W_D1, S.Bv + B_D1, fg, og);
+    __syncthreads();
+    dense4<60, 80, false>(S.Y, S.X, S.W + W_D2, S.Bv + B_D2, fg, og);
+    __syncthreads();
+    float* dst = recon + f0 * D_IN;
+    for (int e = tid; e < nf * D_IN; e += NTHR) {
+      const int fr = e / D_IN, d = e - fr * D_IN;
+      dst[e] = S.X[d * LDA4 + fr];
+    }
+    __syncthreads();
+  }
+}
+
 // FullyConnSexClassifier.forward on its own (FullyConnected.py:88-104): the bottleneck z [B, T, 20] comes from the caller.
 __global__ void __launch_bounds__(NTHR, 1)
 fc_clf_kernel(const float* __restrict__ z, SpanonFcaeWeights w, double* __restrict__ pool, int64_t n_frames, int T) {
@@ -300,15 +526,25 @@ extern "C" int spanon_fcae_fwd(const float* feats, const SpanonFcaeWeights* w, c
   const int n_sm = current_device_sms(&dev);
   if (n_sm <= 0) return SPANON_ERR_CUDA;
   if (first_use_on_device(attr_done, dev))
+  {
     SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sizeof(FcSmem)));
+    SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sizeof(Fc4Smem)));
+  }
   double* pool = reinterpret_cast<double*>(workspace);
   if (run_clf) SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
   const int64_t n_frames = B * T;
   const int64_t n_tiles = ceil_div(n_frames, NTHR);
   const unsigned grid = (unsigned)std::min<int64_t>(n_tiles, n_sm);
-  fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
-                                                  n_frames, (int)T, run_clf);
+  // $SPANON_FCAE=1: the one-frame-per-thread kernel of round 1 (A/B switch); default: the 4-frame register-tile kernel
+  static const bool fcae_v1 = getenv("SPANON_FCAE") && getenv("SPANON_FCAE")[0] == '1';
+  if (fcae_v1)
+    fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                    n_frames, (int)T, run_clf);
+  else
+    fcae4_kernel<<<grid, NTHR, sizeof(Fc4Smem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                      n_frames, (int)T, run_clf);
   SPANON_TRY(check_launch("fcae_kernel"));
   if (run_clf) {
     fcae_head_kernel<<<(unsigned)B, 64, 0, st>>>(pool, pool_noise, *w, (int)T, logp);
@@ -400,15 +636,23 @@ extern "C" int spanon_fcae_fwd_static(const float* feats, const SpanonFcaeWeight
     pool = static_cast<double*>(sym);
     g_fcae_static_ptr[dev].store(pool, std::memory_order_release);
   }
-  if (first_use_on_device(g_fcae_static_attr, dev))
+  if (first_use_on_device(g_fcae_static_attr, dev)) {
     SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FcSmem)));
+    SPANON_CUDA_TRY(cudaFuncSetAttribute(fcae4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Fc4Smem)));
+  }
   // the array holds whatever the previous call left: the accumulators of this batch must start at zero
   if (run_clf) SPANON_CUDA_TRY(cudaMemsetAsync(pool, 0, (size_t)B * 40 * 2 * sizeof(double), st));
   const int64_t n_frames = B * T;
   const int64_t n_tiles = ceil_div(n_frames, NTHR);
   const unsigned grid = (unsigned)std::min<int64_t>(n_tiles, n_sm);
-  fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
-                                                  n_frames, (int)T, run_clf);
+  // $SPANON_FCAE=1: the one-frame-per-thread kernel of round 1 (A/B switch); default: the 4-frame register-tile kernel
+  static const bool fcae_v1 = getenv("SPANON_FCAE") && getenv("SPANON_FCAE")[0] == '1';
+  if (fcae_v1)
+    fcae_kernel<<<grid, NTHR, sizeof(FcSmem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                    n_frames, (int)T, run_clf);
+  else
+    fcae4_kernel<<<grid, NTHR, sizeof(Fc4Smem), st>>>(feats, *w, norm_mean, norm_std, utt_max, top_db, recon, pool,
+                                                      n_frames, (int)T, run_clf);
   SPANON_TRY(check_launch_static("fcae_kernel"));
   if (run_clf) {
     fcae_head_kernel<<<(unsigned)B, 64, 0, st>>>(pool, pool_noise, *w, (int)T, logp);
