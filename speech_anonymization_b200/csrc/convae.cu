@@ -506,23 +506,26 @@ __device__ __forceinline__ float bn_eval(float x, const SpanonBatchNorm& bn, int
   return (x - bn.running_mean[c]) / sqrtf(bn.running_var[c] + 1e-5f) * bn.weight[c] + bn.bias[c];
 }
 
-// classify: Linear(256,128) ReLU BN | Linear(128,64) ReLU BN | Linear(64,2) | log_softmax.  grid = B, block = 128
-__global__ void __launch_bounds__(128)
+// classify: Linear(256,128) ReLU BN | Linear(128,64) ReLU BN | Linear(64,2) | log_softmax.  grid = B, block = 256
+__global__ void __launch_bounds__(256)
 clf_head_kernel(const double* pool, const float* __restrict__ noise, int64_t n /*L3*/,
                 SpanonConvAEWeights w, float* __restrict__ logp, const unsigned* err_flag) {
+  // 256 threads: eight warps share the output rows (a warp per row, the lanes read 128 contiguous bytes of the weight row per
+  // step, sixteen rows' loads in flight per warp).  The 160 KB of weights are cold in L2 every step (5.5 GB of planes pass
+  // between two calls), so the launch is one DRAM-latency chain per batch of rows: a thread per row (round 1) took 36 us,
+  // four warps 26 us.
   __shared__ float s0[256], s1[128], s2[64], s3[2];
-  const int b = blockIdx.x, tid = threadIdx.x;
+  const int b = blockIdx.x, tid = threadIdx.x, t128 = tid & 127, t64 = tid & 63;
   pdl_launch_dependents();      // (common.cuh: launched as a programmatic dependent of tdnn.6 / the pooling pass)
-  // (bias / BatchNorm parameters of row tid are fetched up front, before the wait for the producer)
-  const float b0 = w.cls_b[0][tid], g0 = w.cls_bn[0].weight[tid], be0 = w.cls_bn[0].bias[tid], m0 = w.cls_bn[0].running_mean[tid],
-              v0 = w.cls_bn[0].running_var[tid];
-  const int t64 = tid & 63;
+  // (bias / BatchNorm parameters are fetched up front, before the wait for the producer)
+  const float b0 = w.cls_b[0][t128], g0 = w.cls_bn[0].weight[t128], be0 = w.cls_bn[0].bias[t128],
+              m0 = w.cls_bn[0].running_mean[t128], v0 = w.cls_bn[0].running_var[t128];
   const float b1 = w.cls_b[1][t64], g1 = w.cls_bn[1].weight[t64], be1 = w.cls_bn[1].bias[t64], m1 = w.cls_bn[1].running_mean[t64],
               v1 = w.cls_bn[1].running_var[t64];
   pdl_wait();
   pool = pdl_acquire(pool);     // (produced by the predecessor: see common.cuh)
   err_flag = pdl_acquire(err_flag);
-  {
+  if (tid < 128) {
     const double s = pool[((int64_t)b * 128 + tid) * 2 + 0], q = pool[((int64_t)b * 128 + tid) * 2 + 1];
     const double mean = s / (double)n;
     double var = n > 1 ? (q - s * s / (double)n) / (double)(n - 1) : (double)NAN;
@@ -531,11 +534,9 @@ clf_head_kernel(const double* pool, const float* __restrict__ noise, int64_t n /
     s0[128 + tid] = (float)sqrt(var) + 1e-5f;
   }
   __syncthreads();
-  // a warp per output row: the lanes read 128 contiguous bytes of the weight row per step (a thread per row read its own
-  // 1 KB row sequentially -- 128 uncoalesced streams and one 256-long dependent chain: 36 us for this 60-CTA launch)
   const int lane = tid & 31, warp = tid >> 5;
-#pragma unroll 4
-  for (int j = warp; j < 128; j += 4) {
+#pragma unroll 16
+  for (int j = warp; j < 128; j += 8) {
     const float* wr = w.cls_w[0] + j * 256 + lane;
     float a = 0.f;
 #pragma unroll
@@ -544,10 +545,10 @@ clf_head_kernel(const double* pool, const float* __restrict__ noise, int64_t n /
     if (lane == 0) s1[j] = a;
   }
   __syncthreads();
-  s1[tid] = (fmaxf(s1[tid] + b0, 0.f) - m0) / sqrtf(v0 + 1e-5f) * g0 + be0;
+  if (tid < 128) s1[tid] = (fmaxf(s1[tid] + b0, 0.f) - m0) / sqrtf(v0 + 1e-5f) * g0 + be0;
   __syncthreads();
-#pragma unroll 4
-  for (int j = warp; j < 64; j += 4) {
+#pragma unroll 8
+  for (int j = warp; j < 64; j += 8) {
     const float* wr = w.cls_w[1] + j * 128 + lane;
     float a = 0.f;
 #pragma unroll
@@ -558,11 +559,9 @@ clf_head_kernel(const double* pool, const float* __restrict__ noise, int64_t n /
   __syncthreads();
   if (tid < 64) s2[tid] = (fmaxf(s2[tid] + b1, 0.f) - m1) / sqrtf(v1 + 1e-5f) * g1 + be1;
   __syncthreads();
-  if (tid < 2) {
-    float a = w.cls_b[2][tid];
-    const float* wr = w.cls_w[2] + tid * 64;
-    for (int i = 0; i < 64; ++i) a = fmaf(s2[i], __ldg(wr + i), a);
-    s3[tid] = a;
+  if (warp < 2) {
+    const float a = warp_sum(fmaf(s2[lane], __ldg(w.cls_w[2] + warp * 64 + lane), s2[lane + 32] * __ldg(w.cls_w[2] + warp * 64 + lane + 32)));
+    if (lane == 0) s3[warp] = a + w.cls_b[2][warp];
   }
   __syncthreads();
   if (tid < 2) {
@@ -1134,7 +1133,7 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
         pool_kernel<<<pg, 256, 0, c.st>>>(c.ws.tdnn_out, n_el, n_el, c.ws.pool);
         SPANON_TRY(check_launch("pool_kernel"));
       }
-      SPANON_CUDA_TRY(launch_pdl(clf_head_kernel, dim3((unsigned)nb), dim3(128), 0, c.st, true, (const double*)c.ws.pool,
+      SPANON_CUDA_TRY(launch_pdl(clf_head_kernel, dim3((unsigned)nb), dim3(256), 0, c.st, true, (const double*)c.ws.pool,
                                  pool_noise ? pool_noise + b0 * 128 : (const float*)nullptr, L3, *w, logp + b0 * 2,
                                  (const unsigned*)(c.ws.counter + 1)));
       SPANON_TRY(check_launch("clf_head_kernel"));
