@@ -652,10 +652,10 @@ struct LayerSpec {
   int rows_shrink;          // rows_out = rows_in - rows_shrink (TDNN, no padding)
 };
 
-enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, L_DEC45, N_LAYERS };
+enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, L_DEC45, L_ENC5P, N_LAYERS };
 const char* const kLayerTag[N_LAYERS] = {"tapgemm:enc2", "tapgemm:enc5", "tapgemm:enc8", "tapgemm:enc11", "tapgemm:tdnn0", "tapgemm:tdnn3",
                                         "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8",
-                                        "tapgemm:dec45"};
+                                        "tapgemm:dec45", "tapgemm:enc5"};
 
 // tc = this layer runs on the tcgen05 kernel (fp16 UMMA-packed weights)
 LayerSpec make_spec(int id, bool tc) {
@@ -664,6 +664,10 @@ LayerSpec make_spec(int id, bool tc) {
   switch (id) {
     case L_ENC2:  s = {PACK_CONV_S2, 32, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-1, 0, 1}); break;
     case L_ENC5:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
+    // encoder.5 on ROW PAIRS (tcgen05 path): 64 -> 64 channels, k5 becomes a 3-tap 128 -> 128 layer over L/4 pair rows (10 of
+    // the 12 64x64 blocks non-zero: 20 % more MMA work, but 128 columns per tile instead of 64 -- the N=64 form is bound by
+    // the A-operand fetch).  Its input is encoder.2's output pair-folded, its 128 output columns ARE encoder.8's pair view.
+    case L_ENC5P: s = {PACK_CONV_S1_PAIR, 64, 64, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
     case L_ENC8:  s = {PACK_CONV_S2, 64, 128, 5, 128, 128, 0, {}, 4, 0}; taps({-1, 0, 1}); break;
     case L_ENC11: s = {PACK_CONV_S1, 128, 128, 5, 128, 128, 0, {}, 4, 0}; taps({-2, -1, 0, 1, 2}); break;
     case L_TD0:   s = {PACK_CONV_S1, 128, 128, 5, 128, 128, 0, {}, 4, 4}; taps({0, 1, 2, 3, 4}); break;
@@ -751,6 +755,7 @@ struct Ctx {
   int n_sm;
   int64_t L;
   cudaStream_t st;
+  bool enc5_pair = false;  // encoder.5 as a 128 -> 128 layer on row pairs (L_ENC5P; tcgen05 path, $SPANON_ENC5_PAIR=0: N=64 form)
   bool prepared = false;   // weights_prepared call: no weight-preparation kernel runs ahead of the first layer
 };
 
@@ -970,10 +975,12 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     SPANON_CUDA_TRY(cudaDeviceGetAttribute(&c.n_sm, cudaDevAttrMultiProcessorCount, dev));
   }
   // ---- per-call weight preparation (weights may have changed since the last call) ----
+  static const bool enc5_pair_env = !(getenv("SPANON_ENC5_PAIR") && getenv("SPANON_ENC5_PAIR")[0] == '0');
+  c.enc5_pair = c.tc && enc5_pair_env;
   c.prepared = opts && opts->weights_prepared;
   if (!c.prepared) {
   SPANON_TRY(pack_layer(c, L_ENC2, w->enc_w[1]));
-  SPANON_TRY(pack_layer(c, L_ENC5, w->enc_w[2]));
+  SPANON_TRY(pack_layer(c, c.enc5_pair ? L_ENC5P : L_ENC5, w->enc_w[2]));
   SPANON_TRY(pack_layer(c, L_ENC8, w->enc_w[3]));
   SPANON_TRY(pack_layer(c, L_ENC11, w->enc_w[4]));
   SPANON_TRY(pack_layer(c, L_DEC0, w->dec_w[0]));
@@ -1048,9 +1055,14 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
     {
       LayerIO e2{X[0], X[1], -1, -1, nb_(w->enc_b[1]), 0, -1, 0, OUT_CHANNELS_LAST, w->enc_in_w[0], w->enc_in_b[0], (double)L2};
       if (fuse_enc0) e2.gen = &gen;
+      if (c.enc5_pair) e2.out_fold = OUT_PAIR_FOLD;      // encoder.5 reads row pairs
       SPANON_TRY(run_layer(c, L_ENC2, e2, nb));
     }
     SPANON_TRY(finalize_in(c, L_ENC2, 0, w->enc_in_w[0], w->enc_in_b[0], nb, (double)L2));
+    if (c.enc5_pair)
+      SPANON_TRY(run_layer(c, L_ENC5P, {X[1], X[2], 0, -1, nullptr, 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
+                                        OUT_DIRECT}, nb));
+    else
     SPANON_TRY(run_layer(c, L_ENC5, {X[1], X[2], 0, -1, nb_(w->enc_b[2]), 0, -1, 1, OUT_CHANNELS_LAST, w->enc_in_w[1], w->enc_in_b[1], (double)L2,
                                      OUT_PAIR_FOLD}, nb));
     SPANON_TRY(finalize_in(c, L_ENC5, 1, w->enc_in_w[1], w->enc_in_b[1], nb, (double)L2));
