@@ -634,15 +634,17 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
     // stored, its column sums over the warp's 32 rows leave lane l with the sum (and the sum of squares) of column
     // cb + 2*(l & 15) + (l >> 4); they stay in registers until the utterance changes.
     constexpr bool e_stats = (XF & XF_STATS) != 0;
-    float es[4] = {0.f, 0.f, 0.f, 0.f}, eq[4] = {0.f, 0.f, 0.f, 0.f};
+    // (fp64: the partial sums run over however many tiles of the utterance THIS CTA happens to own -- with fp32 the statistics,
+    //  and through the fp16-rounded affine of the consumer every output, depended on the batch an utterance was in at 1e-3)
+    double es[4] = {0.0, 0.0, 0.0, 0.0}, eq[4] = {0.0, 0.0, 0.0, 0.0};
     auto e_flush = [&](int bb) {
 #pragma unroll
       for (int i = 0; i < CPW / 32; ++i) {
         const int ch = (chalf * CPW + 32 * i + 2 * (lane & 15) + (lane >> 4)) % p.cout_mod;
         double* dst = p.stats + ((int64_t)bb * p.cout_mod + ch) * 2;
-        atomicAdd(dst, (double)es[i]);
-        atomicAdd(dst + 1, (double)eq[i]);
-        es[i] = 0.f; eq[i] = 0.f;
+        atomicAdd(dst, es[i]);
+        atomicAdd(dst + 1, eq[i]);
+        es[i] = 0.0; eq[i] = 0.0;
       }
     };
     int b_prev = -1, b = 0, tin = 0;
@@ -732,7 +734,7 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
           const int cbi = (cb - chalf * CPW) >> 5;
 #pragma unroll
           for (int i = 0; i < CPW / 32; ++i)
-            if (i == cbi) { es[i] += bs; eq[i] += bq; }
+            if (i == cbi) { es[i] += (double)bs; eq[i] += (double)bq; }
         }
       }
       if (p.trace && threadIdx.x == 0 && 2 * k + 1 < TRACE_N) p.trace[((int64_t)blockIdx.x * 6 + 2) * TRACE_N + 2 * k + 1] = clock64();

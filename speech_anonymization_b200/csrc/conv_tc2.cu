@@ -474,15 +474,17 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
     constexpr int NCH = T2_N / 8, CPW = T2_N / (E / 4);
     // InstanceNorm statistics of the output (X2_STATS), as in conv_tc.cu: column sums over the warp's 32 rows of the values
     // AS STORED through a padded shared-memory transpose; lane l keeps column cb + 2*(l & 15) + (l >> 4) of each 32-column block
-    float es[4] = {0.f, 0.f, 0.f, 0.f}, eq[4] = {0.f, 0.f, 0.f, 0.f};
+    // (fp64: the partial sums run over however many tiles of the utterance THIS CTA happens to own -- with fp32 the statistics,
+    //  and through the fp16-rounded affine of the consumer every output, depended on the batch an utterance was in at 1e-3)
+    double es[4] = {0.0, 0.0, 0.0, 0.0}, eq[4] = {0.0, 0.0, 0.0, 0.0};
     auto e_flush = [&](int bb) {
 #pragma unroll
       for (int i = 0; i < CPW / 32; ++i) {
         const int ch = (chalf * CPW + 32 * i + 2 * (lane & 15) + (lane >> 4)) % p.cout_mod;
         double* dst = p.stats + ((int64_t)bb * p.cout_mod + ch) * 2;
-        atomicAdd(dst, (double)es[i]);
-        atomicAdd(dst + 1, (double)eq[i]);
-        es[i] = 0.f; eq[i] = 0.f;
+        atomicAdd(dst, es[i]);
+        atomicAdd(dst + 1, eq[i]);
+        es[i] = 0.0; eq[i] = 0.0;
       }
     };
     int b_prev = -1;
@@ -553,7 +555,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
           const int cbi = (cb - chalf * CPW) >> 5;
 #pragma unroll
           for (int i = 0; i < CPW / 32; ++i)
-            if (i == cbi) { es[i] += bs; eq[i] += bq; }
+            if (i == cbi) { es[i] += (double)bs; eq[i] += (double)bq; }
         }
       }
     }
