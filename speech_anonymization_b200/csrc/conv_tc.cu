@@ -706,6 +706,7 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
               int pl, row;       // destination plane / row in the consumer's view
               if (p.out_fold == OUT_PAIR_FOLD) { pl = (m & 1) * NCH + c8; row = m >> 1; }
               else if (p.out_fold == OUT_PHASE_UNFOLD) { pl = c8 % (NCH / 2); row = 2 * m + c8 / (NCH / 2); }
+              else if (p.out_fold == OUT_PHASE_UNFOLD4) { pl = c8 % (NCH / 4); row = 4 * m + c8 / (NCH / 4); }
               else { pl = c8; row = m; }
               *reinterpret_cast<uint4*>(out_h + (((int64_t)pl * p.out_plane_rows + row) << 3)) = o;
             }

@@ -172,7 +172,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
   if (warp < E) {
     float* ec = reinterpret_cast<float*>(smem + L.epi);
     for (int c = threadIdx.x; c < T2_N; c += E * 32) {
-      ec[c] = p.bias ? p.bias[c % p.cout_mod] : 0.f;
+      ec[c] = p.bias ? p.bias[p.bias_v ? c : c % p.cout_mod] : 0.f;
       if constexpr ((XF & X2_POOL) != 0) { ec[T2_N + c] = p.e_scale[c]; ec[2 * T2_N + c] = p.e_shift[c]; }
     }
   }
@@ -531,6 +531,7 @@ tapgemm_tc2_kernel(const __grid_constant__ TapGemmParams p, int halo_lo, int sla
             if constexpr (e_stats) {
               if (p.out_fold == OUT_PAIR_FOLD) { pl = (m & 1) * NCH + c8; row = m >> 1; }
               else if (p.out_fold == OUT_PHASE_UNFOLD) { pl = c8 % (NCH / 2); row = 2 * m + c8 / (NCH / 2); }
+              else if (p.out_fold == OUT_PHASE_UNFOLD4) { pl = c8 % (NCH / 4); row = 4 * m + c8 / (NCH / 4); }
             }
             *reinterpret_cast<uint4*>(out_h + (((int64_t)pl * p.out_plane_rows + row) << 3)) = o;
           }
@@ -604,11 +605,13 @@ static int tc2_xf(const TapGemmParams& p) {
 bool tapgemm_tc2_supported(const TapGemmParams& p) {
   if (!tapgemm_tc_supported(p)) return false;
   if (p.cin_v != 128 || p.cout_v != 128 || p.gen_feats) return false;
-  if (p.bias_v || p.flag_in || p.flag_out) return false;
+  if (p.flag_in || p.flag_out) return false;
   if (p.pool) {         // tdnn.6 with the pooling sums in its epilogue: ReLU -> BatchNorm affine, no stored output
     if (!p.relu || !p.e_scale || !p.e_shift || p.stats || p.cout_mod != 128 || (p.rows_out & 1)) return false;
   } else if (p.relu || p.e_scale) return false;
-  if (p.stats && p.cout_mod != 128 && p.cout_mod != 64) return false;
+  if (p.stats && (p.cout_mod < 32 || 128 % p.cout_mod != 0)) return false;
+  static const bool unfold4_env = !(getenv("SPANON_TC2_UNFOLD4") && getenv("SPANON_TC2_UNFOLD4")[0] == '0');
+  if (p.out_fold == OUT_PHASE_UNFOLD4 && !unfold4_env) return false;
   if (!p.stats && (p.cout_mod != 128 || p.out_fold != OUT_DIRECT)) return false;
   // measured per layer (same-box A/B): the pair kernel wins on the k5 layers (tdnn.0 -21, decoder.0 -20, encoder.11 -14 us)
   // and on tdnn.3 / tdnn.6 (-5 us); the 3-tap layers that also reduce statistics (encoder.8, decoder.1) are HBM- and

@@ -82,12 +82,41 @@ __global__ void compose_dec45_kernel(const float* __restrict__ w4, const float* 
   }
 }
 
-// bc[ph*C2 + c2] = b5[c2] + sum_c1 b4[c1] * sum_{t = ph (mod 2)} W5[c1][c2][t]
+// The same composition on ROW PAIRS of the input (L_DEC45P): view row m = input rows (2m, 2m+1) -> 128 input channels
+// (q, c0); the four output rows 4m .. 4m+3 = (input row s, phase ph) -> 128 columns (2s + ph, c2); pair tap p = -2 .. 2 holds
+// Wc[ph][u = 2p + q - s] (zero for |u| > 3).  fp16 UMMA layout [5][128/8][128][8].
+__global__ void compose_dec45_pair_kernel(const float* __restrict__ w4, const float* __restrict__ w5, __half* __restrict__ dst,
+                                          int C0, int C1, int C2) {
+  const int cin_v = 2 * C0, cout_v = 4 * C2;
+  const int64_t n = (int64_t)5 * cin_v * cout_v;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i % 8);
+    const int cov = (int)((i / 8) % cout_v);
+    const int kc = (int)((i / (8 * (int64_t)cout_v)) % (cin_v / 8));
+    const int p = (int)(i / ((int64_t)cout_v * cin_v)) - 2;
+    const int civ = kc * 8 + e, q = civ / C0, c0 = civ - q * C0;
+    const int sp = cov / C2, c2 = cov - sp * C2, sr = sp >> 1, ph = sp & 1;
+    const int u = 2 * p + q - sr;
+    float acc = 0.f;
+    if (u >= -3 && u <= 3) {
+      for (int d = -1; d <= 1; ++d) {
+        const int sft = u - d, t = 2 - 2 * d + ph;
+        if (sft < -2 || sft > 2 || t > 4) continue;
+        for (int c1 = 0; c1 < C1; ++c1)
+          acc = fmaf(__ldg(w4 + ((int64_t)c1 * C0 + c0) * 5 + sft + 2), __ldg(w5 + ((int64_t)c1 * C2 + c2) * 5 + t), acc);
+      }
+    }
+    dst[i] = __float2half_rn(acc);
+  }
+}
+
+// bc[cov] = b5[c2] + sum_c1 b4[c1] * sum_{t = ph (mod 2)} W5[c1][c2][t],  ph = (cov / C2) & 1, c2 = cov % C2
+// (n_cols = 2*C2 for the row view, 4*C2 for the pair view: the two input rows of a pair share the constants)
 __global__ void compose_dec45_bias_kernel(const float* __restrict__ b4, const float* __restrict__ w5,
-                                          const float* __restrict__ b5, float* __restrict__ bc, int C1, int C2) {
+                                          const float* __restrict__ b5, float* __restrict__ bc, int C1, int C2, int n_cols) {
   const int cov = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cov >= 2 * C2) return;
-  const int ph = cov / C2, c2 = cov - ph * C2;
+  if (cov >= n_cols) return;
+  const int ph = (cov / C2) & 1, c2 = cov % C2;
   float acc = b5[c2];
   for (int c1 = 0; c1 < C1; ++c1) {
     float ws = 0.f;
@@ -125,14 +154,16 @@ __global__ void compose_dec45_edge_kernel(const float* __restrict__ w4, const fl
 // fp16 of the composed layer's input, scale/shift: its InstanceNorm affine [utt][64]; y: planes [utt][4][2*L2][8] fp16.
 __global__ void __launch_bounds__(384)
 dec45_edge_kernel(const __half* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                  const float* __restrict__ E, __half* __restrict__ y, int L2, double* __restrict__ stats) {
+                  const float* __restrict__ E, __half* __restrict__ y, int L2, double* __restrict__ stats, int folded) {
   constexpr int C0 = 64, C2 = 32;
   __shared__ float xs[4][C0], part[3][4][C2];
   const int b = blockIdx.x, tid = threadIdx.x;
   if (tid < 4 * C0) {   // rows 0, 1, L2-2, L2-1 of the activated input
     const int r = tid / C0, c = tid % C0;
     const int row = r < 2 ? r : L2 - 4 + r;
-    const float v = __half2float(x[(((int64_t)b * (C0 / 8) + c / 8) * L2 + row) * 8 + (c & 7)]);
+    // (folded: the input planes are the pair view [utt][16][L2/2][8], plane (row & 1) * 8 + c / 8, row >> 1)
+    const float v = folded ? __half2float(x[(((int64_t)b * (C0 / 4) + (row & 1) * (C0 / 8) + c / 8) * (L2 / 2) + (row >> 1)) * 8 + (c & 7)])
+                           : __half2float(x[(((int64_t)b * (C0 / 8) + c / 8) * L2 + row) * 8 + (c & 7)]);
     xs[r][c] = silu_fast(fmaf(v, scale[(int64_t)b * C0 + c], shift[(int64_t)b * C0 + c]));
   }
   __syncthreads();
@@ -652,10 +683,10 @@ struct LayerSpec {
   int rows_shrink;          // rows_out = rows_in - rows_shrink (TDNN, no padding)
 };
 
-enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, L_DEC45, L_ENC5P, N_LAYERS };
+enum LayerId { L_ENC2, L_ENC5, L_ENC8, L_ENC11, L_TD0, L_TD3, L_TD6, L_DEC0, L_DEC1, L_DEC4, L_DEC5, L_DEC8, L_DEC45, L_ENC5P, L_DEC45P, N_LAYERS };
 const char* const kLayerTag[N_LAYERS] = {"tapgemm:enc2", "tapgemm:enc5", "tapgemm:enc8", "tapgemm:enc11", "tapgemm:tdnn0", "tapgemm:tdnn3",
                                         "tapgemm:tdnn6", "tapgemm:dec0", "tapgemm:dec1", "tapgemm:dec4", "tapgemm:dec5", "tapgemm:dec8",
-                                        "tapgemm:dec45", "tapgemm:enc5"};
+                                        "tapgemm:dec45", "tapgemm:enc5", "tapgemm:dec45"};
 
 // tc = this layer runs on the tcgen05 kernel (fp16 UMMA-packed weights)
 LayerSpec make_spec(int id, bool tc) {
@@ -678,6 +709,8 @@ LayerSpec make_spec(int id, bool tc) {
     case L_DEC4:  s = {PACK_CONV_S1, 64, 64, 5, 64, 64, 0, {}, 2, 0};    taps({-2, -1, 0, 1, 2}); break;
     case L_DEC5:  s = {PACK_CONVT_S2, 64, 32, 5, 64, 64, 0, {}, 2, 0};   taps({-1, 0, 1}); break;
     case L_DEC45: s = {PACK_COMPOSED, 64, 32, 7, 64, 64, 0, {}, 2, 0};   taps({-3, -2, -1, 0, 1, 2, 3}); break;
+    // the composed layer on ROW PAIRS (compose_dec45_pair_kernel): 5 pair taps, 128 -> 128 columns over L/4 pair rows
+    case L_DEC45P: s = {PACK_COMPOSED, 64, 32, 7, 128, 128, 0, {}, 4, 0}; taps({-2, -1, 0, 1, 2}); break;
     case L_DEC8:
       if (tc) { s = {PACK_TOEPLITZ, 32, 1, 15, 32, 16, 0, {}, 1, 0}; taps({-7}); }   // Toeplitz GEMM, see conv_tc.cu
       else { s = {PACK_CONV_S1, 32, 1, 15, 32, 4, 0, {}, 1, 0}; taps({-7, -6, -5, -4, -3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7}); }
@@ -693,7 +726,7 @@ struct Workspace {
   void* packed[N_LAYERS];
   float* bn_scale[4]; float* bn_shift[4];      // clf norm, tdnn bn 0..2
   float* ones;                                 // [128] 1.0f (unit scale of a bias-only affine on load)
-  float* bias45;                               // [64] per-column bias of the composed decoder.4 o decoder.5 layer
+  float* bias45;                               // [64 | 128] per-column bias of the composed decoder.4 o decoder.5 layer
   float* edge45;                               // [EDGE45_FLOATS] its edge-correction matrices (dec45_edge_kernel)
   double* stats[6];                            // enc3, enc6, enc9, enc12, dec2, dec6   [chunk][C][2]
   float* in_scale[6]; float* in_shift[6];      // [chunk][C]
@@ -730,7 +763,7 @@ void carve(Workspace& ws, char* base, int64_t chunk, int64_t L, bool tc, size_t 
   }
   for (int i = 0; i < 4; ++i) { ws.bn_scale[i] = (float*)take(128 * 4); ws.bn_shift[i] = (float*)take(128 * 4); }
   ws.ones = (float*)take(128 * 4);
-  ws.bias45 = (float*)take(64 * 4);
+  ws.bias45 = (float*)take(128 * 4);
   ws.edge45 = (float*)take(EDGE45_FLOATS * 4);
   // stats, pool and flags are contiguous so one memset clears them
   const size_t stats_off = off;
@@ -755,6 +788,7 @@ struct Ctx {
   int n_sm;
   int64_t L;
   cudaStream_t st;
+  bool dec45_pair = false; // decoder.4 o decoder.5 as a 5-tap 128 -> 128 layer on row pairs (L_DEC45P; opt-in with $SPANON_DEC45_PAIR=1)
   bool enc5_pair = false;  // encoder.5 as a 128 -> 128 layer on row pairs (L_ENC5P; tcgen05 path, $SPANON_ENC5_PAIR=0: N=64 form)
   bool prepared = false;   // weights_prepared call: no weight-preparation kernel runs ahead of the first layer
 };
@@ -822,7 +856,7 @@ TapGemmParams make_params(const Ctx& c, int id, const LayerIO& io, int nb) {
   }
   p.tap_step = s.ntaps > 1 ? s.shift[1] - s.shift[0] : 0;
   if (s.mode == PACK_CONV_S2) p.tap_kmax[s.ntaps - 1] = s.cin;   // tap (2*tap+1) = 5 does not exist
-  if (s.mode == PACK_CONVT_S2 || s.mode == PACK_COMPOSED) p.tap_nmax[0] = s.cout;   // the first shift only feeds the even phase
+  if ((s.mode == PACK_CONVT_S2 || s.mode == PACK_COMPOSED) && id != L_DEC45P) p.tap_nmax[0] = s.cout;   // the first shift only feeds the even phase
   p.w = c.ws.packed[id];
   p.t1_bstride = s.cin;
   if (io.in_norm >= 0) { p.t1_scale = c.ws.in_scale[io.in_norm]; p.t1_shift = c.ws.in_shift[io.in_norm]; p.silu = 1; }
@@ -830,13 +864,14 @@ TapGemmParams make_params(const Ctx& c, int id, const LayerIO& io, int nb) {
   if (io.act >= 0) p.silu = io.act;
   if (io.t2_bn >= 0) { p.t2_scale = c.ws.bn_scale[io.t2_bn]; p.t2_shift = c.ws.bn_shift[io.t2_bn]; }
   p.bias = io.bias;
-  p.bias_v = id == L_DEC45 ? 1 : 0;
+  p.bias_v = (id == L_DEC45 || id == L_DEC45P) ? 1 : 0;
   p.relu = io.relu;
   if (io.e_bn >= 0) { p.e_scale = c.ws.bn_scale[io.e_bn]; p.e_shift = c.ws.bn_shift[io.e_bn]; }
   p.stats = io.out_stats >= 0 ? c.ws.stats[io.out_stats] : nullptr;
   p.out_mode = io.out_mode;
   p.out_fold = io.out_fold;
-  p.out_plane_rows = io.out_fold == OUT_PAIR_FOLD ? p.rows_out / 2 : io.out_fold == OUT_PHASE_UNFOLD ? p.rows_out * 2 : p.rows_out;
+  p.out_plane_rows = io.out_fold == OUT_PAIR_FOLD ? p.rows_out / 2 : io.out_fold == OUT_PHASE_UNFOLD ? p.rows_out * 2
+                     : io.out_fold == OUT_PHASE_UNFOLD4 ? p.rows_out * 4 : p.rows_out;
   p.in_planar = c.tc ? 1 : 0;
   p.out_half = io.out_half;
   if (io.gen) {
@@ -877,13 +912,16 @@ int run_layer(const Ctx& c, int id, const LayerIO& io, int nb) {
     if (tc2_env && tapgemm_tc2_supported(p)) SPANON_TRY(launch_tapgemm_tc2(p, c.n_sm, c.st));
     else
     SPANON_TRY(launch_tapgemm_tc(p, c.n_sm, c.st));
-    if (id == L_DEC45) {   // take the two rows of decoder.4 the reference does not have back out (before the statistics)
+    if (id == L_DEC45 || id == L_DEC45P) {   // take the two rows of decoder.4 the reference does not have back out (before the statistics)
+      const int folded = id == L_DEC45P;
       dec45_edge_kernel<<<(unsigned)nb, 384, 0, c.st>>>((const __half*)io.in, p.t1_scale, p.t1_shift, c.ws.edge45,
-                                                        (__half*)io.out, p.rows_in, fuse ? c.ws.stats[io.out_stats] : nullptr);
+                                                        (__half*)io.out, folded ? 2 * p.rows_in : p.rows_in,
+                                                        fuse ? c.ws.stats[io.out_stats] : nullptr, folded);
       SPANON_TRY(check_launch("dec45_edge_kernel"));
     }
     if (split_stats) {   // one bandwidth-bound pass over the fp16 plane just written (cheaper than reducing in the epilogue)
-      const int P = p.out_fold == OUT_PAIR_FOLD ? s.cout_v / 4 : p.out_fold == OUT_PHASE_UNFOLD ? s.cout_v / 16 : s.cout_v / 8;
+      const int P = p.out_fold == OUT_PAIR_FOLD ? s.cout_v / 4 : p.out_fold == OUT_PHASE_UNFOLD ? s.cout_v / 16
+                    : p.out_fold == OUT_PHASE_UNFOLD4 ? s.cout_v / 32 : s.cout_v / 8;
       dim3 grid((unsigned)ceil_div(p.out_plane_rows, ST_NT * ST_ROWS), (unsigned)P, (unsigned)nb);
       instnorm_stats_kernel<<<grid, ST_NT, 0, c.st>>>((const __half*)io.out, P, p.out_plane_rows, s.cout,
                                                       c.ws.stats[io.out_stats]);
@@ -977,6 +1015,9 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   // ---- per-call weight preparation (weights may have changed since the last call) ----
   static const bool enc5_pair_env = !(getenv("SPANON_ENC5_PAIR") && getenv("SPANON_ENC5_PAIR")[0] == '0');
   c.enc5_pair = c.tc && enc5_pair_env;
+  // (opt-in: measured 225 - 235 us against 213 us for the 7-tap N=64 form -- 43 % more MMA work outweighs the wider tile)
+  static const bool dec45_pair_env = getenv("SPANON_DEC45_PAIR") && getenv("SPANON_DEC45_PAIR")[0] == '1';
+  c.dec45_pair = c.tc && dec45_pair_env && compose_dec45(c);
   c.prepared = opts && opts->weights_prepared;
   if (!c.prepared) {
   SPANON_TRY(pack_layer(c, L_ENC2, w->enc_w[1]));
@@ -986,9 +1027,13 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
   SPANON_TRY(pack_layer(c, L_DEC0, w->dec_w[0]));
   SPANON_TRY(pack_layer(c, L_DEC1, w->dec_w[1]));
   if (compose_dec45(c)) {
-    compose_dec45_kernel<<<112, 256, 0, c.st>>>(w->dec_w[2], w->dec_w[3], (__half*)c.ws.packed[L_DEC45], 64, 64, 32);
+    if (c.dec45_pair)
+      compose_dec45_pair_kernel<<<160, 256, 0, c.st>>>(w->dec_w[2], w->dec_w[3], (__half*)c.ws.packed[L_DEC45P], 64, 64, 32);
+    else
+      compose_dec45_kernel<<<112, 256, 0, c.st>>>(w->dec_w[2], w->dec_w[3], (__half*)c.ws.packed[L_DEC45], 64, 64, 32);
     SPANON_TRY(check_launch("compose_dec45_kernel"));
-    compose_dec45_bias_kernel<<<1, 64, 0, c.st>>>(w->dec_b[2], w->dec_w[3], w->dec_b[3], c.ws.bias45, 64, 32);
+    compose_dec45_bias_kernel<<<1, 128, 0, c.st>>>(w->dec_b[2], w->dec_w[3], w->dec_b[3], c.ws.bias45, 64, 32,
+                                                   c.dec45_pair ? 128 : 64);
     SPANON_TRY(check_launch("compose_dec45_bias_kernel"));
     compose_dec45_edge_kernel<<<(unsigned)ceil_div(EDGE45_FLOATS, 256), 256, 0, c.st>>>(w->dec_w[2], w->dec_b[2], w->dec_w[3],
                                                                                         c.ws.edge45, 64, 64, 32);
@@ -1151,10 +1196,14 @@ extern "C" int spanon_convae_fwd(const float* feats, const SpanonConvAEWeights* 
       SPANON_TRY(check_launch("clf_head_kernel"));
     }
     SPANON_TRY(run_layer(c, L_DEC0, {X[0], X[1], 3, -1, w->dec_b[0], 0, -1, -1, OUT_CHANNELS_LAST}, nb));
+    // (pair form of the composed layer: decoder.1's 128 columns [even | odd phase] ARE its input's pair view -- no unfold)
     SPANON_TRY(run_layer(c, L_DEC1, {X[1], X[2], -1, -1, nb_(w->dec_b[1]), 0, -1, 4, OUT_CHANNELS_LAST, w->dec_in_w[0], w->dec_in_b[0], (double)L2,
-                                     OUT_PHASE_UNFOLD}, nb));
+                                     c.dec45_pair ? OUT_DIRECT : OUT_PHASE_UNFOLD}, nb));
     SPANON_TRY(finalize_in(c, L_DEC1, 4, w->dec_in_w[0], w->dec_in_b[0], nb, (double)L2));
-    if (compose_dec45(c)) {   // decoder.4 o decoder.5 as one 7-tap phase-view layer (compose_dec45_kernel)
+    if (c.dec45_pair) {       // ... as one 5-tap 128 -> 128 layer on row pairs (compose_dec45_pair_kernel)
+      SPANON_TRY(run_layer(c, L_DEC45P, {X[2], X[3], 4, -1, c.ws.bias45, 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
+                                         OUT_PHASE_UNFOLD4}, nb));
+    } else if (compose_dec45(c)) {   // decoder.4 o decoder.5 as one 7-tap phase-view layer (compose_dec45_kernel)
       SPANON_TRY(run_layer(c, L_DEC45, {X[2], X[3], 4, -1, c.ws.bias45, 0, -1, 5, OUT_CHANNELS_LAST, w->dec_in_w[1], w->dec_in_b[1], (double)L,
                                         OUT_PHASE_UNFOLD}, nb));
     } else {

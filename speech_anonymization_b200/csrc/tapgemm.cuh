@@ -34,7 +34,8 @@ enum OutMode {
 enum OutFold {
   OUT_DIRECT = 0,        // plane c/8, row m
   OUT_PAIR_FOLD = 1,     // consumer views row pairs as one row of 2*C channels (stride-2 conv): plane (m&1)*C/8 + c/8, row m>>1
-  OUT_PHASE_UNFOLD = 2   // this layer is a transposed conv computing [even | odd] phases: plane (c % Cout)/8, row 2m + c/Cout
+  OUT_PHASE_UNFOLD = 2,  // this layer is a transposed conv computing [even | odd] phases: plane (c % Cout)/8, row 2m + c/Cout
+  OUT_PHASE_UNFOLD4 = 3  // the same on ROW PAIRS of the input (columns = [pair row s][phase][Cout]): plane (c % Cout)/8, row 4m + c/Cout
 };
 
 struct TapGemmParams {

@@ -1,5 +1,5 @@
 """The A/B switches keep the older kernel forms alive (SPANON_FBANK, SPANON_FCAE, SPANON_TC2, SPANON_POOL_FUSE, SPANON_PDL,
-SPANON_FUSE_ENC0, SPANON_COMPOSE_DEC, ring depths): every form must still meet the parity bars, or the measurements that
+SPANON_FUSE_ENC0, SPANON_COMPOSE_DEC, SPANON_ENC5_PAIR, SPANON_DEC45_PAIR, ring depths): every form must still meet the parity bars, or the measurements that
 compare them mean nothing.  The library reads the switches once per process, so each setting runs in its own process."""
 import json
 import os
@@ -18,6 +18,7 @@ SETTINGS = [
     {"SPANON_POOL_FUSE": "0"}, {"SPANON_PDL": "0"}, {"SPANON_TC2": "0"},
     {"SPANON_FUSE_ENC0": "0"}, {"SPANON_COMPOSE_DEC": "0"}, {"SPANON_FUSED_STATS": "0"},
     {"SPANON_T2_STAGES": "16", "SPANON_TC_STAGES": "32"}, {"SPANON_TC2_STATS3": "1"},
+    {"SPANON_ENC5_PAIR": "0"}, {"SPANON_DEC45_PAIR": "1"}, {"SPANON_DEC45_PAIR": "1", "SPANON_TC2_UNFOLD4": "0"},
 ]
 
 
