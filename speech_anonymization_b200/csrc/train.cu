@@ -337,6 +337,7 @@ norm_bwd_reduce_kernel(const float* __restrict__ z, const float* __restrict__ go
   const int64_t si = (int64_t)b * stat_bstride + c;
   const float mu = mean[si], rs = rstd[si], ga = gamma[c], be = beta[c];
   double s1 = 0.0, s2 = 0.0;
+#pragma unroll 4
   for (int64_t r = m_begin + rr; r < m_end; r += rstep) {
     const int64_t idx = ((int64_t)b * rows + r) * C + c;
     const float xh = (__ldg(z + idx) - mu) * rs;
@@ -416,6 +417,7 @@ colstats_kernel(const float* __restrict__ x, double* __restrict__ stats, int64_t
   const int tid = threadIdx.x, b = blockIdx.y, c = tid % C, rr = tid / C, rstep = 256 / C;
   const int64_t m_begin = (int64_t)blockIdx.x * rows_per_cta, m_end = min(rows, m_begin + rows_per_cta);
   double s = 0.0, q = 0.0;
+#pragma unroll 4
   for (int64_t r = m_begin + rr; r < m_end; r += rstep) {
     const double v = (double)__ldg(x + ((int64_t)b * rows + r) * C + c);
     s += v; q += v * v;
@@ -616,7 +618,13 @@ extern "C" int spanon_tapconv_bwd(const float* in, const float* w, const float* 
     SPANON_CUDA_TRY(cudaMemsetAsync(gwp, 0, (size_t)g.ntaps * g.cin_v * g.cout_v * 4, st));
     int lo = 0, hi = 0, sh[WG_MAXTAPS] = {0, 0, 0, 0, 0};
     for (int t = 0; t < g.ntaps; ++t) { sh[t] = g.shift[t]; lo = std::min(lo, sh[t]); hi = std::max(hi, sh[t]); }
-    const int rpc = 4096;
+    // rows per CTA: about two waves of the co-resident CTAs (two per SM), never a nearly empty last wave -- 4096 rows gave
+    // 160 CTAs on 148 SMs for every layer of the 8 x 10 s step, i.e. a second wave with 12 CTAs: half the throughput
+    // (walking the A slab once for all taps instead of once per tap was tried: fewer shared-memory loads, but slower)
+    const int64_t per_range = (int64_t)(g.cin_v / WG_KC) * B;
+    const int n_sm_w = std::max(1, current_device_sms());
+    const int64_t n_ranges = std::max<int64_t>(1, std::min<int64_t>((4 * (int64_t)n_sm_w) / per_range, ceil_div(g.rows_vout, (int64_t)WG_SUB)));
+    const int rpc = (int)(ceil_div(ceil_div(g.rows_vout, n_ranges), (int64_t)WG_SUB) * WG_SUB);
     const size_t smem = ((size_t)(WG_SUB - lo + hi) * (WG_KC + 4) + (size_t)WG_SUB * g.cout_v) * sizeof(float);
     dim3 grid((unsigned)ceil_div(g.rows_vout, rpc), (unsigned)(g.cin_v / WG_KC), (unsigned)B);
     if (g.cout_v == 128) {
@@ -670,7 +678,7 @@ extern "C" int spanon_colstats(const float* x, double* stats, int64_t B, int64_t
   if (!x || !stats) return SPANON_ERR_NULL_POINTER;
   cudaStream_t st = as_stream(stream);
   SPANON_CUDA_TRY(cudaMemsetAsync(stats, 0, (size_t)B * C * 2 * sizeof(double), st));
-  const int rpc = 2048;
+  const int rpc = 256;      // (2048 rows per CTA left 160 CTAs with two loads in flight per warp: 0.2 TB/s)
   dim3 grid((unsigned)ceil_div(rows, rpc), (unsigned)B);
   colstats_kernel<<<grid, 256, 0, st>>>(x, stats, rows, (int)C, rpc);
   return check_launch("train:colstats");
@@ -711,7 +719,7 @@ extern "C" int spanon_norm_act_bwd(const float* z, const float* gout, const floa
   if (phase < 0 || phase > 2) return SPANON_ERR_UNSUPPORTED;
   if (gamma && phase != 2) {
     SPANON_CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)B * C * 2 * sizeof(double), st));
-    const int rpc = 2048;
+    const int rpc = 256;    // (see colstats: enough CTAs to keep the loads of a bandwidth-bound reduction in flight)
     dim3 grid((unsigned)ceil_div(rows, rpc), (unsigned)B);
     norm_bwd_reduce_kernel<<<grid, 256, 0, st>>>(z, gout, save_mean, save_rstd, sb, gamma, beta, act, scratch, rows, (int)C, rpc);
     SPANON_TRY(check_launch("train:norm_bwd_reduce"));
