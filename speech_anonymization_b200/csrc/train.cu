@@ -142,9 +142,20 @@ wgrad_kernel(const float* __restrict__ a, const float* __restrict__ g, float* __
 #pragma unroll 4
         for (int r = 0; r < WG_SUB; ++r) {
           const float4 gv = *reinterpret_cast<const float4*>(Gs + r * COUT_V + tx * 4);
+          float avv[CPT];       // this thread's CPT consecutive input channels of row r: ONE vector load (rows are 144 B apart)
+          if constexpr (CPT == 4) {
+            const float4 a4 = *reinterpret_cast<const float4*>(at + r * (WG_KC + 4));
+            avv[0] = a4.x; avv[1] = a4.y; avv[2] = a4.z; avv[3] = a4.w;
+          } else if constexpr (CPT == 2) {
+            const float2 a2 = *reinterpret_cast<const float2*>(at + r * (WG_KC + 4));
+            avv[0] = a2.x; avv[1] = a2.y;
+          } else {
+#pragma unroll
+            for (int i = 0; i < CPT; ++i) avv[i] = at[r * (WG_KC + 4) + i];
+          }
 #pragma unroll
           for (int i = 0; i < CPT; ++i) {
-            const float av = at[r * (WG_KC + 4) + i];
+            const float av = avv[i];
             acc[t][i][0] = fmaf(av, gv.x, acc[t][i][0]); acc[t][i][1] = fmaf(av, gv.y, acc[t][i][1]);
             acc[t][i][2] = fmaf(av, gv.z, acc[t][i][2]); acc[t][i][3] = fmaf(av, gv.w, acc[t][i][3]);
           }
@@ -587,7 +598,7 @@ extern "C" int spanon_tapconv_bwd(const float* in, const float* w, const float* 
     }
     if (gw) {    // gw[0][c][t] = sum_l in[l + t - 7][c] gout[l] = sum_l' in[l'][c] gout[l' - (t - 7)]
       SPANON_CUDA_TRY(cudaMemsetAsync(gw, 0, 32 * 15 * 4, st));
-      const int rpc = 8192;
+      const int rpc = 2048;      // (8192 left 80 CTAs for the 8 x 10 s step)
       dim3 grid((unsigned)ceil_div(L, rpc), (unsigned)B);
       corr15_kernel<<<grid, 256, 0, st>>>(gout, in, L, -1, gw, 15, 1, rpc);
       SPANON_TRY(check_launch("train:conv_c1_wgrad"));
@@ -663,7 +674,7 @@ extern "C" int spanon_conv1_bwd(const float* x, const float* gout, float* gw, fl
   cudaStream_t st = as_stream(stream);
   if (gw) {      // gw[c][0][t] = sum_l x[l + t - 7] gout[l][c]
     SPANON_CUDA_TRY(cudaMemsetAsync(gw, 0, 32 * 15 * 4, st));
-    const int rpc = 8192;
+    const int rpc = 2048;      // (8192 left 80 CTAs for the 8 x 10 s step)
     dim3 grid((unsigned)ceil_div(L, rpc), (unsigned)B);
     corr15_kernel<<<grid, 256, 0, st>>>(x, gout, (int)L, 1, gw, 15, 1, rpc);
     SPANON_TRY(check_launch("train:conv1_wgrad"));
@@ -742,7 +753,7 @@ extern "C" int spanon_pool_reinterp_fwd(const float* x, const float* noise, floa
   if (!x || !out || !save || !scratch) return SPANON_ERR_NULL_POINTER;
   cudaStream_t st = as_stream(stream);
   SPANON_CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)B * 128 * 2 * sizeof(double), st));
-  const int rpc = 1024;
+  const int rpc = 256;       // (a multiple of 128, see the kernel; 1024 left 160 small CTAs for the 8 x 10 s step)
   dim3 grid((unsigned)ceil_div(rows, rpc), (unsigned)B);
   pool_reinterp_sums_kernel<<<grid, 128, 0, st>>>(x, scratch, (int)rows, rpc);
   SPANON_TRY(check_launch("train:pool_sums"));
