@@ -62,11 +62,11 @@ constexpr int TC_EPI_THREADS = 128;       // Toeplitz epilogue (always four warp
 constexpr int TC_STAGE_CH = 16;           // input channels per A stage (one K=16 MMA step per tap)
 constexpr int TC_MAX_STAGES = 32;
 // operand transform of a launch (compile-time: one lean instruction stream per mode, the roles share the I-cache)
-enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16, XF_DYN = 32, XF_FLOW = 64 };
+enum { XF_IDENT = 0, XF_SILU = 1, XF_RELU = 2, XF_T2 = 4, XF_STATS = 8, XF_GEN = 16, XF_DYN = 32, XF_FLOW = 64, XF_EPI8 = 128 };
 constexpr int TC_GEN_SIG = 320;           // fp16 samples of one tile's signal window (XF_GEN)
 constexpr int TC_GEN_SLOTS = 4;           // signal windows in flight (filled by the loader warps, read by the transform warps)
 constexpr int TC_GEN_MAXF = 128;          // mel bins the per-warp (mean, 1/std) table holds
-__host__ __device__ constexpr int tc_epi_warps(int xf) { return (xf & XF_STATS) ? 8 : 4; }
+__host__ __device__ constexpr int tc_epi_warps(int xf) { return (xf & (XF_STATS | XF_EPI8)) ? 8 : 4; }
 constexpr size_t TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int TRACE_N = 128;
 constexpr int TC_TOEP_TAPS = 15;          // decoder.8 as a Toeplitz GEMM: 15 taps -> 16 output columns
@@ -103,7 +103,7 @@ __host__ __device__ inline TcLayout tc_layout(int ntaps, int cin_v, int cout_v, 
   L.epi = L.w + L.w_bytes;                            // bias | e_scale | e_shift   [3][cout_v] fp32
   L.red = L.epi + 3u * cout_v * 4u;                   // Toeplitz epilogue: 2 x [128][17] fp32 copies of the tile;
                                                       // statistics: one [32][17] fp32 transpose buffer per epilogue warp
-  L.sig = L.red + (cout_v == 16 ? 2u * TC_M * 17u * 4u : stats ? 8u * 32u * TC_ST_PITCH * 4u : 0u);
+  L.sig = L.red + (cout_v == 16 ? 4u * TC_M * 17u * 4u : stats ? 8u * 32u * TC_ST_PITCH * 4u : 0u);
   // XF_GEN: ring of TC_GEN_SLOTS signal windows (two fp16 copies each, the second shifted by one sample) + one
   // (mean, 1/std) table per loader warp
   L.bars = L.sig + (gen ? (uint32_t)TC_GEN_SLOTS * 2u * TC_GEN_SIG * 2u + (uint32_t)TC_LOAD_WARPS * 2u * TC_GEN_MAXF * 4u : 0u);
@@ -179,7 +179,8 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
         mbar_init(BAR(B_FULL + i), 1);
         mbar_init(BAR(B_EMPTY + i), 1);
       }
-      for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), E); }
+      // (Toeplitz epilogue on eight warps: each accumulator buffer belongs to ONE group of four warps)
+      for (int i = 0; i < 2; ++i) { mbar_init(BAR(B_TFULL + i), 1); mbar_init(BAR(B_TEMPTY + i), (COUT_V == 16 && E == 8) ? 4 : E); }
       mbar_init(BAR(B_W), 1);
       if constexpr ((XF & XF_GEN) != 0)
         for (int i = 0; i < TC_GEN_SLOTS; ++i) { mbar_init(BAR(B_SFULL + i), 1); mbar_init(BAR(B_SEMPTY + i), (uint32_t)(p.cin_v / TC_STAGE_CH)); }
@@ -265,6 +266,35 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
         if (lane == 0) mbar_arrive(BAR(B_SFULL + slot));
         if (p.trace && lane == 0 && k * n_stage_tile < TRACE_N)
           for (int s2 = 0; s2 < n_stage_tile; ++s2) p.trace[((int64_t)blockIdx.x * 6 + 3) * TRACE_N + k * n_stage_tile + s2] = clock64();
+      }
+    } else if (COUT_V == 16 && n_stage_tile == 2) {
+      // decoder.8 (32 input channels = two stages per tile, 2 KB copies): with one stage per loader and tile the launch was paced
+      // by the loader warps' own instruction chain (~670 cycles per iteration for ~100 dependent instructions, clock64
+      // trace).  Here the two loaders take alternate TILES and issue both stages of a tile from one set of addresses.
+      const __half* in_base = reinterpret_cast<const __half*>(p.in);
+      const int lw = wd >> 2;
+      int b = 0, tin = 0;
+      if (lw < n_my_tiles) locate(lw, b, tin);
+      const int64_t plane_stride = (int64_t)p.rows_in * 8;
+      for (int k = lw; k < n_my_tiles; k += TC_LOAD_WARPS, advance(k, TC_LOAD_WARPS, b, tin)) {
+        const int g0 = tin * tile_step - halo_lo;
+        const int lo = g0 < 0 ? -g0 : 0;
+        const int hi = min(slab_used, p.rows_in - g0);
+        const uint32_t bytes = hi > lo ? (uint32_t)(hi - lo) * 16u : 0u;
+        const __half* src = in_base + (((int64_t)b * planes_in) * p.rows_in + (g0 + lo)) * 8;
+        const uint32_t it0 = (uint32_t)k * 2u;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const uint32_t it = it0 + (uint32_t)s, stage = it % (uint32_t)L.n_stages, ph = (it / (uint32_t)L.n_stages) & 1u;
+          mbar_wait(BAR(B_EMPTY + stage), ph ^ 1u);
+          mbar_expect_tx_elect(BAR(B_RAW + stage), bytes * (TC_STAGE_CH / 8));
+          if (bytes) {
+            const uint32_t dst = s_base + L.a + stage * L.stage_bytes + (uint32_t)lo * 16u;
+            bulk_g2s_elect(dst, src, bytes, BAR(B_RAW + stage));
+            bulk_g2s_elect(dst + L.lbo_a, src + plane_stride, bytes, BAR(B_RAW + stage));
+          }
+          src += (int64_t)(TC_STAGE_CH / 8) * plane_stride;
+        }
       }
     } else {
       const __half* in_base = reinterpret_cast<const __half*>(p.in);
@@ -604,9 +634,14 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
       //      for the 128 slab rows; out[l] = bias + sum_t D[l - m0 + t][t]  (slab row 0 = global row m0 - 7)
       float* dt = reinterpret_cast<float*>(smem + L.red);
       const float bias0 = ec[0];
+      // Per tile the epilogue is ONE latency chain (accumulator load -> transposed store -> barrier -> 15 dependent adds ->
+      // store, ~670 cycles in the clock64 trace) and paced the launch.  With eight warps (XF_EPI8) two groups of four take
+      // alternate tiles -- tile k lives in accumulator buffer k & 1, so each group owns one buffer -- and two chains overlap.
+      constexpr int NG = E / 4;                       // groups of four warps
+      const int grp = warp >> 2;
       int b = 0, tin = 0;
-      if (n_my_tiles > 0) locate(0, b, tin);
-      for (int k = 0; k < n_my_tiles; ++k, advance(k, 1, b, tin)) {
+      if (grp < n_my_tiles) locate(grp, b, tin);
+      for (int k = grp; k < n_my_tiles; k += NG, advance(k, NG, b, tin)) {
         const int m0 = tin * tile_step;
         const uint32_t buf = (uint32_t)k & 1u;
         mbar_wait(BAR(B_TFULL + buf), ((uint32_t)k >> 1) & 1u);
@@ -616,10 +651,13 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(BAR(B_TEMPTY + buf));
-        float* d = dt + buf * (TC_M * 17);
+        // two transposition buffers per group: a group's buffer is rewritten two of ITS tiles later, i.e. after its next barrier
+        float* d = dt + (grp * 2 + (((uint32_t)k / NG) & 1u)) * (TC_M * 17);
 #pragma unroll
         for (int t = 0; t < 16; ++t) d[mloc * 17 + t] = v[t];
-        epi_bar();     // dt[buf] is rewritten two tiles later, i.e. after the next tile's barrier
+        if (NG == 1) epi_bar();
+        else if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+        else asm volatile("bar.sync 2, 128;" ::: "memory");
         const int m = m0 + mloc;
         if (mloc < TC_TOEP_STEP && m < p.rows_out) {
           float acc = bias0;
@@ -940,7 +978,11 @@ int launch_tapgemm_tc(const TapGemmParams& p, int n_sm, cudaStream_t st) {
     if (p.cout_v != 64 || act != XF_IDENT) return SPANON_ERR_UNSUPPORTED;
     return p.stats ? launch_tc<64, XF_GEN | XF_STATS>(p, n_sm, st) : launch_tc<64, XF_GEN>(p, n_sm, st);
   }
-  if (p.cout_v == 16 && xf == XF_SILU) return launch_tc<16, XF_SILU>(p, n_sm, st);
+  if (p.cout_v == 16 && xf == XF_SILU) {
+    // $SPANON_TOEP_EPI8=0: four epilogue warps (A/B switch)
+    static const bool epi8 = !(getenv("SPANON_TOEP_EPI8") && getenv("SPANON_TOEP_EPI8")[0] == '0');
+    return epi8 ? launch_tc<16, XF_SILU | XF_EPI8>(p, n_sm, st) : launch_tc<16, XF_SILU>(p, n_sm, st);
+  }
   if (p.cout_v == 64 && xf == XF_IDENT) return launch_tc<64, XF_IDENT>(p, n_sm, st);
   if (p.cout_v == 64 && xf == XF_SILU) return launch_tc<64, XF_SILU>(p, n_sm, st);
   if (p.cout_v == 128 && xf == XF_IDENT) return launch_tc<128, XF_IDENT>(p, n_sm, st);
