@@ -18,7 +18,7 @@ SETTINGS = [
     {"SPANON_POOL_FUSE": "0"}, {"SPANON_PDL": "0"}, {"SPANON_TC2": "0"},
     {"SPANON_FUSE_ENC0": "0"}, {"SPANON_COMPOSE_DEC": "0"}, {"SPANON_FUSED_STATS": "0"},
     {"SPANON_T2_STAGES": "16", "SPANON_TC_STAGES": "32"}, {"SPANON_TC2_STATS3": "1"},
-    {"SPANON_ENC5_PAIR": "0"}, {"SPANON_DEC45_PAIR": "1"}, {"SPANON_DEC45_PAIR": "1", "SPANON_TC2_UNFOLD4": "0"},
+    {"SPANON_TOEP_EPI8": "0"}, {"SPANON_ENC5_PAIR": "0"}, {"SPANON_DEC45_PAIR": "1"}, {"SPANON_DEC45_PAIR": "1", "SPANON_TC2_UNFOLD4": "0"},
 ]
 
 
