@@ -402,25 +402,7 @@ def run_ours(a):
     ms_sync = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev) / n_sync
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    # ---- sustained: the device-resident step for another --sustained-steps replays (reported beside `value`, never instead
-    # of it).  Under the board's power cap the SM clock sags from ~1.9 GHz in the first tens of milliseconds of load to
-    # ~1.55 GHz; a K-step timed region of 40 - 80 ms sees mostly the former, a long-running service the latter.
     sustained = None
-    if a.sustained_steps > 0:
-        sampler2 = ClockSampler(local)
-        sampler2.start()
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s0.record()
-        for i in range(a.sustained_steps):
-            step_device(a.warmup + a.steps + i)
-        s1.record()
-        torch.cuda.synchronize()
-        sampler2.stop_flag = True
-        sampler2.join(timeout=2)
-        ms_s = max_over_ranks(s0.elapsed_time(s1), world, dev) / a.sustained_steps
-        sustained = {"steps": a.sustained_steps, "ms_per_step": ms_s, "value": world * B * UTT_SECONDS / (ms_s * 1e-3),
-                     "clocks": sampler2.summary()}
-        barrier(world)
     gc.enable()
     e2e = {"value": world * B * UTT_SECONDS / (ms_e2e * 1e-3), "unit": "audio-s/s", "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": B * N_SAMPLES * 2, "d2h_bytes_per_step": B * Tp * 80 * (2 if out16 else 4) + B * 8,
@@ -444,6 +426,25 @@ def run_ours(a):
         k = (a.warmup + a.steps + i) % n_batches
         pipe(dev_pool[k * B:(k + 1) * B], pool_noise=noise)
     prof = _lib.profile_end()
+    # ---- sustained: the device-resident step for another --sustained-steps replays, reported beside `value`, never instead
+    # of it -- and run AFTER the per-kernel profile, so that the profile sees the clocks of the timed region.  Under the
+    # board's power cap the SM clock sags from ~1.9 GHz in the first tens of milliseconds of load to ~1.55 GHz; a K-step
+    # timed region of 40 - 80 ms sees mostly the former, a long-running service the latter.
+    if a.sustained_steps > 0:
+        sampler2 = ClockSampler(local)
+        sampler2.start()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(a.sustained_steps):
+            step_device(a.warmup + a.steps + i)
+        s1.record()
+        torch.cuda.synchronize()
+        sampler2.stop_flag = True
+        sampler2.join(timeout=2)
+        ms_s = max_over_ranks(s0.elapsed_time(s1), world, dev) / a.sustained_steps
+        sustained = {"steps": a.sustained_steps, "ms_per_step": ms_s, "value": world * B * UTT_SECONDS / (ms_s * 1e-3),
+                     "clocks": sampler2.summary()}
+        barrier(world)
     kern = {k: {"launches_per_step": n / n_prof, "ms_per_step": ms / n_prof} for k, (n, ms) in prof.items()}
     prof_ms = sum(v["ms_per_step"] for v in kern.values())
     if a.workload == "convae":
