@@ -760,12 +760,17 @@ __device__ __forceinline__ void tc_body(const TapGemmParams& p, int halo_lo, int
           for (int j = 0; j < 16; ++j) tb[lane * TC_ST_PITCH + j] = valid ? hw[j] : 0u;
           __syncwarp();
           const uint32_t* col = tb + ((lane >> 4) * 16) * TC_ST_PITCH + (lane & 15);
-          float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
+          float a0, a1, q0, q1;
+          {   // packed fp32 pairs (FADD2 / FFMA2): two issue slots per word instead of four
+            float2 sa = make_float2(0.f, 0.f), sq = make_float2(0.f, 0.f);
 #pragma unroll
-          for (int r = 0; r < 16; ++r) {
-            const uint32_t w = col[r * TC_ST_PITCH];
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
-            a0 += f.x; a1 += f.y; q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
+            for (int r = 0; r < 16; ++r) {
+              const uint32_t w = col[r * TC_ST_PITCH];
+              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+              sa = fadd2(sa, f);
+              sq = ffma2(f, f, sq);
+            }
+            a0 = sa.x; a1 = sa.y; q0 = sq.x; q1 = sq.y;
           }
           a0 += __shfl_xor_sync(0xffffffffu, a0, 16); a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
           q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
